@@ -1,0 +1,195 @@
+"""CPU restatement of the 2D joint reprojection + keypoint losses (torch-CPU).
+
+TEST INFRASTRUCTURE -- see ``oracle/__init__.py``.
+
+Parity status: **parity unpinned at the PyTorch3D boundary**.  The reference calls
+``pytorch3d.renderer.FoVPerspectiveCameras.transform_points_screen`` (pytorch3d 0.7.8,
+``environment.yml:35``; call sites ``smal_fitter/p3d_renderer.py:134-137``,
+``smal_fitter/neuralSMIL/multiview_smil_regressor.py:1674-1695``).  PyTorch3D is a
+third-party dependency that is neither vendored in ``/root/reference`` nor installed
+here, so its published algorithm is restated below (row-vector convention, 4x4
+world->view, FoV projection matrix, NDC->screen with xy flip) and cross-checked
+against the reference's *own* OpenCV-side numpy helper
+``project_world_to_pixel`` (``smal_fitter/multiview_common/canonical_frame.py:162-187``)
+composed with ``_sleap_to_pytorch3d_camera``
+(``smal_fitter/sleap_data/sleap_multiview_dataset.py:197-223``) by
+``oracle/pin_against_reference.py``; the loss arithmetic itself follows reference
+Python that is quoted line by line.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+
+
+def look_at_default(dist: float = 2.7, dtype=torch.float32):
+    """``look_at_view_transform(dist, 0, 0)`` as used by ``Renderer.__init__``
+    (p3d_renderer.py:34): camera on +z looking at the origin -> R=diag(-1,1,-1), T=(0,0,dist)."""
+    R = torch.diag(torch.tensor([-1.0, 1.0, -1.0], dtype=dtype))[None]
+    T = torch.tensor([[0.0, 0.0, dist]], dtype=dtype)
+    return R, T
+
+
+def look_at_ring(num_views: int, radius: float, elev_deg: float, dtype=torch.float32):
+    """``look_at_view_transform(dist, elev, azim)`` for cameras on a ring (the set-up of
+    tests/test_triangulation_consistency.py:73-107).  PyTorch3D: camera centre
+    C = dist*(cos e sin a, sin e, cos e cos a); z = normalize(at - C); x = normalize(up x z);
+    y = normalize(z x x); R = [x y z] as columns (row-vector convention); T = -R^T C."""
+    Rs, Ts = [], []
+    for v in range(num_views):
+        a = math.radians(360.0 * v / num_views)
+        e = math.radians(elev_deg)
+        C = torch.tensor([radius * math.cos(e) * math.sin(a), radius * math.sin(e), radius * math.cos(e) * math.cos(a)],
+                         dtype=torch.float64)
+        z = -C / C.norm()
+        up = torch.tensor([0.0, 1.0, 0.0], dtype=torch.float64)
+        x = torch.linalg.cross(up, z)
+        x = x / x.norm()
+        y = torch.linalg.cross(z, x)
+        y = y / y.norm()
+        R = torch.stack([x, y, z], dim=1)  # columns
+        T = -(R.T @ C)
+        Rs.append(R)
+        Ts.append(T)
+    return torch.stack(Rs).to(dtype), torch.stack(Ts).to(dtype)
+
+
+def fov_project_screen(points, R, T, fov_deg, aspect, image_size: float, znear=0.001, zfar=1000.0):
+    """PyTorch3D ``FoVPerspectiveCameras(R,T,fov,aspect).transform_points_screen(points,
+    image_size=(S,S))`` for a square image, returning ``(N,P,3)`` screen xyz.
+
+    points (N,P,3); R (N|1,3,3); T (N|1,3); fov_deg (N|1,); aspect (N|1,).
+    """
+    dt = points.dtype
+    N = points.shape[0]
+    R = R.expand(N, 3, 3)
+    T = T.expand(N, 3)
+    fov = fov_deg.reshape(-1).expand(N) * (math.pi / 180.0)
+    aspect = aspect.reshape(-1).expand(N)
+    # world -> view, row vectors: [X 1] @ [[R 0],[T 1]]
+    W2V = torch.zeros(N, 4, 4, dtype=dt)
+    W2V[:, :3, :3] = R
+    W2V[:, 3, :3] = T
+    W2V[:, 3, 3] = 1.0
+    # FoV projection matrix (column-vector form K, applied transposed)
+    th = torch.tan(fov / 2)
+    max_y = th * znear
+    max_x = max_y * aspect
+    K = torch.zeros(N, 4, 4, dtype=dt)
+    K[:, 0, 0] = 2.0 * znear / (2.0 * max_x)
+    K[:, 1, 1] = 2.0 * znear / (2.0 * max_y)
+    K[:, 3, 2] = 1.0
+    K[:, 2, 2] = zfar / (zfar - znear)
+    K[:, 2, 3] = -(zfar * znear) / (zfar - znear)
+    M = W2V @ K.transpose(1, 2)
+    ph = torch.cat([points, torch.ones(N, points.shape[1], 1, dtype=dt)], dim=2) @ M
+    ndc = ph[..., :3] / ph[..., 3:4]
+    # NDC -> screen with xy flip: x_s = W/2 - (min(H,W)/2) * x_ndc
+    half = image_size / 2.0
+    xs = half - half * ndc[..., 0]
+    ys = half - half * ndc[..., 1]
+    return torch.stack([xs, ys, ndc[..., 2]], dim=-1)
+
+
+def project_yx(points, R, T, fov_deg, aspect, image_size):
+    """``transform_points_screen(...)[:, :, [1, 0]]`` (p3d_renderer.py:137)."""
+    return fov_project_screen(points, R, T, fov_deg, aspect, image_size)[:, :, [1, 0]]
+
+
+# ---- row 9: SMALFitter joint loss (smal_fitter/fitter.py:280-296) ---------------------------
+def fitter_joint_loss(joints, trans, R, T, fov_deg, target_yx, visibility, w_j2d, image_size, canonical=None):
+    j = joints + trans[:, None, :]
+    if canonical is not None:
+        j = j[:, canonical]
+    N = j.shape[0]
+    aspect = torch.ones(1, dtype=j.dtype)
+    p = project_yx(j, R, T, fov_deg, aspect, image_size)
+    vis = visibility.bool()
+    p = torch.where(vis[..., None], p, torch.full_like(p, -1.0))
+    t = torch.where(vis[..., None], target_yx, torch.full_like(target_yx, -1.0))
+    return w_j2d * torch.mean((p - t) ** 2), p
+
+
+# ---- row 10: multi-view loss (multiview_smil_regressor.py:1623-1705, 2319-2388) --------------
+def multiview_project(joints, R, T, fov_deg, aspect, image_size):
+    """joints (B,J,3); cams (B,V,...) -> (B,V,J,2) normalised (y,x), clamped to [0,1]."""
+    B, V = R.shape[:2]
+    J = joints.shape[1]
+    jf = joints[:, None].expand(B, V, J, 3).reshape(B * V, J, 3)
+    p = project_yx(jf, R.reshape(B * V, 3, 3), T.reshape(B * V, 3), fov_deg.reshape(B * V), aspect.reshape(B * V),
+                   image_size)
+    p = p / (float(image_size) + 1e-8)
+    return torch.clamp(p, 0.0, 1.0).reshape(B, V, J, 2)
+
+
+def multiview_keypoint_loss(pred, target, visibility, view_mask=None, joint_weights=None):
+    eps = 1e-8
+    pred = torch.nan_to_num(pred, nan=0.0, posinf=0.0, neginf=0.0)
+    valid = visibility.bool() & ((target >= 0.0) & (target <= 1.0)).all(dim=-1)
+    if view_mask is not None:
+        valid = valid & view_mask.bool()[..., None]
+    if not valid.any():
+        return torch.tensor(eps, dtype=pred.dtype)
+    w = valid.to(pred.dtype)[..., None]
+    if joint_weights is not None:
+        w = w * joint_weights.view(1, 1, -1, 1)
+        denom = (valid.to(pred.dtype) * joint_weights.view(1, 1, -1)).sum() * 2 + eps
+    else:
+        denom = valid.sum().to(pred.dtype) * 2 + eps
+    return (((pred - target) ** 2) * w).sum() / denom + eps
+
+
+# ---- row 11: single-view losses (smil_image_regressor.py:2727-2732, 3032-3115, 3334-3407) -----
+def singleview_project(joints, R, T, fov_deg, image_size, norm_size=512.0):
+    aspect = torch.ones(1, dtype=joints.dtype)
+    p = project_yx(joints, R, T, fov_deg, aspect, image_size) / (norm_size + 1e-8)
+    return torch.clamp(p, -10.0, 10.0)
+
+
+def singleview_keypoint_loss(pred, target, visibility, joint_weights=None, sample_mask=None):
+    """Per-sample normalisation then mean over samples that have >=1 valid joint."""
+    eps = 1e-8
+    total, nvalid = 0.0, 0
+    for i in range(pred.shape[0]):
+        if sample_mask is not None and not bool(sample_mask[i]):
+            continue
+        valid = visibility[i].bool() & ((target[i] >= 0.0) & (target[i] <= 1.0)).all(dim=-1)
+        p = torch.nan_to_num(pred[i], nan=0.0, posinf=0.0, neginf=0.0)
+        if not valid.any():
+            continue
+        mw = valid.to(pred.dtype)
+        if joint_weights is not None:
+            mw = mw * joint_weights
+            denom = (valid.to(pred.dtype) * joint_weights).sum() * 2 + eps
+        else:
+            denom = valid.sum().to(pred.dtype) * 2 + eps
+        total = total + (((p - target[i]) ** 2) * mw[:, None]).sum() / denom
+        nvalid += 1
+    if nvalid == 0:
+        return torch.tensor(eps, dtype=pred.dtype)
+    return total / nvalid + eps
+
+
+def keypoint3d_loss(joints3d, target3d, visibility, joint_weights=None, sample_mask=None):
+    eps = 1e-8
+    total, nvalid = 0.0, 0
+    for i in range(joints3d.shape[0]):
+        if sample_mask is not None and not bool(sample_mask[i]):
+            continue
+        finite = torch.isfinite(joints3d[i]).all(dim=-1) & torch.isfinite(target3d[i]).all(dim=-1)
+        valid = visibility[i].bool() & finite & (target3d[i].abs().sum(dim=-1) > 0)
+        if not valid.any():
+            continue
+        mw = valid.to(joints3d.dtype)
+        if joint_weights is not None:
+            mw = mw * joint_weights
+            denom = (valid.to(joints3d.dtype) * joint_weights).sum() * 3 + eps
+        else:
+            denom = valid.sum().to(joints3d.dtype) * 3 + eps
+        total = total + (((joints3d[i] - target3d[i]) ** 2) * mw[:, None]).sum() / denom
+        nvalid += 1
+    if nvalid == 0:
+        return torch.tensor(eps, dtype=joints3d.dtype)
+    return total / nvalid + eps
