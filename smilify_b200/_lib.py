@@ -1,0 +1,219 @@
+"""ctypes binding of ``libsmil_b200.so`` (the C ABI in ``include/smil_b200.h``).
+
+There is no CPU fallback: if the shared library is missing or a call fails, a RuntimeError is
+raised with the library's own message."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsmil_b200.so")
+ABI_VERSION = 1
+
+c_f = C.POINTER(C.c_float)
+c_i = C.POINTER(C.c_int32)
+
+
+class SmilModelDesc(C.Structure):
+    _fields_ = [
+        ("device", C.c_int32), ("num_verts", C.c_int32), ("num_joints", C.c_int32), ("num_betas", C.c_int32),
+        ("num_pose_basis", C.c_int32), ("skin_k", C.c_int32), ("jreg_nnz", C.c_int32), ("num_levels", C.c_int32),
+        ("max_width", C.c_int32), ("num_pairs", C.c_int32), ("has_static", C.c_int32),
+        ("fwd_chunk", C.c_int32), ("fwd_nchunk", C.c_int32), ("v_pad", C.c_int32),
+        ("bwd_chunk", C.c_int32), ("bwd_ntile", C.c_int32), ("bwd_warps", C.c_int32), ("bwd_rec", C.c_int32),
+        ("num_units", C.c_int32), ("num_items", C.c_int32), ("bwd_max_tile_items", C.c_int32), ("fused_ok", C.c_int32),
+        ("v_template", c_f), ("shapedirs", c_f), ("posedirs", c_f), ("J_static", c_f),
+        ("skin_idx", c_i), ("skin_w", c_f),
+        ("jc_ptr", c_i), ("jc_vid", c_i), ("jc_val", c_f),
+        ("jr_ptr", c_i), ("jr_jid", c_i), ("jr_val", c_f),
+        ("parents", c_i), ("order", c_i), ("level_ptr", c_i), ("child_ptr", c_i), ("child_idx", c_i),
+        ("JT", c_f), ("JS", c_f), ("jreg_rowsum", c_f),
+        ("pj_ptr", c_i), ("pj_bone", c_i), ("pj_joint", c_i), ("pj_c0", c_f), ("pj_cm", c_f),
+        ("pb_ptr", c_i), ("pb_pair", c_i),
+        ("vconst", c_f), ("ell_idx", c_i), ("ell_w", c_f),
+        ("vrec", c_f), ("unit_bone", c_i), ("unit_ptr", c_i), ("unit_tile", c_i), ("tile_unit_ptr", c_i),
+        ("warp_unit_ptr", c_i), ("warp_unit", c_i), ("it_v", c_i), ("it_w", c_f), ("it_first", c_f),
+        ("sb_ptr", c_i), ("sb_slot", c_i),
+    ]
+
+
+class SmilModelInfo(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "num_verts", "num_joints", "num_betas", "num_pose_basis", "skin_k", "jreg_nnz", "tree_depth",
+        "max_level_width", "posedirs_zero", "joint_bone_pairs", "num_chunks", "num_ga_slots")]
+
+
+class SmilFwdArgs(C.Structure):
+    _fields_ = [
+        ("batch", C.c_int32), ("num_betas_used", C.c_int32), ("flags", C.c_uint32), ("_pad", C.c_int32),
+        ("beta", C.c_void_p), ("beta_stride", C.c_int64),
+        ("theta", C.c_void_p), ("theta_stride", C.c_int64),
+        ("trans", C.c_void_p), ("trans_stride", C.c_int64),
+        ("betas_logscale", C.c_void_p), ("logscale_stride", C.c_int64),
+        ("betas_trans", C.c_void_p), ("btrans_stride", C.c_int64),
+        ("del_v", C.c_void_p), ("del_v_stride", C.c_int64),
+        ("v_template", C.c_void_p),
+        ("verts", C.c_void_p), ("joints", C.c_void_p), ("Rs", C.c_void_p), ("v_shaped", C.c_void_p),
+        ("J_transformed", C.c_void_p),
+        ("saved", C.c_void_p), ("saved_bytes", C.c_size_t),
+        ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+    ]
+
+
+class SmilBwdArgs(C.Structure):
+    _fields_ = [
+        ("fwd", SmilFwdArgs),
+        ("g_verts", C.c_void_p), ("g_joints", C.c_void_p), ("g_Rs", C.c_void_p), ("g_v_shaped", C.c_void_p),
+        ("g_beta", C.c_void_p), ("g_theta", C.c_void_p), ("g_trans", C.c_void_p), ("g_logscale", C.c_void_p),
+        ("g_btrans", C.c_void_p), ("g_del_v", C.c_void_p),
+        ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+    ]
+
+
+class SmilChainArgs(C.Structure):
+    _fields_ = [
+        ("batch", C.c_int32), ("flags", C.c_uint32),
+        ("Rs", C.c_void_p), ("Js", C.c_void_p), ("betas_logscale", C.c_void_p), ("betas_trans", C.c_void_p),
+        ("new_J", C.c_void_p), ("A", C.c_void_p),
+        ("g_new_J", C.c_void_p), ("g_A", C.c_void_p),
+        ("g_Rs", C.c_void_p), ("g_Js", C.c_void_p), ("g_logscale", C.c_void_p), ("g_btrans", C.c_void_p),
+    ]
+
+
+class SmilProjArgs(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int32), ("batch", C.c_int32), ("num_views", C.c_int32), ("num_joints", C.c_int32),
+        ("image_size", C.c_float), ("norm_size", C.c_float), ("clamp_lo", C.c_float), ("clamp_hi", C.c_float),
+        ("weight", C.c_float), ("_pad", C.c_int32),
+        ("joints", C.c_void_p), ("joints_stride", C.c_int64),
+        ("cam_R", C.c_void_p), ("R_bstride", C.c_int64), ("R_vstride", C.c_int64),
+        ("cam_T", C.c_void_p), ("T_bstride", C.c_int64), ("T_vstride", C.c_int64),
+        ("fov_deg", C.c_void_p), ("fov_bstride", C.c_int64), ("fov_vstride", C.c_int64),
+        ("aspect", C.c_void_p), ("asp_bstride", C.c_int64), ("asp_vstride", C.c_int64),
+        ("target", C.c_void_p), ("visibility", C.c_void_p), ("view_mask", C.c_void_p),
+        ("joint_weights", C.c_void_p), ("sample_mask", C.c_void_p),
+        ("proj", C.c_void_p), ("loss", C.c_void_p), ("partials", C.c_void_p),
+        ("g_loss", C.c_void_p), ("g_joints", C.c_void_p), ("g_cam_R", C.c_void_p), ("g_cam_T", C.c_void_p),
+        ("g_fov", C.c_void_p),
+    ]
+
+
+class SmilKp3dArgs(C.Structure):
+    _fields_ = [
+        ("batch", C.c_int32), ("num_joints", C.c_int32),
+        ("joints", C.c_void_p), ("target", C.c_void_p), ("visibility", C.c_void_p), ("joint_weights", C.c_void_p),
+        ("sample_mask", C.c_void_p), ("loss", C.c_void_p), ("partials", C.c_void_p),
+        ("g_loss", C.c_void_p), ("g_joints", C.c_void_p),
+    ]
+
+
+F_THETA_IS_ROTMAT = 1 << 0
+F_STATIC_JOINTS = 1 << 1
+F_PROPAGATE_SCALING = 1 << 2
+F_JOINTS_ONLY = 1 << 3
+F_FORCE_GENERIC = 1 << 4
+LOSS_FITTER, LOSS_MULTIVIEW, LOSS_SINGLEVIEW = 0, 1, 2
+
+# every symbol include/smil_b200.h declares
+EXPORTS = (
+    "smil_abi_version", "smil_last_error", "smil_model_create", "smil_model_destroy", "smil_model_info",
+    "smil_saved_bytes", "smil_fwd_scratch_bytes", "smil_bwd_scratch_bytes", "smil_forward", "smil_backward",
+    "smil_rodrigues_forward", "smil_rodrigues_backward", "smil_chain_forward", "smil_chain_backward",
+    "smil_project_loss_forward", "smil_project_loss_backward", "smil_keypoint3d_loss_forward",
+    "smil_keypoint3d_loss_backward",
+)
+
+_lib = None
+
+
+def lib():
+    """The loaded library; raises loudly when it is missing (no CPU fallback exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "smilify_b200: %s is missing -- build it with `python -m smilify_b200.build` "
+            "(there is no CPU fallback)" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    L.smil_abi_version.restype = C.c_int
+    L.smil_last_error.restype = C.c_char_p
+    L.smil_model_create.argtypes = [C.POINTER(SmilModelDesc), C.POINTER(C.c_void_p)]
+    L.smil_model_destroy.argtypes = [C.c_void_p]
+    L.smil_model_destroy.restype = None
+    L.smil_model_info.argtypes = [C.c_void_p, C.POINTER(SmilModelInfo)]
+    L.smil_saved_bytes.argtypes = [C.c_void_p, C.c_int32, C.c_uint32]
+    L.smil_saved_bytes.restype = C.c_size_t
+    L.smil_fwd_scratch_bytes.argtypes = [C.c_void_p, C.POINTER(SmilFwdArgs)]
+    L.smil_fwd_scratch_bytes.restype = C.c_size_t
+    L.smil_bwd_scratch_bytes.argtypes = [C.c_void_p, C.POINTER(SmilBwdArgs)]
+    L.smil_bwd_scratch_bytes.restype = C.c_size_t
+    L.smil_forward.argtypes = [C.c_void_p, C.POINTER(SmilFwdArgs), C.c_void_p]
+    L.smil_backward.argtypes = [C.c_void_p, C.POINTER(SmilBwdArgs), C.c_void_p]
+    L.smil_rodrigues_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+    L.smil_rodrigues_backward.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+    L.smil_chain_forward.argtypes = [C.c_void_p, C.POINTER(SmilChainArgs), C.c_void_p]
+    L.smil_chain_backward.argtypes = [C.c_void_p, C.POINTER(SmilChainArgs), C.c_void_p]
+    L.smil_project_loss_forward.argtypes = [C.POINTER(SmilProjArgs), C.c_void_p]
+    L.smil_project_loss_backward.argtypes = [C.POINTER(SmilProjArgs), C.c_void_p]
+    L.smil_keypoint3d_loss_forward.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
+    L.smil_keypoint3d_loss_backward.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
+    for name in EXPORTS:
+        fn = getattr(L, name)
+        if fn.restype is C.c_int and name not in ("smil_abi_version",):
+            pass
+    if L.smil_abi_version() != ABI_VERSION:
+        raise RuntimeError("smilify_b200: ABI mismatch (library %d, binding %d)" % (L.smil_abi_version(), ABI_VERSION))
+    _lib = L
+    return L
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = lib().smil_last_error()
+        raise RuntimeError("%s failed (%d): %s" % (what, rc, msg.decode("utf-8", "replace") if msg else "?"))
+
+
+def _np_ptr(a: np.ndarray, ctype):
+    if a is None or a.size == 0:
+        return C.cast(None, C.POINTER(ctype))
+    return a.ctypes.data_as(C.POINTER(ctype))
+
+
+_DESC_F32 = ("v_template", "shapedirs", "posedirs", "J_static", "skin_w", "jc_val", "jr_val", "JT", "JS", "jreg_rowsum",
+             "pj_c0", "pj_cm", "vconst", "ell_w", "vrec", "it_w", "it_first")
+_DESC_I32 = ("skin_idx", "jc_ptr", "jc_vid", "jr_ptr", "jr_jid", "parents", "order", "level_ptr", "child_ptr",
+             "child_idx", "pj_ptr", "pj_bone", "pj_joint", "pb_ptr", "pb_pair", "ell_idx", "unit_bone", "unit_ptr",
+             "unit_tile", "tile_unit_ptr", "warp_unit_ptr", "warp_unit", "it_v", "sb_ptr", "sb_slot")
+
+
+def desc_from_tables(t: dict, device: int):
+    """Fill a SmilModelDesc from packer tables.  Returns (desc, keepalive list)."""
+    d = SmilModelDesc()
+    keep = []
+    d.device = device
+    d.num_verts, d.num_joints, d.num_betas, d.num_pose_basis = t.get("V", 0), t["J"], t.get("nB", 0), t.get("P", 0)
+    d.skin_k, d.jreg_nnz = t.get("K", 0), t.get("jreg_nnz", 0)
+    d.num_levels, d.max_width, d.num_pairs = t["num_levels"], t["max_width"], t.get("npairs", 0)
+    js = t.get("J_static")
+    d.has_static = int(js is not None and js.size > 0)
+    d.fwd_chunk, d.fwd_nchunk, d.v_pad = t.get("fwd_chunk", 0), t.get("fwd_nchunk", 0), t.get("Vpad", 0)
+    d.bwd_chunk, d.bwd_ntile, d.bwd_warps, d.bwd_rec = (t.get("bwd_chunk", 0), t.get("bwd_ntile", 0),
+                                                        t.get("bwd_warps", 0), t.get("bwd_rec", 0))
+    d.num_units, d.num_items = t.get("nunits", 0), t.get("nitems", 0)
+    d.bwd_max_tile_items = t.get("bwd_max_tile_items", 0)
+    d.fused_ok = int(t.get("fused_ok", False))
+    for name in _DESC_F32:
+        a = t.get(name)
+        a = np.ascontiguousarray(a, dtype=np.float32) if a is not None else None
+        keep.append(a)
+        setattr(d, name, _np_ptr(a, C.c_float))
+    for name in _DESC_I32:
+        a = t.get(name)
+        a = np.ascontiguousarray(a, dtype=np.int32) if a is not None else None
+        keep.append(a)
+        setattr(d, name, _np_ptr(a, C.c_int32))
+    return d, keep

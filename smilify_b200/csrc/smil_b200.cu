@@ -1,0 +1,604 @@
+// C-ABI entry points of the B200-native SMAL/SMIL hot path (see include/smil_b200.h).
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -shared -Xcompiler -fPIC
+#include <new>
+#include <vector>
+
+#include "fused_kernels.cuh"
+#include "generic_kernels.cuh"
+#include "pose_kernels.cuh"
+#include "proj_kernels.cuh"
+#include "smil_common.cuh"
+
+using namespace smil;
+
+struct SmilModel {
+  DevModel d;
+};
+
+namespace {
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct ArenaPlan {
+  struct Item { const void* src; size_t bytes; const void** dst; };
+  std::vector<Item> items;
+  size_t total = 0;
+  template <typename T>
+  void add(const T* src, size_t count, const T** dst) {
+    *dst = nullptr;
+    if (!src || count == 0) return;
+    items.push_back({src, count * sizeof(T), reinterpret_cast<const void**>(dst)});
+    total = align_up(total, 256) + count * sizeof(T);
+  }
+};
+
+inline int pick_lps(int max_width) { return max_width <= 8 ? 8 : (max_width <= 16 ? 16 : 32); }
+
+inline int nbt_of(int nb) {
+  static const int vals[] = {1, 2, 3, 4, 5, 6, 8, 10, 13, 16};
+  for (int v : vals)
+    if (v >= nb) return v;
+  return 0;
+}
+
+template <typename Kern>
+int set_smem(Kern k, size_t bytes) {
+  if (bytes > 227 * 1024) return fail(SMIL_EUNSUPPORTED, "kernel needs %zu bytes of shared memory (> 227 KB)", bytes);
+  if (bytes > 48 * 1024) SMIL_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return SMIL_OK;
+}
+
+// ---- pose kernel launchers ---------------------------------------------------------------------
+int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_t st) {
+  const int lps = pick_lps(m.max_width);
+  PoseSmem L;
+  L.J = m.J;
+  L.nbp = (std::max(a.nb, 1) + 3) & ~3;
+  L.lps = lps;
+  const int spb = POSE_THREADS / lps;
+  const size_t per = (size_t)(((backward ? L.bwd_floats() : L.fwd_floats()) + 3) & ~3) * sizeof(float);
+  const size_t smem = per * spb;
+  const int grid = (a.B + spb - 1) / spb;
+  int rc = SMIL_OK;
+#define SMIL_POSE_CASE(LPS)                                                           \
+  if (lps == LPS) {                                                                   \
+    if (backward) {                                                                   \
+      if ((rc = set_smem(pose_bwd_kernel<LPS>, smem)) != SMIL_OK) return rc;          \
+      pose_bwd_kernel<LPS><<<grid, POSE_THREADS, smem, st>>>(m, a, L);                \
+    } else {                                                                          \
+      if ((rc = set_smem(pose_fwd_kernel<LPS>, smem)) != SMIL_OK) return rc;          \
+      pose_fwd_kernel<LPS><<<grid, POSE_THREADS, smem, st>>>(m, a, L);                \
+    }                                                                                 \
+  }
+  SMIL_POSE_CASE(8)
+  SMIL_POSE_CASE(16)
+  SMIL_POSE_CASE(32)
+#undef SMIL_POSE_CASE
+  SMIL_LAUNCH_CHECK(backward ? "pose_bwd_kernel" : "pose_fwd_kernel");
+  return SMIL_OK;
+}
+
+// ---- fused skin launchers ----------------------------------------------------------------------
+template <int NBT, int K>
+int launch_skin_fwd_inst(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
+  const size_t smem = skin_fwd_smem_bytes(a.G, m.J, NBT, SKIN_FWD_THREADS);
+  int rc = set_smem(skin_fwd_kernel<NBT, K>, smem);
+  if (rc != SMIL_OK) return rc;
+  dim3 grid(m.fwd_nchunk, (a.B + a.G - 1) / a.G);
+  skin_fwd_kernel<NBT, K><<<grid, SKIN_FWD_THREADS, smem, st>>>(m, a);
+  SMIL_LAUNCH_CHECK("skin_fwd_kernel");
+  return SMIL_OK;
+}
+template <int NBT>
+int launch_skin_fwd_k(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
+  if (m.K <= 1) return launch_skin_fwd_inst<NBT, 1>(m, a, st);
+  if (m.K <= 2) return launch_skin_fwd_inst<NBT, 2>(m, a, st);
+  return launch_skin_fwd_inst<NBT, 4>(m, a, st);
+}
+int launch_skin_fwd(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
+  switch (nbt_of(a.nb)) {
+    case 1: return launch_skin_fwd_k<1>(m, a, st);
+    case 2: return launch_skin_fwd_k<2>(m, a, st);
+    case 3: return launch_skin_fwd_k<3>(m, a, st);
+    case 4: return launch_skin_fwd_k<4>(m, a, st);
+    case 5: return launch_skin_fwd_k<5>(m, a, st);
+    case 6: return launch_skin_fwd_k<6>(m, a, st);
+    case 8: return launch_skin_fwd_k<8>(m, a, st);
+    case 10: return launch_skin_fwd_k<10>(m, a, st);
+    case 13: return launch_skin_fwd_k<13>(m, a, st);
+    case 16: return launch_skin_fwd_k<16>(m, a, st);
+  }
+  return fail(SMIL_EUNSUPPORTED, "fused forward: %d betas not covered", a.nb);
+}
+
+template <int NBT>
+int launch_skin_bwd_inst(const DevModel& m, const SkinBwdArgs& a, cudaStream_t st) {
+  const size_t smem = skin_bwd_smem_bytes(m.bwd_chunk, m.bwd_rec, a.max_tile_items, NBT);
+  int rc = set_smem(skin_bwd_kernel<NBT>, smem);
+  if (rc != SMIL_OK) return rc;
+  const int ngroups = (a.B + SKIN_BWD_G - 1) / SKIN_BWD_G;
+  dim3 grid(m.bwd_ntile, (ngroups + a.groups_per_cta - 1) / a.groups_per_cta);
+  skin_bwd_kernel<NBT><<<grid, 128, smem, st>>>(m, a);
+  SMIL_LAUNCH_CHECK("skin_bwd_kernel");
+  return SMIL_OK;
+}
+int launch_skin_bwd(const DevModel& m, const SkinBwdArgs& a, cudaStream_t st) {
+  switch (nbt_of(a.nb)) {
+    case 1: return launch_skin_bwd_inst<1>(m, a, st);
+    case 2: return launch_skin_bwd_inst<2>(m, a, st);
+    case 3: return launch_skin_bwd_inst<3>(m, a, st);
+    case 4: return launch_skin_bwd_inst<4>(m, a, st);
+    case 5: return launch_skin_bwd_inst<5>(m, a, st);
+    case 6: return launch_skin_bwd_inst<6>(m, a, st);
+    case 8: return launch_skin_bwd_inst<8>(m, a, st);
+    case 10: return launch_skin_bwd_inst<10>(m, a, st);
+    case 13: return launch_skin_bwd_inst<13>(m, a, st);
+    case 16: return launch_skin_bwd_inst<16>(m, a, st);
+  }
+  return fail(SMIL_EUNSUPPORTED, "fused backward: %d betas not covered", a.nb);
+}
+
+// ---- mode selection shared by forward and backward ---------------------------------------------
+struct Plan {
+  bool fused;      // fused skinning + closed-form regressions
+  bool is_static;
+  bool rotmat;
+  bool joints_only;
+  int jrest_mode;  // 0 closed form, 1 static, 2 regressed from v_shaped (saved)
+};
+
+int make_plan(const DevModel& m, const SmilFwdArgs& f, Plan* p) {
+  if (f.batch <= 0) return fail(SMIL_EINVAL, "batch must be positive (got %d)", f.batch);
+  if (f.num_betas_used < 0 || f.num_betas_used > m.nB)
+    return fail(SMIL_EINVAL, "num_betas_used=%d outside [0,%d]", f.num_betas_used, m.nB);
+  if (f.num_betas_used == 0 && f.batch != 1)
+    return fail(SMIL_EINVAL, "beta with 0 columns is only defined for batch 1 (smal_torch.py:250-253)");
+  if (!f.theta) return fail(SMIL_EINVAL, "theta is NULL");
+  if (f.num_betas_used > 0 && !f.beta) return fail(SMIL_EINVAL, "beta is NULL");
+  p->is_static = (f.flags & SMIL_F_STATIC_JOINTS) != 0;
+  if (p->is_static && !m.has_static) return fail(SMIL_EINVAL, "STATIC_JOINTS requested but the model has no J table");
+  p->rotmat = (f.flags & SMIL_F_THETA_IS_ROTMAT) != 0;
+  p->joints_only = (f.flags & SMIL_F_JOINTS_ONLY) != 0;
+  const bool custom_shape = f.del_v != nullptr || f.v_template != nullptr;
+  p->fused = m.fused_ok && !custom_shape && !(f.flags & SMIL_F_FORCE_GENERIC);
+  p->jrest_mode = p->is_static ? 1 : (custom_shape ? 2 : 0);
+  return SMIL_OK;
+}
+
+size_t saved_bytes_for(const DevModel& m, int B) { return align_up((size_t)B * m.J * 12 * 4, 256) + (size_t)B * m.J * 3 * 4; }
+
+PoseArgs base_pose_args(const DevModel& m, const SmilFwdArgs& f, const Plan& p) {
+  PoseArgs a;
+  memset(&a, 0, sizeof(a));
+  a.B = f.batch;
+  a.nb = f.num_betas_used;
+  a.flags = f.flags;
+  a.jrest_mode = p.jrest_mode;
+  a.beta = f.beta; a.beta_stride = f.beta_stride;
+  a.theta = f.theta; a.theta_stride = f.theta_stride;
+  a.trans = f.trans; a.trans_stride = f.trans_stride;
+  a.ls = f.betas_logscale; a.ls_stride = f.logscale_stride;
+  a.bt = f.betas_trans; a.bt_stride = f.btrans_stride;
+  (void)m;
+  return a;
+}
+
+inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+}  // namespace
+
+// =====================================================================================================
+extern "C" {
+
+int smil_abi_version(void) { return SMIL_ABI_VERSION; }
+const char* smil_last_error(void) { return err_buf(); }
+
+int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
+  if (!s || !out) return fail(SMIL_EINVAL, "smil_model_create: NULL argument");
+  *out = nullptr;
+  if (s->num_joints <= 0) return fail(SMIL_EINVAL, "num_joints must be positive");
+  if (!s->parents || !s->order || !s->level_ptr || !s->child_ptr)
+    return fail(SMIL_EINVAL, "tree tables (parents/order/level_ptr/child_ptr) are required");
+  SMIL_CUDA(cudaSetDevice(s->device));
+  SmilModel* M = new (std::nothrow) SmilModel();
+  if (!M) return fail(SMIL_ENOMEM, "out of host memory");
+  DevModel& d = M->d;
+  memset(&d, 0, sizeof(d));
+  d.V = s->num_verts; d.J = s->num_joints; d.nB = s->num_betas; d.P = s->num_pose_basis; d.K = s->skin_k;
+  d.jreg_nnz = s->jreg_nnz; d.num_levels = s->num_levels; d.max_width = s->max_width; d.npairs = s->num_pairs;
+  d.has_static = s->has_static && s->J_static;
+  d.fwd_chunk = s->fwd_chunk; d.fwd_nchunk = s->fwd_nchunk; d.v_pad = s->v_pad;
+  d.bwd_chunk = s->bwd_chunk; d.bwd_ntile = s->bwd_ntile; d.bwd_warps = s->bwd_warps; d.bwd_rec = s->bwd_rec;
+  d.num_units = s->num_units; d.num_items = s->num_items;
+  d.h_max_units_per_tile = s->bwd_max_tile_items;
+  d.fused_ok = s->fused_ok && d.V > 0 && s->fwd_chunk == SKIN_FWD_THREADS && s->bwd_warps == 4 && d.K <= 4 &&
+               nbt_of(d.nB) > 0 && d.P == 0 && (s->bwd_chunk % 32) == 0 &&
+               s->bwd_rec >= 4 * ((3 + 3 * nbt_of(d.nB) + 3) / 4);
+  d.device = s->device;
+  SMIL_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, s->device));
+
+  const size_t V = d.V, J = d.J, nB = d.nB, K = d.K, np = std::max(d.npairs, 1);
+  ArenaPlan ap;
+  ap.add(s->v_template, V * 3, &d.v_template);
+  ap.add(s->shapedirs, nB * 3 * V, &d.shapedirs);
+  ap.add(s->posedirs, (size_t)d.P * 3 * V, &d.posedirs);
+  ap.add(s->J_static, d.has_static ? J * 3 : 0, &d.J_static);
+  ap.add(s->skin_idx, V * K, &d.skin_idx);
+  ap.add(s->skin_w, V * K, &d.skin_w);
+  ap.add(s->jc_ptr, V ? J + 1 : 0, &d.jc_ptr);
+  ap.add(s->jc_vid, V ? std::max(d.jreg_nnz, 1) : 0, &d.jc_vid);
+  ap.add(s->jc_val, V ? std::max(d.jreg_nnz, 1) : 0, &d.jc_val);
+  ap.add(s->jr_ptr, V ? V + 1 : 0, &d.jr_ptr);
+  ap.add(s->jr_jid, V ? std::max(d.jreg_nnz, 1) : 0, &d.jr_jid);
+  ap.add(s->jr_val, V ? std::max(d.jreg_nnz, 1) : 0, &d.jr_val);
+  ap.add(s->parents, J, &d.parents);
+  ap.add(s->order, J, &d.order);
+  ap.add(s->level_ptr, (size_t)d.num_levels + 1, &d.level_ptr);
+  ap.add(s->child_ptr, J + 1, &d.child_ptr);
+  ap.add(s->child_idx, std::max<size_t>(J - 1, 1), &d.child_idx);
+  ap.add(s->JT, V ? J * 3 : 0, &d.JT);
+  ap.add(s->JS, V ? nB * J * 3 : 0, &d.JS);
+  ap.add(s->jreg_rowsum, V ? J : 0, &d.jreg_rowsum);
+  ap.add(s->pj_ptr, V ? J + 1 : 0, &d.pj_ptr);
+  ap.add(s->pj_bone, V ? np : 0, &d.pj_bone);
+  ap.add(s->pj_joint, V ? np : 0, &d.pj_joint);
+  ap.add(s->pj_c0, V ? np * 4 : 0, &d.pj_c0);
+  ap.add(s->pj_cm, V ? np * std::max<size_t>(nB, 1) * 3 : 0, &d.pj_cm);
+  ap.add(s->pb_ptr, V ? J + 1 : 0, &d.pb_ptr);
+  ap.add(s->pb_pair, V ? np : 0, &d.pb_pair);
+  ap.add(s->vconst, (3 + 3 * nB) * (size_t)d.v_pad, &d.vconst);
+  ap.add(s->ell_idx, K * (size_t)d.v_pad, &d.ell_idx);
+  ap.add(s->ell_w, K * (size_t)d.v_pad, &d.ell_w);
+  ap.add(s->vrec, (size_t)d.bwd_ntile * d.bwd_chunk * d.bwd_rec, &d.vrec);
+  ap.add(s->unit_bone, (size_t)d.num_units, &d.unit_bone);
+  ap.add(s->unit_ptr, d.num_units ? (size_t)d.num_units + 1 : 0, &d.unit_ptr);
+  ap.add(s->unit_tile, (size_t)d.num_units, &d.unit_tile);
+  ap.add(s->tile_unit_ptr, d.num_units ? (size_t)d.bwd_ntile + 1 : 0, &d.tile_unit_ptr);
+  ap.add(s->warp_unit_ptr, d.num_units ? (size_t)d.bwd_ntile * d.bwd_warps + 1 : 0, &d.warp_unit_ptr);
+  ap.add(s->warp_unit, (size_t)d.num_units, &d.warp_unit);
+  ap.add(s->it_v, (size_t)d.num_items, &d.it_v);
+  ap.add(s->it_w, (size_t)d.num_items, &d.it_w);
+  ap.add(s->it_first, (size_t)d.num_items, &d.it_first);
+  ap.add(s->sb_ptr, d.num_units ? J + 1 : 0, &d.sb_ptr);
+  ap.add(s->sb_slot, (size_t)d.num_units, &d.sb_slot);
+
+  void* arena = nullptr;
+  cudaError_t e = cudaMalloc(&arena, std::max<size_t>(ap.total, 256));
+  if (e != cudaSuccess) {
+    delete M;
+    return fail(SMIL_ENOMEM, "cudaMalloc of %zu bytes for the packed model failed: %s", ap.total, cudaGetErrorString(e));
+  }
+  d.arena = arena;
+  size_t off = 0;
+  for (auto& it : ap.items) {
+    off = align_up(off, 256);
+    e = cudaMemcpy(static_cast<char*>(arena) + off, it.src, it.bytes, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+      cudaFree(arena);
+      delete M;
+      return fail(SMIL_ECUDA, "upload of a model table failed: %s", cudaGetErrorString(e));
+    }
+    *it.dst = static_cast<char*>(arena) + off;
+    off += it.bytes;
+  }
+  *out = M;
+  return SMIL_OK;
+}
+
+void smil_model_destroy(SmilModel* model) {
+  if (!model) return;
+  if (model->d.arena) cudaFree(model->d.arena);
+  delete model;
+}
+
+int smil_model_info(const SmilModel* model, SmilModelInfo* info) {
+  if (!model || !info) return fail(SMIL_EINVAL, "smil_model_info: NULL argument");
+  const DevModel& d = model->d;
+  info->num_verts = d.V; info->num_joints = d.J; info->num_betas = d.nB; info->num_pose_basis = d.P;
+  info->skin_k = d.K; info->jreg_nnz = d.jreg_nnz; info->tree_depth = d.num_levels - 1;
+  info->max_level_width = d.max_width; info->posedirs_zero = d.P == 0; info->joint_bone_pairs = d.npairs;
+  info->num_chunks = d.fwd_nchunk; info->num_ga_slots = d.num_units;
+  return SMIL_OK;
+}
+
+size_t smil_saved_bytes(const SmilModel* model, int32_t batch, uint32_t) {
+  if (!model || batch <= 0) return 0;
+  return saved_bytes_for(model->d, batch);
+}
+
+size_t smil_fwd_scratch_bytes(const SmilModel* model, const SmilFwdArgs* f) {
+  if (!model || !f || f->batch <= 0) return 0;
+  const DevModel& m = model->d;
+  Plan p;
+  if (make_plan(m, *f, &p) == SMIL_OK && p.fused) return 0;  // the fused path needs no forward scratch
+  const size_t vb = align_up((size_t)f->batch * m.V * 3 * 4, 256);
+  // generic path: v_posed (pose blendshapes) + v_shaped / verts stand-ins for get_skin=False
+  return 3 * vb + 256;
+}
+
+size_t smil_bwd_scratch_bytes(const SmilModel* model, const SmilBwdArgs* g) {
+  if (!model || !g || g->fwd.batch <= 0) return 0;
+  const DevModel& m = model->d;
+  const size_t B = g->fwd.batch;
+  const size_t vb = align_up(B * m.V * 3 * 4, 256);
+  const size_t fused = align_up(B * std::max(m.num_units, 1) * 48, 256) +
+                       align_up(B * std::max(m.bwd_ntile, 1) * (m.nB + 3) * 4, 256);
+  const size_t generic = 2 * vb + align_up(B * m.J * 48, 256) + align_up(B * m.J * 36, 256) +
+                         align_up(B * m.J * 12, 256) + align_up(B * 12, 256);
+  return std::max(fused, generic) + 256;
+}
+
+int smil_forward(const SmilModel* model, const SmilFwdArgs* f, void* stream) {
+  if (!model || !f) return fail(SMIL_EINVAL, "smil_forward: NULL argument");
+  const DevModel& m = model->d;
+  if (m.V <= 0) return fail(SMIL_EINVAL, "model has no vertices (tree-only model)");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  Plan p;
+  int rc = make_plan(m, *f, &p);
+  if (rc != SMIL_OK) return rc;
+  const int B = f->batch;
+  if (!f->saved || f->saved_bytes < saved_bytes_for(m, B)) return fail(SMIL_ENOMEM, "saved buffer too small");
+  if (!f->joints) return fail(SMIL_EINVAL, "joints output is NULL");
+  if (!p.joints_only && (!f->verts || !f->v_shaped)) return fail(SMIL_EINVAL, "verts / v_shaped outputs are NULL");
+  if (((uintptr_t)f->verts | (uintptr_t)f->v_shaped | (uintptr_t)f->saved) & 15)
+    return fail(SMIL_EINVAL, "verts, v_shaped and saved must be 16-byte aligned");
+  float* A = static_cast<float*>(f->saved);
+  float* jrest = reinterpret_cast<float*>(static_cast<char*>(f->saved) + align_up((size_t)B * m.J * 48, 256));
+
+  PoseArgs pa = base_pose_args(m, *f, p);
+  pa.Rs = p.rotmat ? nullptr : f->Rs;
+  pa.A = A;
+  pa.newJ = f->J_transformed;
+  pa.joints = f->joints;
+
+  if (p.fused) {
+    pa.joints_mode = p.is_static ? 2 : 1;
+    if ((rc = launch_pose(m, pa, false, st)) != SMIL_OK) return rc;
+    if (!p.joints_only) {
+      SkinFwdArgs sa;
+      sa.B = B; sa.nb = f->num_betas_used;
+      const long long ctas_wanted = 4LL * m.sm_count * 4;
+      long long G = ((long long)B * m.fwd_nchunk) / ctas_wanted;
+      sa.G = (int)std::min<long long>(SKIN_FWD_GMAX, std::max<long long>(1, G));
+      sa.beta = f->beta; sa.beta_stride = f->beta_stride;
+      sa.trans = f->trans; sa.trans_stride = f->trans_stride;
+      sa.A = A; sa.verts = f->verts; sa.v_shaped = f->v_shaped;
+      if ((rc = launch_skin_fwd(m, sa, st)) != SMIL_OK) return rc;
+    }
+    return SMIL_OK;
+  }
+
+  // ---- generic (unfused) path ----
+  const size_t vb = align_up((size_t)B * m.V * 3 * 4, 256);
+  if (!f->scratch || f->scratch_bytes < 3 * vb) return fail(SMIL_ENOMEM, "forward scratch too small");
+  char* sc = static_cast<char*>(f->scratch);
+  float* v_posed_buf = reinterpret_cast<float*>(sc);
+  float* v_shaped = p.joints_only ? reinterpret_cast<float*>(sc + vb) : f->v_shaped;
+  float* verts = p.joints_only ? reinterpret_cast<float*>(sc + 2 * vb) : f->verts;
+  const float* vt = f->v_template ? f->v_template : m.v_template;
+  const long long nv3 = (long long)B * m.V * 3, nbv = (long long)B * m.V;
+  shape_fwd_kernel<<<blocks_for(nv3, 256), 256, 0, st>>>(m, B, f->num_betas_used, f->beta, f->beta_stride, vt, f->del_v,
+                                                         f->del_v_stride, v_shaped);
+  SMIL_LAUNCH_CHECK("shape_fwd_kernel");
+  if (p.jrest_mode == 2) {
+    regress_fwd_kernel<<<blocks_for((long long)B * m.J * 32, 256), 256, 0, st>>>(m, B, v_shaped, jrest);
+    SMIL_LAUNCH_CHECK("regress_fwd_kernel");
+    pa.jrest_in = jrest;
+  }
+  pa.joints_mode = p.is_static ? 2 : 0;
+  if (m.P > 0 && !p.rotmat && !f->Rs) return fail(SMIL_EINVAL, "Rs output required for a rig with pose blendshapes");
+  if ((rc = launch_pose(m, pa, false, st)) != SMIL_OK) return rc;
+  const float* v_posed = v_shaped;
+  if (m.P > 0) {
+    const float* Rs = p.rotmat ? f->theta : f->Rs;
+    if (p.rotmat && f->theta_stride != (long long)m.J * 9)
+      return fail(SMIL_EUNSUPPORTED, "rotation-matrix theta must be contiguous for rigs with pose blendshapes");
+    dim3 grid(blocks_for(3LL * m.V, 256), B);
+    const size_t sh = (size_t)m.P * 4;
+    if ((rc = set_smem(posedirs_fwd_kernel, sh)) != SMIL_OK) return rc;
+    posedirs_fwd_kernel<<<grid, 256, sh, st>>>(m, B, Rs, v_shaped, v_posed_buf);
+    SMIL_LAUNCH_CHECK("posedirs_fwd_kernel");
+    v_posed = v_posed_buf;
+  }
+  lbs_fwd_kernel<<<blocks_for(nbv, 256), 256, 0, st>>>(m, B, A, v_posed, f->trans, f->trans_stride, verts);
+  SMIL_LAUNCH_CHECK("lbs_fwd_kernel");
+  if (!p.is_static) {
+    regress_fwd_kernel<<<blocks_for((long long)B * m.J * 32, 256), 256, 0, st>>>(m, B, verts, f->joints);
+    SMIL_LAUNCH_CHECK("regress_fwd_kernel");
+  }
+  return SMIL_OK;
+}
+
+int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
+  if (!model || !g) return fail(SMIL_EINVAL, "smil_backward: NULL argument");
+  const DevModel& m = model->d;
+  const SmilFwdArgs* f = &g->fwd;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  Plan p;
+  int rc = make_plan(m, *f, &p);
+  if (rc != SMIL_OK) return rc;
+  const int B = f->batch, nb = f->num_betas_used;
+  if (!f->saved || f->saved_bytes < saved_bytes_for(m, B)) return fail(SMIL_ENOMEM, "saved buffer too small");
+  if (!g->scratch || g->scratch_bytes < smil_bwd_scratch_bytes(model, g)) return fail(SMIL_ENOMEM, "backward scratch too small");
+  const float* A = static_cast<const float*>(f->saved);
+  const float* jrest = reinterpret_cast<const float*>(static_cast<const char*>(f->saved) + align_up((size_t)B * m.J * 48, 256));
+  char* sc = static_cast<char*>(g->scratch);
+  const bool fused = p.fused && !g->g_v_shaped && !g->g_del_v;
+
+  PoseArgs pa = base_pose_args(m, *f, p);
+  pa.jrest_in = jrest;
+  pa.g_joints = g->g_joints;
+  pa.g_Rs = g->g_Rs;
+  pa.g_theta = g->g_theta;
+  pa.g_ls = f->betas_logscale ? g->g_logscale : nullptr;
+  pa.g_bt = f->betas_trans ? g->g_btrans : nullptr;
+
+  if (fused) {
+    float* slots = reinterpret_cast<float*>(sc);
+    float* part = reinterpret_cast<float*>(sc + align_up((size_t)B * std::max(m.num_units, 1) * 48, 256));
+    if (g->g_verts) {
+      if (((uintptr_t)g->g_verts) & 15) return fail(SMIL_EINVAL, "g_verts must be 16-byte aligned");
+      SkinBwdArgs sa;
+      sa.B = B; sa.nb = nb;
+      const int ngroups = (B + SKIN_BWD_G - 1) / SKIN_BWD_G;
+      long long gpc = ((long long)ngroups * m.bwd_ntile) / (6LL * m.sm_count);
+      sa.groups_per_cta = (int)std::min<long long>(32, std::max<long long>(1, gpc));
+      sa.max_tile_items = m.h_max_units_per_tile;
+      sa.beta = f->beta; sa.beta_stride = f->beta_stride;
+      sa.A = A; sa.g_verts = g->g_verts;
+      sa.total_floats = (long long)B * m.V * 3;
+      sa.gA_slots = slots; sa.gbt_part = part;
+      if ((rc = launch_skin_bwd(m, sa, st)) != SMIL_OK) return rc;
+      pa.gA_slots = slots; pa.nslots = m.num_units;
+      pa.gbt_part = part; pa.ntile = m.bwd_ntile;
+    }
+    pa.joints_mode = p.is_static ? 2 : 1;
+    pa.g_beta = g->g_beta; pa.g_trans = g->g_trans;
+    pa.beta_final = 1;
+    return launch_pose(m, pa, true, st);
+  }
+
+  // ---- generic (unfused) path ----
+  if (!f->v_shaped) return fail(SMIL_EINVAL, "generic backward needs the forward's v_shaped output");
+  const size_t vb = align_up((size_t)B * m.V * 3 * 4, 256);
+  float* g_vp = reinterpret_cast<float*>(sc);
+  float* v_posed_buf = reinterpret_cast<float*>(sc + vb);
+  float* gA = reinterpret_cast<float*>(sc + 2 * vb);
+  float* gRs2 = reinterpret_cast<float*>(reinterpret_cast<char*>(gA) + align_up((size_t)B * m.J * 48, 256));
+  float* g_jrest = reinterpret_cast<float*>(reinterpret_cast<char*>(gRs2) + align_up((size_t)B * m.J * 36, 256));
+  float* g_trans = g->g_trans ? g->g_trans
+                              : reinterpret_cast<float*>(reinterpret_cast<char*>(g_jrest) + align_up((size_t)B * m.J * 12, 256));
+  const long long nbv = (long long)B * m.V;
+  const float* v_posed = f->v_shaped;
+  const float* Rs = p.rotmat ? f->theta : f->Rs;
+  if (m.P > 0) {
+    if (!Rs) return fail(SMIL_EINVAL, "generic backward needs the forward's Rs output for pose blendshapes");
+    dim3 grid(blocks_for(3LL * m.V, 256), B);
+    const size_t sh = (size_t)m.P * 4;
+    if ((rc = set_smem(posedirs_fwd_kernel, sh)) != SMIL_OK) return rc;
+    posedirs_fwd_kernel<<<grid, 256, sh, st>>>(m, B, Rs, f->v_shaped, v_posed_buf);
+    SMIL_LAUNCH_CHECK("posedirs_fwd_kernel");
+    v_posed = v_posed_buf;
+    SMIL_CUDA(cudaMemsetAsync(gRs2, 0, (size_t)B * m.J * 36, st));
+  }
+  SMIL_CUDA(cudaMemsetAsync(gA, 0, (size_t)B * m.J * 48, st));
+  SMIL_CUDA(cudaMemsetAsync(g_trans, 0, (size_t)B * 12, st));
+  const float* gj_regress = (!p.is_static) ? g->g_joints : nullptr;
+  lbs_bwd_kernel<<<blocks_for(nbv, 256), 256, 0, st>>>(m, B, A, v_posed, g->g_verts, gj_regress, g_vp, gA, g_trans);
+  SMIL_LAUNCH_CHECK("lbs_bwd_kernel");
+  if (m.P > 0) {
+    posedirs_bwd_kernel<<<blocks_for((long long)B * m.P * 32, 256), 256, 0, st>>>(m, B, g_vp, gRs2);
+    SMIL_LAUNCH_CHECK("posedirs_bwd_kernel");
+    pa.g_Rs2 = gRs2;
+  }
+  pa.gA_dense = gA;
+  pa.joints_mode = p.is_static ? 2 : 0;
+  pa.g_jrest = p.is_static ? nullptr : g_jrest;
+  pa.beta_final = 0;
+  if ((rc = launch_pose(m, pa, true, st)) != SMIL_OK) return rc;
+  vshaped_grad_kernel<<<blocks_for(nbv, 256), 256, 0, st>>>(m, B, g_vp, g->g_v_shaped, p.is_static ? nullptr : g_jrest,
+                                                            f->del_v ? g->g_del_v : nullptr);
+  SMIL_LAUNCH_CHECK("vshaped_grad_kernel");
+  if (g->g_beta && nb > 0) {
+    shape_bwd_kernel<<<blocks_for((long long)B * nb * 32, 256), 256, 0, st>>>(m, B, nb, g_vp, g->g_beta);
+    SMIL_LAUNCH_CHECK("shape_bwd_kernel");
+  }
+  return SMIL_OK;
+}
+
+// ---- stand-alone pieces ---------------------------------------------------------------------------
+int smil_rodrigues_forward(const float* theta, float* R, int64_t n, void* stream) {
+  if (n <= 0) return SMIL_OK;
+  if (!theta || !R) return fail(SMIL_EINVAL, "smil_rodrigues_forward: NULL argument");
+  rodrigues_fwd_kernel<<<blocks_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(theta, R, n);
+  SMIL_LAUNCH_CHECK("rodrigues_fwd_kernel");
+  return SMIL_OK;
+}
+int smil_rodrigues_backward(const float* theta, const float* g_R, float* g_theta, int64_t n, void* stream) {
+  if (n <= 0) return SMIL_OK;
+  if (!theta || !g_R || !g_theta) return fail(SMIL_EINVAL, "smil_rodrigues_backward: NULL argument");
+  rodrigues_bwd_kernel<<<blocks_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(theta, g_R, g_theta, n);
+  SMIL_LAUNCH_CHECK("rodrigues_bwd_kernel");
+  return SMIL_OK;
+}
+
+static PoseArgs chain_pose_args(const DevModel& m, const SmilChainArgs* c) {
+  PoseArgs a;
+  memset(&a, 0, sizeof(a));
+  a.B = c->batch; a.nb = 0;
+  a.flags = (c->flags & SMIL_F_PROPAGATE_SCALING) | SMIL_F_THETA_IS_ROTMAT;
+  a.jrest_mode = 2;
+  a.theta = c->Rs; a.theta_stride = (long long)m.J * 9;
+  a.ls = c->betas_logscale; a.ls_stride = (long long)m.J * 3;
+  a.bt = c->betas_trans; a.bt_stride = (long long)m.J * 3;
+  a.jrest_in = c->Js;
+  return a;
+}
+int smil_chain_forward(const SmilModel* model, const SmilChainArgs* c, void* stream) {
+  if (!model || !c || !c->Rs || !c->Js) return fail(SMIL_EINVAL, "smil_chain_forward: NULL argument");
+  if (c->batch <= 0) return fail(SMIL_EINVAL, "batch must be positive");
+  PoseArgs a = chain_pose_args(model->d, c);
+  a.A = c->A; a.newJ = c->new_J;
+  return launch_pose(model->d, a, false, static_cast<cudaStream_t>(stream));
+}
+int smil_chain_backward(const SmilModel* model, const SmilChainArgs* c, void* stream) {
+  if (!model || !c || !c->Rs || !c->Js) return fail(SMIL_EINVAL, "smil_chain_backward: NULL argument");
+  if (c->batch <= 0) return fail(SMIL_EINVAL, "batch must be positive");
+  PoseArgs a = chain_pose_args(model->d, c);
+  a.gA_dense = c->g_A; a.g_newJ = c->g_new_J;
+  a.g_theta = c->g_Rs; a.g_jrest = c->g_Js;
+  a.g_ls = c->betas_logscale ? c->g_logscale : nullptr;
+  a.g_bt = c->betas_trans ? c->g_btrans : nullptr;
+  return launch_pose(model->d, a, true, static_cast<cudaStream_t>(stream));
+}
+
+// ---- reprojection losses ----------------------------------------------------------------------------
+static int check_proj(const SmilProjArgs* a) {
+  if (!a) return fail(SMIL_EINVAL, "SmilProjArgs is NULL");
+  if (a->kind < SMIL_LOSS_FITTER || a->kind > SMIL_LOSS_SINGLEVIEW) return fail(SMIL_EINVAL, "unknown loss kind %d", a->kind);
+  if (a->batch <= 0 || a->num_views <= 0 || a->num_joints <= 0)
+    return fail(SMIL_EINVAL, "batch/num_views/num_joints must be positive");
+  if (!a->joints || !a->cam_R || !a->cam_T || !a->fov_deg || !a->target || !a->partials)
+    return fail(SMIL_EINVAL, "joints, cam_R, cam_T, fov_deg, target and partials are required");
+  if (a->kind != SMIL_LOSS_FITTER && !(a->norm_size > 0.f)) return fail(SMIL_EINVAL, "norm_size must be positive");
+  return SMIL_OK;
+}
+int smil_project_loss_forward(const SmilProjArgs* a, void* stream) {
+  int rc = check_proj(a);
+  if (rc != SMIL_OK) return rc;
+  if (!a->loss) return fail(SMIL_EINVAL, "loss output is NULL");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long warps = (long long)a->batch * a->num_views;
+  proj_fwd_kernel<<<blocks_for(warps * 32, 256), 256, 0, st>>>(*a);
+  SMIL_LAUNCH_CHECK("proj_fwd_kernel");
+  proj_finalize_kernel<<<1, 256, 0, st>>>(*a);
+  SMIL_LAUNCH_CHECK("proj_finalize_kernel");
+  return SMIL_OK;
+}
+int smil_project_loss_backward(const SmilProjArgs* a, void* stream) {
+  int rc = check_proj(a);
+  if (rc != SMIL_OK) return rc;
+  const int threads = std::min(128, std::max(32, ((std::max(a->num_joints, a->num_views) + 31) / 32) * 32));
+  proj_bwd_kernel<<<a->batch, threads, 0, static_cast<cudaStream_t>(stream)>>>(*a);
+  SMIL_LAUNCH_CHECK("proj_bwd_kernel");
+  return SMIL_OK;
+}
+int smil_keypoint3d_loss_forward(const SmilKp3dArgs* a, void* stream) {
+  if (!a || !a->joints || !a->target || !a->loss || !a->partials) return fail(SMIL_EINVAL, "smil_keypoint3d_loss_forward: NULL argument");
+  if (a->batch <= 0 || a->num_joints <= 0) return fail(SMIL_EINVAL, "batch/num_joints must be positive");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  kp3d_fwd_kernel<<<blocks_for((long long)a->batch * 32, 256), 256, 0, st>>>(*a);
+  SMIL_LAUNCH_CHECK("kp3d_fwd_kernel");
+  kp3d_finalize_kernel<<<1, 256, 0, st>>>(*a);
+  SMIL_LAUNCH_CHECK("kp3d_finalize_kernel");
+  return SMIL_OK;
+}
+int smil_keypoint3d_loss_backward(const SmilKp3dArgs* a, void* stream) {
+  if (!a || !a->joints || !a->target || !a->g_joints || !a->partials) return fail(SMIL_EINVAL, "smil_keypoint3d_loss_backward: NULL argument");
+  if (a->batch <= 0 || a->num_joints <= 0) return fail(SMIL_EINVAL, "batch/num_joints must be positive");
+  kp3d_bwd_kernel<<<blocks_for((long long)a->batch * a->num_joints, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(*a);
+  SMIL_LAUNCH_CHECK("kp3d_bwd_kernel");
+  return SMIL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,257 @@
+"""Load-time packer: reference-layout model arrays -> compact tables for the CUDA kernels.
+
+Input is exactly what ``SMAL.__init__`` holds (/root/reference/smal_model/smal_torch.py:120-196):
+``v_template (V,3)``, ``shapedirs (nB,3V)``, ``posedirs (P,3V)``, ``J_regressor (V,J)``,
+``weights (V,J)``, ``parents int32 (J,)``, optional static ``J (J,3)``.  Output is a dict of
+flat numpy arrays (fp32 / int32) that ``smil_model_create`` uploads verbatim.
+
+What the packing exploits ("hard parts"):
+  * skinning weights have <= K non-zeros per vertex (K = 2 for every SMIL rig shipped)
+    -> ELL ``(bone, weight)`` pairs instead of the dense (V,J) matrix the reference
+    multiplies with (smal_torch.py:320-323);
+  * ``J_regressor`` is sparse (STICK: 1 544 of 166 100) -> CSC/CSR;
+  * rest joints are linear in beta:  J = Jreg^T v_template + sum_m beta_m Jreg^T S_m;
+  * posed joints are linear in the bone transforms:
+        joints_j = sum_k A_k [c0_jk + sum_m beta_m cm_jkm ; .] + rowsum_j * trans
+    with c0_jk = sum_v Jreg[v,j] w[v,k] [T_v;1], cm_jkm = sum_v Jreg[v,j] w[v,k] S_m[v]
+    -> both regressions leave the per-vertex pass entirely (tables ``pj_*``);
+  * the kinematic tree is walked level by level -> ``order`` / ``level_ptr`` / children CSR;
+  * all-zero ``posedirs`` (every SMIL rig) is detected and the 9(J-1) x 3V GEMM skipped.
+
+All index arrays are int32 and bit-exact with the reference's
+``kintree_table[0].astype(np.int32)`` (smal_torch.py:193).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+FWD_CHUNK = 256  # vertices per CTA of the fused forward skinning pass (one per thread)
+BWD_CHUNK = 256  # vertices per CTA tile of the fused backward pass
+BWD_WARPS = 4    # warps per CTA of the fused backward pass
+MAX_FUSED_K = 4
+MAX_FUSED_NB = 16
+NBT_VALUES = (1, 2, 3, 4, 5, 6, 8, 10, 13, 16)  # beta-count template instances of the fused kernels
+
+
+def nbt_of(nb: int) -> int:
+    """Smallest compiled beta-count instance >= nb (0 if the fused kernels do not cover nb)."""
+    for v in NBT_VALUES:
+        if v >= nb:
+            return v
+    return 0
+
+
+def _f32(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float32))
+
+
+def _i32(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.int32))
+
+
+def tree_tables(parents: np.ndarray):
+    """Levels, topological order and children lists of the kinematic tree.
+
+    ``parents[i] < i`` is required for i >= 1 -- the reference indexes a growing Python list
+    with it (batch_lbs.py:157,179) and would raise IndexError otherwise; the root is joint 0
+    whatever ``parents[0]`` holds (batch_lbs.py:151-152)."""
+    J = int(parents.shape[0])
+    par = parents.astype(np.int64).copy()
+    par[0] = -1
+    for i in range(1, J):
+        if not (0 <= par[i] < i):
+            raise IndexError("parents[%d]=%d: the kinematic chain needs 0 <= parents[i] < i" % (i, par[i]))
+    depth = np.zeros(J, dtype=np.int64)
+    for i in range(1, J):
+        depth[i] = depth[par[i]] + 1
+    order = np.argsort(depth, kind="stable")
+    nlev = int(depth.max()) + 1
+    level_ptr = np.zeros(nlev + 1, dtype=np.int64)
+    for d in depth:
+        level_ptr[d + 1] += 1
+    level_ptr = np.cumsum(level_ptr)
+    child_ptr = np.zeros(J + 1, dtype=np.int64)
+    for i in range(1, J):
+        child_ptr[par[i] + 1] += 1
+    child_ptr = np.cumsum(child_ptr)
+    child_idx = np.zeros(max(J - 1, 1), dtype=np.int64)
+    fill = child_ptr[:-1].copy()
+    for i in range(1, J):
+        child_idx[fill[par[i]]] = i
+        fill[par[i]] += 1
+    widths = np.diff(level_ptr)
+    return dict(
+        parents=_i32(par), order=_i32(order), level_ptr=_i32(level_ptr), child_ptr=_i32(child_ptr),
+        child_idx=_i32(child_idx), depth=_i32(depth), num_levels=nlev, max_width=int(widths.max()),
+    )
+
+
+def pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static=None):
+    vt = np.asarray(v_template, dtype=np.float64)
+    V = vt.shape[0]
+    sd = np.asarray(shapedirs, dtype=np.float64)
+    nB = sd.shape[0]
+    assert sd.shape == (nB, 3 * V), sd.shape
+    W = np.asarray(weights, dtype=np.float64)
+    J = W.shape[1]
+    jr = np.asarray(J_regressor, dtype=np.float64)
+    assert jr.shape == (V, J) and W.shape == (V, J)
+    t = dict(V=V, J=J, nB=nB)
+
+    # ---- posedirs ------------------------------------------------------------------------
+    P = 0
+    pd = None
+    if posedirs is not None:
+        pd = np.asarray(posedirs)
+        if pd.ndim == 2 and pd.shape[1] == 3 * V and pd.shape[0] == 9 * (J - 1) and np.any(pd != 0):
+            P = pd.shape[0]
+        elif pd.size and np.any(pd != 0):
+            raise ValueError("posedirs shape %s is not (9(J-1), 3V)" % (pd.shape,))
+    t["P"] = P
+    t["posedirs"] = _f32(pd) if P else np.zeros(0, np.float32)
+
+    t["v_template"] = _f32(vt)
+    t["shapedirs"] = _f32(sd)
+    t["J_static"] = _f32(J_static) if J_static is not None else np.zeros(0, np.float32)
+    t.update(tree_tables(np.asarray(parents)))
+
+    # ---- skinning ELL ----------------------------------------------------------------------
+    nnz_row = (W != 0).sum(1)
+    K = max(int(nnz_row.max()), 1)
+    idx = np.zeros((V, K), dtype=np.int32)
+    val = np.zeros((V, K), dtype=np.float32)
+    for v in range(V):
+        cols = np.nonzero(W[v])[0]
+        idx[v, : len(cols)] = cols
+        val[v, : len(cols)] = W[v, cols]
+    t["K"] = K
+    t["skin_idx"] = _i32(idx)
+    t["skin_w"] = _f32(val)
+    t["skin_cnt"] = _i32(nnz_row)
+
+    # ---- joint regressor CSC (by joint) / CSR (by vertex) ------------------------------------
+    vv, jj = np.nonzero(jr)
+    o = np.lexsort((vv, jj))
+    t["jc_ptr"] = _i32(np.concatenate([[0], np.cumsum(np.bincount(jj, minlength=J))]))
+    t["jc_vid"] = _i32(vv[o]) if len(o) else np.zeros(1, np.int32)
+    t["jc_val"] = _f32(jr[vv[o], jj[o]]) if len(o) else np.zeros(1, np.float32)
+    o = np.lexsort((jj, vv))
+    t["jr_ptr"] = _i32(np.concatenate([[0], np.cumsum(np.bincount(vv, minlength=V))]))
+    t["jr_jid"] = _i32(jj[o]) if len(o) else np.zeros(1, np.int32)
+    t["jr_val"] = _f32(jr[vv[o], jj[o]]) if len(o) else np.zeros(1, np.float32)
+    t["jreg_nnz"] = int(len(vv))
+
+    # ---- closed-form regressions -------------------------------------------------------------
+    S3 = sd.reshape(nB, V, 3)
+    t["JT"] = _f32(jr.T @ vt)                                    # (J,3)
+    t["JS"] = _f32(np.einsum("vj,mvc->mjc", jr, S3))              # (nB,J,3)
+    t["jreg_rowsum"] = _f32(jr.sum(0))                            # (J,)
+    X = np.concatenate([vt, np.ones((V, 1)), S3.transpose(1, 0, 2).reshape(V, 3 * nB)], axis=1)  # (V, 4+3nB)
+    pj_ptr = [0]
+    pj_bone, pj_joint, pj_c0, pj_cm = [], [], [], []
+    for j in range(J):
+        rows = np.nonzero(jr[:, j])[0]
+        if len(rows):
+            coup = (jr[rows, j][:, None, None] * W[rows][:, :, None] * X[rows][:, None, :]).sum(0)  # (J, 4+3nB)
+            bones = np.nonzero((W[rows] != 0).any(0))[0]
+            for k in bones:
+                pj_bone.append(k)
+                pj_joint.append(j)
+                pj_c0.append(coup[k, :4])
+                pj_cm.append(coup[k, 4:].reshape(nB, 3))
+        pj_ptr.append(len(pj_bone))
+    npairs = len(pj_bone)
+    t["npairs"] = npairs
+    t["pj_ptr"] = _i32(pj_ptr)
+    t["pj_bone"] = _i32(pj_bone) if npairs else np.zeros(1, np.int32)
+    t["pj_joint"] = _i32(pj_joint) if npairs else np.zeros(1, np.int32)
+    t["pj_c0"] = _f32(pj_c0).reshape(-1, 4) if npairs else np.zeros((1, 4), np.float32)
+    t["pj_cm"] = _f32(pj_cm).reshape(-1, nB, 3) if npairs else np.zeros((1, max(nB, 1), 3), np.float32)
+    # the same pairs grouped by bone (backward accumulates g_A per bone without atomics)
+    pb = np.argsort(np.asarray(pj_bone, dtype=np.int64), kind="stable") if npairs else np.zeros(0, np.int64)
+    t["pb_ptr"] = _i32(np.concatenate([[0], np.cumsum(np.bincount(np.asarray(pj_bone, dtype=np.int64), minlength=J))])
+                       if npairs else np.zeros(J + 1))
+    t["pb_pair"] = _i32(pb) if npairs else np.zeros(1, np.int32)
+
+    # ---- fused forward skinning pass: per-vertex constants, SoA over a padded vertex axis -----
+    nchunk = (V + FWD_CHUNK - 1) // FWD_CHUNK
+    Vpad = nchunk * FWD_CHUNK
+    nconst = 3 + 3 * nB
+    vconst = np.zeros((nconst, Vpad), dtype=np.float32)
+    vconst[:3, :V] = vt.T
+    vconst[3:, :V] = S3.transpose(0, 2, 1).reshape(3 * nB, V)      # row 3+3m+c = S_m[:,c]
+    ell_i = np.zeros((K, Vpad), dtype=np.int32)
+    ell_w = np.zeros((K, Vpad), dtype=np.float32)
+    ell_i[:, :V] = idx.T
+    ell_w[:, :V] = val.T
+    t.update(fwd_chunk=FWD_CHUNK, fwd_nchunk=nchunk, Vpad=Vpad, vconst=_f32(vconst), ell_idx=_i32(ell_i),
+             ell_w=_f32(ell_w))
+
+    # ---- fused backward pass: item-major tables ------------------------------------------------
+    t.update(pack_backward_items(vt, S3, idx, val, nnz_row, J, nB))
+    t["fused_ok"] = bool(K <= MAX_FUSED_K and nbt_of(nB) > 0 and P == 0)
+    return t
+
+
+def pack_backward_items(vt, S3, idx, val, nnz_row, J, nB, chunk=BWD_CHUNK, nwarps=BWD_WARPS):
+    """Items ``(vertex, bone, weight)`` grouped per vertex tile and, inside a tile, per bone.
+
+    A tile is ``chunk`` consecutive vertices (the unit that is staged through shared memory by
+    one bulk copy per sample).  Inside a tile, every bone with at least one item forms a *unit*;
+    a unit is processed by one warp and produces one 3x4 partial of g_A written to its own
+    *slot* (no atomics, deterministic).  ``sb_*`` lists, per bone, the slots to add up."""
+    V = vt.shape[0]
+    ntile = (V + chunk - 1) // chunk
+    # floats per vertex record {T, S_0..}: sized (and zero padded) for the kernel instance that
+    # serves nB, so that instance never reads past a record
+    rec = 4 * ((3 + 3 * max(nbt_of(nB), nB) + 3) // 4)
+    vrec = np.zeros((ntile * chunk, rec), dtype=np.float32)
+    vrec[:V, :3] = vt
+    vrec[:V, 3:3 + 3 * nB] = S3.transpose(1, 0, 2).reshape(V, 3 * nB)   # [m][c]
+    unit_bone, unit_ptr, unit_tile = [], [0], []
+    it_v, it_w, it_first = [], [], []
+    tile_unit_ptr = [0]
+    warp_unit_ptr, warp_unit = [], []
+    for ti in range(ntile):
+        v0, v1 = ti * chunk, min(V, (ti + 1) * chunk)
+        per_bone = {}
+        for v in range(v0, v1):
+            for s in range(int(nnz_row[v])):
+                per_bone.setdefault(int(idx[v, s]), []).append((v - v0, float(val[v, s]), 1.0 if s == 0 else 0.0))
+        first_unit = len(unit_bone)
+        for b in sorted(per_bone):
+            unit_bone.append(b)
+            unit_tile.append(ti)
+            for (lv, w, f) in per_bone[b]:
+                it_v.append(lv)
+                it_w.append(w)
+                it_first.append(f)
+            unit_ptr.append(len(it_v))
+        tile_unit_ptr.append(len(unit_bone))
+        # longest-processing-time assignment of the tile's units to warps
+        units = list(range(first_unit, len(unit_bone)))
+        units.sort(key=lambda u: -(unit_ptr[u + 1] - unit_ptr[u]))
+        load = [0] * nwarps
+        lists = [[] for _ in range(nwarps)]
+        for u in units:
+            w = int(np.argmin(load))
+            lists[w].append(u)
+            load[w] += unit_ptr[u + 1] - unit_ptr[u] + 8
+        for w in range(nwarps):
+            warp_unit_ptr.append(len(warp_unit))
+            warp_unit.extend(lists[w])
+    warp_unit_ptr.append(len(warp_unit))
+    nunits = len(unit_bone)
+    tup = np.asarray(tile_unit_ptr, dtype=np.int64)
+    uptr = np.asarray(unit_ptr, dtype=np.int64)
+    max_tile_items = int((uptr[tup[1:]] - uptr[tup[:-1]]).max()) if ntile else 0
+    ub = np.asarray(unit_bone, dtype=np.int64)
+    order = np.argsort(ub, kind="stable")
+    sb_ptr = np.concatenate([[0], np.cumsum(np.bincount(ub, minlength=J))])
+    return dict(
+        bwd_chunk=chunk, bwd_ntile=ntile, bwd_warps=nwarps, bwd_rec=rec, vrec=_f32(vrec),
+        unit_bone=_i32(unit_bone), unit_ptr=_i32(unit_ptr), unit_tile=_i32(unit_tile),
+        tile_unit_ptr=_i32(tile_unit_ptr), warp_unit_ptr=_i32(warp_unit_ptr), warp_unit=_i32(warp_unit),
+        it_v=_i32(it_v), it_w=_f32(it_w), it_first=_f32(it_first), nunits=nunits, nitems=len(it_v),
+        sb_ptr=_i32(sb_ptr), sb_slot=_i32(order), bwd_max_tile_items=max_tile_items,
+    )

@@ -1,0 +1,177 @@
+"""float64 numpy emulation of the *algorithms* the CUDA kernels implement, driven by the
+packed tables of ``smilify_b200.packer``.  Test infrastructure only: it lets the CPU test
+suite prove that the sparse / closed-form / item-major reformulation (and the hand-derived
+backward of the chain and of Rodrigues) equals the dense oracle and its autograd, before any
+GPU time is spent.  The CUDA kernels are transcriptions of these functions."""
+from __future__ import annotations
+
+import numpy as np
+
+FLIP = np.array([1.0, -1.0, 1.0])
+
+
+def rodrigues_fwd(theta):
+    """theta (...,3) -> R (...,3,3); /root/reference/smal_model/batch_lbs.py:31-50."""
+    a = np.sqrt(((theta + 1e-8) ** 2).sum(-1, keepdims=True))
+    r = theta / a
+    c, s = np.cos(a)[..., None], np.sin(a)[..., None]
+    K = np.zeros(theta.shape[:-1] + (3, 3))
+    K[..., 0, 1], K[..., 0, 2] = -r[..., 2], r[..., 1]
+    K[..., 1, 0], K[..., 1, 2] = r[..., 2], -r[..., 0]
+    K[..., 2, 0], K[..., 2, 1] = -r[..., 1], r[..., 0]
+    return c * np.eye(3) + (1 - c) * r[..., :, None] * r[..., None, :] + s * K
+
+
+def rodrigues_bwd(theta, G):
+    tp = theta + 1e-8
+    a = np.sqrt((tp ** 2).sum(-1, keepdims=True))
+    r = theta / a
+    c, s = np.cos(a), np.sin(a)
+    kG = np.stack([G[..., 2, 1] - G[..., 1, 2], G[..., 0, 2] - G[..., 2, 0], G[..., 1, 0] - G[..., 0, 1]], -1)
+    Gr = np.einsum("...ij,...j->...i", G + np.swapaxes(G, -1, -2), r)
+    rGr = np.einsum("...i,...ij,...j->...", r, G, r)[..., None]
+    tr = (G[..., 0, 0] + G[..., 1, 1] + G[..., 2, 2])[..., None]
+    gc = tr - rGr
+    gs = (r * kG).sum(-1, keepdims=True)
+    gr = (1 - c) * Gr + s * kG
+    ga = -s * gc + c * gs - (gr * theta).sum(-1, keepdims=True) / (a * a)
+    return gr / a + ga * tp / a
+
+
+def chain_fwd(t, R, Jrest, ls, bt, propagate):
+    """R (B,J,3,3), Jrest (B,J,3) -> dict with GR,Gt,M,tl,s,pinv (all (B,J,...))."""
+    B, J = R.shape[:2]
+    par = t["parents"]
+    s = np.exp(ls) if ls is not None else np.ones((B, J, 3))
+    GR = np.zeros((B, J, 3, 3))
+    Gt = np.zeros((B, J, 3))
+    M = np.zeros((B, J, 3, 3))
+    tl = np.zeros((B, J, 3))
+    pinv = np.ones((B, J, 3))
+    GR[:, 0], Gt[:, 0], M[:, 0] = R[:, 0], Jrest[:, 0], R[:, 0]
+    for i in t["order"][1:]:
+        p = par[i]
+        if not propagate:
+            pinv[:, i] = 1.0 / s[:, p]
+        M[:, i] = pinv[:, i][:, :, None] * R[:, i] * s[:, i][:, None, :]
+        tl[:, i] = Jrest[:, i] - Jrest[:, p] + (bt[:, i] * FLIP if bt is not None else 0.0)
+        GR[:, i] = GR[:, p] @ M[:, i]
+        Gt[:, i] = np.einsum("bij,bj->bi", GR[:, p], tl[:, i]) + Gt[:, p]
+    At = Gt - np.einsum("bjik,bjk->bji", GR, Jrest)
+    return dict(GR=GR, Gt=Gt, M=M, tl=tl, s=s, pinv=pinv, At=At)
+
+
+def chain_bwd(t, R, Jrest, ls, bt, propagate, f, gAR, gAt, g_newJ):
+    """VJP of chain_fwd.  gAR (B,J,3,3), gAt (B,J,3) grads of A=[GR | Gt-GR Jrest]; g_newJ of Gt."""
+    B, J = R.shape[:2]
+    par = t["parents"]
+    gGR = gAR - gAt[..., :, None] * Jrest[..., None, :]
+    gGt = gAt + (g_newJ if g_newJ is not None else 0.0)
+    gJ = -np.einsum("bjki,bjk->bji", f["GR"], gAt)
+    gR = np.zeros((B, J, 3, 3))
+    gls = np.zeros((B, J, 3))
+    gbt = np.zeros((B, J, 3))
+    for i in t["order"][:0:-1]:
+        p = par[i]
+        gM = np.einsum("bki,bkj->bij", f["GR"][:, p], gGR[:, i])
+        gtl = np.einsum("bki,bk->bi", f["GR"][:, p], gGt[:, i])
+        gGR[:, p] += gGR[:, i] @ np.swapaxes(f["M"][:, i], -1, -2) + gGt[:, i][:, :, None] * f["tl"][:, i][:, None, :]
+        gGt[:, p] += gGt[:, i]
+        pin, s = f["pinv"][:, i], f["s"][:, i]
+        gR[:, i] = pin[:, :, None] * gM * s[:, None, :]
+        gls[:, i] += (pin[:, :, None] * R[:, i] * gM).sum(1) * s
+        if not propagate:
+            gls[:, p] -= (gM * R[:, i] * s[:, None, :]).sum(2) * pin
+        gJ[:, i] += gtl
+        gJ[:, p] -= gtl
+        gbt[:, i] = gtl * FLIP
+    gR[:, 0] = gGR[:, 0]
+    gJ[:, 0] += gGt[:, 0]
+    return gR, gJ, (gls if ls is not None else None), (gbt if bt is not None else None)
+
+
+def fast_forward(t, beta, theta, trans, ls, bt, propagate, static, rotmat=False):
+    """The fused path: closed-form rest joints and posed joints, ELL skinning."""
+    B = theta.shape[0]
+    V, J, nB = t["V"], t["J"], t["nB"]
+    nb = beta.shape[1]
+    R = theta if rotmat else rodrigues_fwd(theta)
+    if static:
+        Jrest = np.broadcast_to(t["J_static"].astype(np.float64).reshape(1, J, 3), (B, J, 3)).copy()
+    else:
+        Jrest = t["JT"].astype(np.float64)[None] + np.einsum("bm,mjc->bjc", beta, t["JS"].astype(np.float64)[:nb])
+    f = chain_fwd(t, R, Jrest, ls, bt, propagate)
+    vs = t["v_template"].astype(np.float64)[None] + (beta @ t["shapedirs"].astype(np.float64)[:nb]).reshape(B, V, 3)
+    verts = np.zeros((B, V, 3))
+    for k in range(t["K"]):
+        b_id = t["skin_idx"][:, k]
+        w = t["skin_w"][:, k].astype(np.float64)
+        verts += w[None, :, None] * (np.einsum("bvij,bvj->bvi", f["GR"][:, b_id], vs) + f["At"][:, b_id])
+    tr = trans if trans is not None else np.zeros((B, 3))
+    verts = verts + tr[:, None]
+    if static:
+        joints = f["Gt"].copy()
+    else:
+        joints = t["jreg_rowsum"].astype(np.float64)[None, :, None] * tr[:, None, :]
+        for pi in range(t["npairs"]):
+            j, k = t["pj_joint"][pi], t["pj_bone"][pi]
+            c0 = t["pj_c0"][pi].astype(np.float64)
+            q = c0[None, :3] + beta @ t["pj_cm"][pi].astype(np.float64)[:nb]
+            joints[:, j] += np.einsum("bij,bj->bi", f["GR"][:, k], q) + f["At"][:, k] * c0[3]
+    return dict(verts=verts, joints=joints, Rs=R, v_shaped=vs, J_transformed=f["Gt"], chain=f, Jrest=Jrest)
+
+
+def fast_backward(t, beta, theta, trans, ls, bt, propagate, static, fw, g_verts, g_joints, g_Rs=None, rotmat=False):
+    """Item-major backward of the fused path (what skin_bwd + pose_bwd compute)."""
+    B = theta.shape[0]
+    V, J, nB = t["V"], t["J"], t["nB"]
+    nb = beta.shape[1]
+    f = fw["chain"]
+    C = t["bwd_chunk"]
+    rec = t["vrec"].astype(np.float64)
+    g_beta = np.zeros((B, nb))
+    g_trans = np.zeros((B, 3))
+    nun = t["nunits"]
+    slots = np.zeros((B, nun, 3, 4))
+    gv = g_verts if g_verts is not None else np.zeros((B, V, 3))
+    for u in range(nun):
+        k = t["unit_bone"][u]
+        base = t["unit_tile"][u] * C
+        AkR = f["GR"][:, k]
+        for it in range(t["unit_ptr"][u], t["unit_ptr"][u + 1]):
+            v = base + t["it_v"][it]
+            w = float(t["it_w"][it])
+            g = gv[:, v]
+            T_, S_ = rec[v, :3], rec[v, 3:3 + 3 * nB].reshape(nB, 3)[:nb]
+            vp = T_[None] + beta @ S_
+            uvec = np.einsum("bki,bk->bi", AkR, g)
+            g_beta += w * (uvec @ S_.T)
+            wg = w * g
+            slots[:, u, :, :3] += wg[:, :, None] * vp[:, None, :]
+            slots[:, u, :, 3] += wg
+            g_trans += float(t["it_first"][it]) * g
+    gA = np.zeros((B, J, 3, 4))
+    for k in range(J):
+        for si in range(t["sb_ptr"][k], t["sb_ptr"][k + 1]):
+            gA[:, k] += slots[:, t["sb_slot"][si]]
+    g_newJ = None
+    if static:
+        g_newJ = g_joints
+    elif g_joints is not None:
+        g_trans += np.einsum("j,bjc->bc", t["jreg_rowsum"].astype(np.float64), g_joints)
+        for pi in range(t["npairs"]):
+            j, k = t["pj_joint"][pi], t["pj_bone"][pi]
+            c0 = t["pj_c0"][pi].astype(np.float64)
+            cm = t["pj_cm"][pi].astype(np.float64)[:nb]
+            q = c0[None, :3] + beta @ cm
+            gj = g_joints[:, j]
+            gA[:, k, :, :3] += gj[:, :, None] * q[:, None, :]
+            gA[:, k, :, 3] += gj * c0[3]
+            g_beta += np.einsum("bki,bk->bi", f["GR"][:, k], gj) @ cm.T
+    gR, gJ, gls, gbt = chain_bwd(t, fw["Rs"], fw["Jrest"], ls, bt, propagate, f, gA[..., :3], gA[..., 3], g_newJ)
+    if g_Rs is not None:
+        gR = gR + g_Rs
+    if not static:
+        g_beta += np.einsum("bjc,mjc->bm", gJ, t["JS"].astype(np.float64)[:nb])
+    g_theta = gR if rotmat else rodrigues_bwd(theta, gR)
+    return dict(beta=g_beta, theta=g_theta, trans=g_trans, betas_logscale=gls, betas_trans=gbt)
