@@ -65,8 +65,11 @@ struct SkinFwdArgs {
 };
 
 __host__ __device__ inline int skin_fwd_stage_floats(int chunk) { return ((3 * chunk + 4) + 3) & ~3; }
+// beta block padded to a 16-byte multiple: the staging tiles behind it are bulk-store sources
+__host__ __device__ inline int skin_fwd_beta_floats(int G, int NBT) { return (G * NBT + 3) & ~3; }
 __host__ inline size_t skin_fwd_smem_bytes(int G, int J, int NBT, int chunk) {
-  return 16 + (size_t)G * J * 48 + (size_t)G * NBT * 4 + (size_t)G * 16 + 4ull * skin_fwd_stage_floats(chunk) * 4;
+  return 16 + (size_t)G * J * 48 + (size_t)skin_fwd_beta_floats(G, NBT) * 4 + (size_t)G * 16 +
+         4ull * skin_fwd_stage_floats(chunk) * 4;
 }
 
 // Writes one staged tile (n floats starting `phase` floats into `stage`) to global `dst` (+off floats):
@@ -92,7 +95,7 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw);
   float* sA = reinterpret_cast<float*>(smem_raw + 16);
   float* sBeta = sA + (size_t)a.G * J * 12;
-  float* sTrans = sBeta + (size_t)a.G * NBT;
+  float* sTrans = sBeta + skin_fwd_beta_floats(a.G, NBT);
   float* sStage = sTrans + (size_t)a.G * 4;
   const int SF = skin_fwd_stage_floats(C);
 

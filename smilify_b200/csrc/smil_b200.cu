@@ -323,7 +323,7 @@ size_t smil_bwd_scratch_bytes(const SmilModel* model, const SmilBwdArgs* g) {
   const size_t vb = align_up(B * m.V * 3 * 4, 256);
   const size_t fused = align_up(B * std::max(m.num_units, 1) * 48, 256) +
                        align_up(B * std::max(m.bwd_ntile, 1) * (m.nB + 3) * 4, 256);
-  const size_t generic = 2 * vb + align_up(B * m.J * 48, 256) + align_up(B * m.J * 36, 256) +
+  const size_t generic = 3 * vb + align_up(B * m.J * 48, 256) + align_up(B * m.J * 36, 256) +
                          align_up(B * m.J * 12, 256) + align_up(B * 12, 256);
   return std::max(fused, generic) + 256;
 }
@@ -459,24 +459,31 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
   }
 
   // ---- generic (unfused) path ----
-  if (!f->v_shaped) return fail(SMIL_EINVAL, "generic backward needs the forward's v_shaped output");
   const size_t vb = align_up((size_t)B * m.V * 3 * 4, 256);
   float* g_vp = reinterpret_cast<float*>(sc);
   float* v_posed_buf = reinterpret_cast<float*>(sc + vb);
-  float* gA = reinterpret_cast<float*>(sc + 2 * vb);
+  const float* v_shaped = f->v_shaped;
+  if (!v_shaped) {  // get_skin=False forward kept v_shaped in its own scratch: recompute it here
+    float* vs = reinterpret_cast<float*>(sc + 2 * vb);
+    shape_fwd_kernel<<<blocks_for((long long)B * m.V * 3, 256), 256, 0, st>>>(
+        m, B, nb, f->beta, f->beta_stride, f->v_template ? f->v_template : m.v_template, f->del_v, f->del_v_stride, vs);
+    SMIL_LAUNCH_CHECK("shape_fwd_kernel");
+    v_shaped = vs;
+  }
+  float* gA = reinterpret_cast<float*>(sc + 3 * vb);
   float* gRs2 = reinterpret_cast<float*>(reinterpret_cast<char*>(gA) + align_up((size_t)B * m.J * 48, 256));
   float* g_jrest = reinterpret_cast<float*>(reinterpret_cast<char*>(gRs2) + align_up((size_t)B * m.J * 36, 256));
   float* g_trans = g->g_trans ? g->g_trans
                               : reinterpret_cast<float*>(reinterpret_cast<char*>(g_jrest) + align_up((size_t)B * m.J * 12, 256));
   const long long nbv = (long long)B * m.V;
-  const float* v_posed = f->v_shaped;
+  const float* v_posed = v_shaped;
   const float* Rs = p.rotmat ? f->theta : f->Rs;
   if (m.P > 0) {
     if (!Rs) return fail(SMIL_EINVAL, "generic backward needs the forward's Rs output for pose blendshapes");
     dim3 grid(blocks_for(3LL * m.V, 256), B);
     const size_t sh = (size_t)m.P * 4;
     if ((rc = set_smem(posedirs_fwd_kernel, sh)) != SMIL_OK) return rc;
-    posedirs_fwd_kernel<<<grid, 256, sh, st>>>(m, B, Rs, f->v_shaped, v_posed_buf);
+    posedirs_fwd_kernel<<<grid, 256, sh, st>>>(m, B, Rs, v_shaped, v_posed_buf);
     SMIL_LAUNCH_CHECK("posedirs_fwd_kernel");
     v_posed = v_posed_buf;
     SMIL_CUDA(cudaMemsetAsync(gRs2, 0, (size_t)B * m.J * 36, st));

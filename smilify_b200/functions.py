@@ -152,6 +152,9 @@ class SmalFunction(torch.autograd.Function):
             del scratch
 
         ctx.dm, ctx.flags, ctx.nb = dm, flags, nb
+        # an output nobody differentiates arrives as None in backward (not a zero tensor), so the
+        # kernels skip it; a zero g_v_shaped would also push the call off the fused path
+        ctx.set_materialize_grads(False)
         ctx.has = (trans is not None, del_v is not None, betas_logscale is not None, betas_trans is not None,
                    v_template is not None)
         ctx.del_v_shape = tuple(del_v.shape) if del_v is not None else None
@@ -231,8 +234,6 @@ class SmalFunction(torch.autograd.Function):
             _lib.check(L.smil_backward(dm.handle, C.byref(g), _stream()), "smil_backward")
         if o_delv is not None and ctx.del_v_shape != (B, V, 3):
             o_delv = o_delv.sum(0).reshape(ctx.del_v_shape)
-        if o_beta is None and need[3]:
-            o_beta = torch.zeros_like(beta)
         return None, None, None, o_beta, o_theta, o_trans, o_delv, o_ls, o_bt
 
 
