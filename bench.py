@@ -1,0 +1,405 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd posed meshes/s of the SMAL/SMIL hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): SMILy_STICK (V=3020, J=55, nB=5), batch 4096 random
+poses/shapes PER GPU (frames are independent: ranks shard them with no data-path collective ->
+weak scaling), one step = SMAL forward (verts, joints, Rs, v_shaped) + the full backward to
+beta/theta/trans from upstream gradients on verts and joints.
+
+Arms
+  ours       the CUDA path through ``smilify_b200.smal_torch.SMAL`` (-> C ABI -> sm_100a kernels).
+             ``value``: inputs and upstream gradients resident in HBM, step replayed from a CUDA
+             graph captured through that public API (``--no-graph`` times the eager call instead).
+             ``e2e``: the same step with HOST (pinned) pose/shape parameters copied in and the
+             parameter gradients + posed joints copied back inside the timed region.
+  reference  the reference's algorithm on the box's host cores: SMILify is Python/torch, so this
+             is the torch-CPU restatement in oracle/ (pinned against the real reference, see
+             oracle/pin_against_reference.py), all host threads, on a bounded sample of the batch.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "fwd+bwd posed meshes/s (SMIL LBS, B=4096)"
+UNIT = "meshes/s"
+
+
+def algorithmic_bytes(V, J, nB):
+    """fp32, every tensor of the call contract moved exactly once."""
+    n_in = nB + 3 * J + 3
+    fwd = 4 * (n_in + 3 * V + 3 * J + 9 * J + 3 * V)
+    bwd = 4 * (3 * V + 3 * J + 2 * n_in)
+    per_kernel = {  # the contract tensors each kernel of the fused path moves
+        "pose_fwd_kernel": 4 * (n_in + 9 * J + 3 * J),          # params in; Rs, joints out
+        "skin_fwd_kernel": 4 * (3 * V + 3 * V),                 # verts, v_shaped out
+        "skin_bwd_kernel": 4 * (3 * V),                         # g_verts in
+        "pose_bwd_kernel": 4 * (3 * J + 2 * n_in),              # g_joints + params in; param grads out
+    }
+    assert sum(per_kernel.values()) == fwd + bwd
+    return fwd, bwd, per_kernel
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def synth_inputs(B, V, J, nB, seed):
+    """SURVEY.md section 8(d) config 2 distributions."""
+    rs = np.random.RandomState(seed)
+    return dict(
+        beta=(rs.standard_normal((B, nB)) * 0.5).astype(np.float32),
+        theta=(rs.standard_normal((B, J, 3)) * 0.3).astype(np.float32),
+        trans=rs.standard_normal((B, 3)).astype(np.float32),
+        g_verts=rs.standard_normal((B, V, 3)).astype(np.float32),
+        g_joints=rs.standard_normal((B, J, 3)).astype(np.float32),
+    )
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the GPU is under load."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.path = os.path.join(tempfile.gettempdir(), "smil_clocks_%d.csv" % os.getpid())
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        try:
+            os.remove(self.path)
+        except OSError:
+            pass
+        return out
+
+
+# ---- CPU arm: the reference's algorithm on the host cores (oracle/ restatement) -----------------------
+def cpu_step_fn(rig_path, B, seed=0):
+    """-> (callable running one fwd+bwd of the oracle on B samples, V, J, nB)."""
+    import torch
+
+    from oracle import smal_oracle as SO
+
+    dd = SO.load_model_dict(rig_path)
+    m = SO.build_model(dd, dtype=torch.float32)
+    V, J, nB = m.num_verts, m.num_joints, m.num_betas
+    x = synth_inputs(B, V, J, nB, seed)
+    beta, theta, trans = (torch.from_numpy(x[k]).requires_grad_(True) for k in ("beta", "theta", "trans"))
+    gv, gj = torch.from_numpy(x["g_verts"]), torch.from_numpy(x["g_joints"])
+
+    def step():
+        verts, joints, _Rs, _vs = SO.smal_forward(m, beta, theta, trans)
+        torch.autograd.backward([verts, joints], [gv, gj])
+        beta.grad = theta.grad = trans.grad = None
+
+    return step, V, J, nB
+
+
+def time_cpu(rig_path, B, budget_s, min_iters=2, warmup=1):
+    import torch
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    step, V, J, nB = cpu_step_fn(rig_path, B)
+    for _ in range(warmup):
+        step()
+    times = []
+    t_end = time.perf_counter() + budget_s
+    while len(times) < min_iters or time.perf_counter() < t_end:
+        t0 = time.perf_counter()
+        step()
+        times.append(time.perf_counter() - t0)
+        if len(times) >= 200:
+            break
+    return B / statistics.median(times), cores, len(times)
+
+
+def run_reference(args, rank, world):
+    """--impl reference: rank 0 alone times the CPU path; other ranks exit 0 without work."""
+    if rank != 0:
+        return
+    import torch
+
+    from tests import rigs
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    Bs = args.cpu_batch
+    step, V, J, nB = cpu_step_fn(rigs.REAL_RIGS[args.rig], Bs)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    value = Bs * args.steps / dt
+    sample = "%d of the %d meshes of a step per CPU step (SMAL fwd+bwd, torch-CPU, %d threads)" % (Bs, args.batch, cores)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "SMILy_STICK.pkl fwd+bwd batch %d synthetic poses (CPU arm: %d-mesh sample per step)"
+                               % (args.batch, Bs), "rig": args.rig, "V": V, "J": J, "nB": nB, "batch_per_gpu": args.batch},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference is Python/torch (nothing to compile into oracle/_ref); timed: oracle/smal_oracle.py, "
+                "pinned against the unmodified reference by oracle/pin_against_reference.py",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---- GPU arm ---------------------------------------------------------------------------------------
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    import smilify_b200
+    from smilify_b200 import _lib
+    from smilify_b200.graphed import GraphedStep
+    from smilify_b200.smal_torch import SMAL
+    from tests import rigs
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl ours needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    smilify_b200.configure(rigs.REAL_RIGS[args.rig])
+    model = SMAL(dev)
+    V, J, nB = model._tables["V"], model._tables["J"], model.num_betas
+    B, K, W = args.batch, args.steps, args.warmup
+    x = synth_inputs(B, V, J, nB, seed=rank)
+    fwd_b, bwd_b, per_kernel = algorithmic_bytes(V, J, nB)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return ms
+
+    # --- the step ------------------------------------------------------------------------------
+    if args.no_graph:
+        beta, theta, trans = (torch.from_numpy(x[k]).to(dev).requires_grad_(True) for k in ("beta", "theta", "trans"))
+        gv, gj = torch.from_numpy(x["g_verts"]).to(dev), torch.from_numpy(x["g_joints"]).to(dev)
+        state = {}
+
+        def step():
+            verts, joints, Rs, vs = model(beta, theta, trans=trans)
+            state["joints"] = joints
+            state["grads"] = torch.autograd.grad([verts, joints], [beta, theta, trans], [gv, gj])
+
+        def outputs():
+            return state["grads"] + (state["joints"],)
+        dst_in = (beta, theta, trans)
+    else:
+        gs = GraphedStep(model, B)
+        with torch.no_grad():
+            gs.beta.copy_(torch.from_numpy(x["beta"])); gs.theta.copy_(torch.from_numpy(x["theta"]))
+            gs.trans.copy_(torch.from_numpy(x["trans"]))
+            gs.g_verts.copy_(torch.from_numpy(x["g_verts"])); gs.g_joints.copy_(torch.from_numpy(x["g_joints"]))
+        step = gs.replay
+
+        def outputs():
+            return (gs.grad_beta, gs.grad_theta, gs.grad_trans, gs.joints)
+        dst_in = (gs.beta, gs.theta, gs.trans)
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    # pre-warm so that clock samples are taken under load even when K is small
+    t_end = time.perf_counter() + 0.6
+    while time.perf_counter() < t_end:
+        step()
+        torch.cuda.synchronize()
+    for _ in range(max(W, 3)):
+        step()
+    launches0 = _lib.launch_count()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    eager_launches = _lib.launch_count() - launches0
+
+    # --- e2e: host parameters in, parameter gradients + joints out, every step -----------------------
+    h_in = [torch.from_numpy(x[k]).pin_memory() for k in ("beta", "theta", "trans")]
+    step()
+    h_out = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in outputs()]
+    h2d = sum(t.numel() * 4 for t in h_in)
+    d2h = sum(t.numel() * 4 for t in h_out)
+
+    def e2e_step():
+        with torch.no_grad():
+            for d, h in zip(dst_in, h_in):
+                d.copy_(h, non_blocking=True)
+        step()
+        for h, d in zip(h_out, outputs()):
+            h.copy_(d.detach(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the caller reads the result
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(K):
+        e2e_step()
+    e1.record()
+    barrier()
+    e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3 if world == 1 else 0.0))
+    clocks = sampler.stop() if sampler else None
+
+    # --- per-kernel device time (eager, event pair around every launch) -> roofline of the dominant kernel
+    roofline = None
+    kernels = {}
+    if rank == 0:
+        beta, theta, trans = (torch.from_numpy(x[k]).to(dev).requires_grad_(True) for k in ("beta", "theta", "trans"))
+        gv, gj = torch.from_numpy(x["g_verts"]).to(dev), torch.from_numpy(x["g_joints"]).to(dev)
+        n_prof = min(max(K, 5), 50)
+        _lib.profile_enable(16 * n_prof)
+        for _ in range(n_prof):
+            verts, joints, Rs, vs = model(beta, theta, trans=trans)
+            torch.autograd.grad([verts, joints], [beta, theta, trans], [gv, gj])
+        torch.cuda.synchronize()
+        prof = _lib.profile_collect()
+        _lib.profile_enable(0)
+        peak, peak_src = measured_peaks()
+        for name, (n, ms) in prof.items():
+            us = ms / n * 1e3
+            ab = per_kernel.get(name)
+            kernels[name] = {"launches_per_step": n / n_prof, "avg_us": round(us, 2),
+                             "alg_bytes_per_launch": ab * B if ab else None,
+                             "GBps": round(ab * B / (us * 1e-6) / 1e9, 1) if ab else None}
+        if prof:
+            top = max(prof, key=lambda k: prof[k][1])
+            ab = per_kernel.get(top, 0) * B
+            ach = ab / (prof[top][1] / prof[top][0] * 1e-3) / 1e9
+            roofline = {"kernel": top, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
+                        "frac": round(ach / peak, 4), "traffic": args.traffic, "peak_source": peak_src,
+                        "alg_bytes_per_launch": ab, "avg_us": kernels[top]["avg_us"]}
+    if rank != 0:
+        return
+    peak, peak_src = measured_peaks()
+    ms_step = ms_total / K
+    value = world * B * K / (ms_total * 1e-3)
+    step_gbs = (fwd_b + bwd_b) * B / (ms_step * 1e-3) / 1e9
+    cpu_val, cores, n_it = time_cpu(rigs.REAL_RIGS[args.rig], args.cpu_batch, args.cpu_seconds) if world == 1 else (None, None, 0)
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "SMILy_STICK.pkl fwd+bwd batch %d synthetic poses per GPU (BASELINE configs[1])" % B,
+                   "rig": args.rig, "V": V, "J": J, "nB": nB, "batch_per_gpu": B, "global_batch": B * world,
+                   "parallelism": "frames sharded, dp%d, no collective" % world,
+                   "launch": "eager" if args.no_graph else "cuda-graph replay of SMAL.__call__ + autograd",
+                   "l2": "per-step working set %.0f MB > 126 MB L2 (no flush needed)" % ((fwd_b + bwd_b) * B / 1e6)},
+        "e2e": {"value": world * B * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / K},
+        "gpu_launches": int(eager_launches) if args.no_graph else 4 * K,
+        "clocks": clocks,
+        "roofline": roofline,
+        "roofline_step": {"bound": "hbm", "alg_bytes_per_mesh": fwd_b + bwd_b, "achieved": round(step_gbs, 1),
+                          "peak": peak, "unit": "GB/s", "frac": round(step_gbs / peak, 4), "peak_source": peak_src},
+        "kernels": kernels,
+    }
+    if cpu_val is not None:
+        line["cpu_baseline"] = {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": "%d-mesh batches of the same workload, %d timed fwd+bwd (median), torch-CPU "
+                                          "oracle, %d threads" % (args.cpu_batch, n_it, cores)}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rig", default="stick", choices=["stick", "mouse"])
+    ap.add_argument("--batch", type=int, default=4096, help="meshes per GPU per step")
+    ap.add_argument("--no-graph", action="store_true", help="time the eager Python call instead of the graph replay")
+    ap.add_argument("--cpu-batch", type=int, default=256, help="meshes per CPU step (bounded sample)")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--traffic", type=float, default=None, help="dram bytes/launch of the dominant kernel from ncu")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -128,6 +128,20 @@ typedef struct SmilModelInfo {
 int smil_abi_version(void);
 const char* smil_last_error(void);
 
+/* Number of kernels this library has launched since load (all threads). */
+long long smil_launch_count(void);
+
+/* Optional per-kernel device timing for bench.py's roofline line: while enabled every kernel
+ * launch is bracketed by a cudaEvent pair on the launching stream (up to `max_launches` launches
+ * between two collects; 0 disables and frees the events).  Not for use during stream capture. */
+typedef struct SmilProfileEntry {
+  char name[48];
+  int32_t launches;
+  float total_ms;
+} SmilProfileEntry;
+int smil_profile_enable(int max_launches);
+int smil_profile_collect(SmilProfileEntry* out, int max_entries, int* num_entries);
+
 int smil_model_create(const SmilModelDesc* desc, SmilModel** out);
 void smil_model_destroy(SmilModel* model);
 int smil_model_info(const SmilModel* model, SmilModelInfo* info);

@@ -46,6 +46,10 @@ class SmilModelInfo(C.Structure):
         "max_level_width", "posedirs_zero", "joint_bone_pairs", "num_chunks", "num_ga_slots")]
 
 
+class SmilProfileEntry(C.Structure):
+    _fields_ = [("name", C.c_char * 48), ("launches", C.c_int32), ("total_ms", C.c_float)]
+
+
 class SmilFwdArgs(C.Structure):
     _fields_ = [
         ("batch", C.c_int32), ("num_betas_used", C.c_int32), ("flags", C.c_uint32), ("_pad", C.c_int32),
@@ -119,7 +123,8 @@ LOSS_FITTER, LOSS_MULTIVIEW, LOSS_SINGLEVIEW = 0, 1, 2
 
 # every symbol include/smil_b200.h declares
 EXPORTS = (
-    "smil_abi_version", "smil_last_error", "smil_model_create", "smil_model_destroy", "smil_model_info",
+    "smil_abi_version", "smil_last_error", "smil_launch_count", "smil_profile_enable", "smil_profile_collect",
+    "smil_model_create", "smil_model_destroy", "smil_model_info",
     "smil_saved_bytes", "smil_fwd_scratch_bytes", "smil_bwd_scratch_bytes", "smil_forward", "smil_backward",
     "smil_rodrigues_forward", "smil_rodrigues_backward", "smil_chain_forward", "smil_chain_backward",
     "smil_project_loss_forward", "smil_project_loss_backward", "smil_keypoint3d_loss_forward",
@@ -141,6 +146,9 @@ def lib():
     L = C.CDLL(LIB_PATH)
     L.smil_abi_version.restype = C.c_int
     L.smil_last_error.restype = C.c_char_p
+    L.smil_launch_count.restype = C.c_longlong
+    L.smil_profile_enable.argtypes = [C.c_int]
+    L.smil_profile_collect.argtypes = [C.POINTER(SmilProfileEntry), C.c_int, C.POINTER(C.c_int)]
     L.smil_model_create.argtypes = [C.POINTER(SmilModelDesc), C.POINTER(C.c_void_p)]
     L.smil_model_destroy.argtypes = [C.c_void_p]
     L.smil_model_destroy.restype = None
@@ -162,9 +170,7 @@ def lib():
     L.smil_keypoint3d_loss_forward.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
     L.smil_keypoint3d_loss_backward.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
     for name in EXPORTS:
-        fn = getattr(L, name)
-        if fn.restype is C.c_int and name not in ("smil_abi_version",):
-            pass
+        getattr(L, name)  # AttributeError here = the .so is older than include/smil_b200.h
     if L.smil_abi_version() != ABI_VERSION:
         raise RuntimeError("smilify_b200: ABI mismatch (library %d, binding %d)" % (L.smil_abi_version(), ABI_VERSION))
     _lib = L
@@ -175,6 +181,22 @@ def check(rc: int, what: str):
     if rc != 0:
         msg = lib().smil_last_error()
         raise RuntimeError("%s failed (%d): %s" % (what, rc, msg.decode("utf-8", "replace") if msg else "?"))
+
+
+def launch_count() -> int:
+    return int(lib().smil_launch_count())
+
+
+def profile_enable(max_launches: int):
+    check(lib().smil_profile_enable(int(max_launches)), "smil_profile_enable")
+
+
+def profile_collect() -> dict:
+    """-> {kernel name: (launches, total device ms)} since the previous collect."""
+    buf = (SmilProfileEntry * 64)()
+    n = C.c_int(0)
+    check(lib().smil_profile_collect(buf, 64, C.byref(n)), "smil_profile_collect")
+    return {buf[i].name.decode(): (int(buf[i].launches), float(buf[i].total_ms)) for i in range(n.value)}
 
 
 def _np_ptr(a: np.ndarray, ctype):

@@ -1,5 +1,7 @@
 // C-ABI entry points of the B200-native SMAL/SMIL hot path (see include/smil_b200.h).
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -shared -Xcompiler -fPIC
+#include <atomic>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -14,6 +16,39 @@ using namespace smil;
 struct SmilModel {
   DevModel d;
 };
+
+// ---- launch counter and optional per-kernel timing ----------------------------------------------
+namespace smil {
+namespace {
+struct ProfSlot { const char* name; cudaEvent_t beg, end; };
+std::atomic<long long> g_launches{0};
+std::atomic<int> g_prof_on{0};
+std::mutex g_prof_mu;
+std::vector<ProfSlot> g_prof_slots;   // event pairs, created by smil_profile_enable
+size_t g_prof_used = 0;
+thread_local int t_prof_cur = -1;
+thread_local cudaStream_t t_prof_stream = nullptr;
+}  // namespace
+
+void prof_begin(const char* name, cudaStream_t st) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  t_prof_cur = -1;
+  if (!g_prof_on.load(std::memory_order_relaxed)) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (g_prof_used >= g_prof_slots.size()) return;
+  ProfSlot& s = g_prof_slots[g_prof_used];
+  s.name = name;
+  if (cudaEventRecord(s.beg, st) != cudaSuccess) { cudaGetLastError(); return; }
+  t_prof_cur = (int)g_prof_used++;
+  t_prof_stream = st;
+}
+void prof_end() {
+  if (t_prof_cur < 0) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if ((size_t)t_prof_cur < g_prof_slots.size()) cudaEventRecord(g_prof_slots[t_prof_cur].end, t_prof_stream);
+  t_prof_cur = -1;
+}
+}  // namespace smil
 
 namespace {
 
@@ -60,6 +95,7 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
   const size_t smem = per * spb;
   const int grid = (a.B + spb - 1) / spb;
   int rc = SMIL_OK;
+  prof_begin(backward ? "pose_bwd_kernel" : "pose_fwd_kernel", st);
 #define SMIL_POSE_CASE(LPS)                                                           \
   if (lps == LPS) {                                                                   \
     if (backward) {                                                                   \
@@ -85,6 +121,7 @@ int launch_skin_fwd_inst(const DevModel& m, const SkinFwdArgs& a, cudaStream_t s
   int rc = set_smem(skin_fwd_kernel<NBT, K>, smem);
   if (rc != SMIL_OK) return rc;
   dim3 grid(m.fwd_nchunk, (a.B + a.G - 1) / a.G);
+  prof_begin("skin_fwd_kernel", st);
   skin_fwd_kernel<NBT, K><<<grid, SKIN_FWD_THREADS, smem, st>>>(m, a);
   SMIL_LAUNCH_CHECK("skin_fwd_kernel");
   return SMIL_OK;
@@ -118,6 +155,7 @@ int launch_skin_bwd_inst(const DevModel& m, const SkinBwdArgs& a, cudaStream_t s
   if (rc != SMIL_OK) return rc;
   const int ngroups = (a.B + SKIN_BWD_G - 1) / SKIN_BWD_G;
   dim3 grid(m.bwd_ntile, (ngroups + a.groups_per_cta - 1) / a.groups_per_cta);
+  prof_begin("skin_bwd_kernel", st);
   skin_bwd_kernel<NBT><<<grid, 128, smem, st>>>(m, a);
   SMIL_LAUNCH_CHECK("skin_bwd_kernel");
   return SMIL_OK;
@@ -192,6 +230,53 @@ extern "C" {
 
 int smil_abi_version(void) { return SMIL_ABI_VERSION; }
 const char* smil_last_error(void) { return err_buf(); }
+
+long long smil_launch_count(void) { return g_launches.load(); }
+
+int smil_profile_enable(int max_launches) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_on.store(0);
+  for (auto& s : g_prof_slots) { cudaEventDestroy(s.beg); cudaEventDestroy(s.end); }
+  g_prof_slots.clear();
+  g_prof_used = 0;
+  if (max_launches <= 0) return SMIL_OK;
+  g_prof_slots.resize((size_t)max_launches);
+  for (auto& s : g_prof_slots) {
+    s.name = nullptr;
+    if (cudaEventCreate(&s.beg) != cudaSuccess || cudaEventCreate(&s.end) != cudaSuccess) {
+      g_prof_slots.clear();
+      return fail(SMIL_ECUDA, "smil_profile_enable: cudaEventCreate failed: %s", cudaGetErrorString(cudaGetLastError()));
+    }
+  }
+  g_prof_on.store(1);
+  return SMIL_OK;
+}
+
+int smil_profile_collect(SmilProfileEntry* out, int max_entries, int* num_entries) {
+  if (!out || !num_entries || max_entries <= 0) return fail(SMIL_EINVAL, "smil_profile_collect: bad argument");
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  int n = 0;
+  for (size_t i = 0; i < g_prof_used; ++i) {
+    ProfSlot& s = g_prof_slots[i];
+    SMIL_CUDA(cudaEventSynchronize(s.end));
+    float ms = 0.f;
+    SMIL_CUDA(cudaEventElapsedTime(&ms, s.beg, s.end));
+    int k = 0;
+    for (; k < n; ++k)
+      if (strncmp(out[k].name, s.name, sizeof(out[k].name) - 1) == 0) break;
+    if (k == n) {
+      if (n == max_entries) continue;
+      memset(&out[n], 0, sizeof(out[n]));
+      strncpy(out[n].name, s.name, sizeof(out[n].name) - 1);
+      ++n;
+    }
+    out[k].launches += 1;
+    out[k].total_ms += ms;
+  }
+  g_prof_used = 0;
+  *num_entries = n;
+  return SMIL_OK;
+}
 
 int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   if (!s || !out) return fail(SMIL_EINVAL, "smil_model_create: NULL argument");
@@ -377,10 +462,12 @@ int smil_forward(const SmilModel* model, const SmilFwdArgs* f, void* stream) {
   float* verts = p.joints_only ? reinterpret_cast<float*>(sc + 2 * vb) : f->verts;
   const float* vt = f->v_template ? f->v_template : m.v_template;
   const long long nv3 = (long long)B * m.V * 3, nbv = (long long)B * m.V;
+  prof_begin("shape_fwd_kernel", st);
   shape_fwd_kernel<<<blocks_for(nv3, 256), 256, 0, st>>>(m, B, f->num_betas_used, f->beta, f->beta_stride, vt, f->del_v,
                                                          f->del_v_stride, v_shaped);
   SMIL_LAUNCH_CHECK("shape_fwd_kernel");
   if (p.jrest_mode == 2) {
+    prof_begin("regress_fwd_kernel", st);
     regress_fwd_kernel<<<blocks_for((long long)B * m.J * 32, 256), 256, 0, st>>>(m, B, v_shaped, jrest);
     SMIL_LAUNCH_CHECK("regress_fwd_kernel");
     pa.jrest_in = jrest;
@@ -396,13 +483,16 @@ int smil_forward(const SmilModel* model, const SmilFwdArgs* f, void* stream) {
     dim3 grid(blocks_for(3LL * m.V, 256), B);
     const size_t sh = (size_t)m.P * 4;
     if ((rc = set_smem(posedirs_fwd_kernel, sh)) != SMIL_OK) return rc;
+    prof_begin("posedirs_fwd_kernel", st);
     posedirs_fwd_kernel<<<grid, 256, sh, st>>>(m, B, Rs, v_shaped, v_posed_buf);
     SMIL_LAUNCH_CHECK("posedirs_fwd_kernel");
     v_posed = v_posed_buf;
   }
+  prof_begin("lbs_fwd_kernel", st);
   lbs_fwd_kernel<<<blocks_for(nbv, 256), 256, 0, st>>>(m, B, A, v_posed, f->trans, f->trans_stride, verts);
   SMIL_LAUNCH_CHECK("lbs_fwd_kernel");
   if (!p.is_static) {
+    prof_begin("regress_fwd_kernel", st);
     regress_fwd_kernel<<<blocks_for((long long)B * m.J * 32, 256), 256, 0, st>>>(m, B, verts, f->joints);
     SMIL_LAUNCH_CHECK("regress_fwd_kernel");
   }
@@ -465,6 +555,7 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
   const float* v_shaped = f->v_shaped;
   if (!v_shaped) {  // get_skin=False forward kept v_shaped in its own scratch: recompute it here
     float* vs = reinterpret_cast<float*>(sc + 2 * vb);
+    prof_begin("shape_fwd_kernel", st);
     shape_fwd_kernel<<<blocks_for((long long)B * m.V * 3, 256), 256, 0, st>>>(
         m, B, nb, f->beta, f->beta_stride, f->v_template ? f->v_template : m.v_template, f->del_v, f->del_v_stride, vs);
     SMIL_LAUNCH_CHECK("shape_fwd_kernel");
@@ -483,6 +574,7 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
     dim3 grid(blocks_for(3LL * m.V, 256), B);
     const size_t sh = (size_t)m.P * 4;
     if ((rc = set_smem(posedirs_fwd_kernel, sh)) != SMIL_OK) return rc;
+    prof_begin("posedirs_fwd_kernel", st);
     posedirs_fwd_kernel<<<grid, 256, sh, st>>>(m, B, Rs, v_shaped, v_posed_buf);
     SMIL_LAUNCH_CHECK("posedirs_fwd_kernel");
     v_posed = v_posed_buf;
@@ -491,9 +583,11 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
   SMIL_CUDA(cudaMemsetAsync(gA, 0, (size_t)B * m.J * 48, st));
   SMIL_CUDA(cudaMemsetAsync(g_trans, 0, (size_t)B * 12, st));
   const float* gj_regress = (!p.is_static) ? g->g_joints : nullptr;
+  prof_begin("lbs_bwd_kernel", st);
   lbs_bwd_kernel<<<blocks_for(nbv, 256), 256, 0, st>>>(m, B, A, v_posed, g->g_verts, gj_regress, g_vp, gA, g_trans);
   SMIL_LAUNCH_CHECK("lbs_bwd_kernel");
   if (m.P > 0) {
+    prof_begin("posedirs_bwd_kernel", st);
     posedirs_bwd_kernel<<<blocks_for((long long)B * m.P * 32, 256), 256, 0, st>>>(m, B, g_vp, gRs2);
     SMIL_LAUNCH_CHECK("posedirs_bwd_kernel");
     pa.g_Rs2 = gRs2;
@@ -503,10 +597,12 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
   pa.g_jrest = p.is_static ? nullptr : g_jrest;
   pa.beta_final = 0;
   if ((rc = launch_pose(m, pa, true, st)) != SMIL_OK) return rc;
+  prof_begin("vshaped_grad_kernel", st);
   vshaped_grad_kernel<<<blocks_for(nbv, 256), 256, 0, st>>>(m, B, g_vp, g->g_v_shaped, p.is_static ? nullptr : g_jrest,
                                                             f->del_v ? g->g_del_v : nullptr);
   SMIL_LAUNCH_CHECK("vshaped_grad_kernel");
   if (g->g_beta && nb > 0) {
+    prof_begin("shape_bwd_kernel", st);
     shape_bwd_kernel<<<blocks_for((long long)B * nb * 32, 256), 256, 0, st>>>(m, B, nb, g_vp, g->g_beta);
     SMIL_LAUNCH_CHECK("shape_bwd_kernel");
   }
@@ -517,6 +613,7 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
 int smil_rodrigues_forward(const float* theta, float* R, int64_t n, void* stream) {
   if (n <= 0) return SMIL_OK;
   if (!theta || !R) return fail(SMIL_EINVAL, "smil_rodrigues_forward: NULL argument");
+  prof_begin("rodrigues_fwd_kernel", static_cast<cudaStream_t>(stream));
   rodrigues_fwd_kernel<<<blocks_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(theta, R, n);
   SMIL_LAUNCH_CHECK("rodrigues_fwd_kernel");
   return SMIL_OK;
@@ -524,6 +621,7 @@ int smil_rodrigues_forward(const float* theta, float* R, int64_t n, void* stream
 int smil_rodrigues_backward(const float* theta, const float* g_R, float* g_theta, int64_t n, void* stream) {
   if (n <= 0) return SMIL_OK;
   if (!theta || !g_R || !g_theta) return fail(SMIL_EINVAL, "smil_rodrigues_backward: NULL argument");
+  prof_begin("rodrigues_bwd_kernel", static_cast<cudaStream_t>(stream));
   rodrigues_bwd_kernel<<<blocks_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(theta, g_R, g_theta, n);
   SMIL_LAUNCH_CHECK("rodrigues_bwd_kernel");
   return SMIL_OK;
@@ -576,8 +674,10 @@ int smil_project_loss_forward(const SmilProjArgs* a, void* stream) {
   if (!a->loss) return fail(SMIL_EINVAL, "loss output is NULL");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long warps = (long long)a->batch * a->num_views;
+  prof_begin("proj_fwd_kernel", st);
   proj_fwd_kernel<<<blocks_for(warps * 32, 256), 256, 0, st>>>(*a);
   SMIL_LAUNCH_CHECK("proj_fwd_kernel");
+  prof_begin("proj_finalize_kernel", st);
   proj_finalize_kernel<<<1, 256, 0, st>>>(*a);
   SMIL_LAUNCH_CHECK("proj_finalize_kernel");
   return SMIL_OK;
@@ -586,6 +686,7 @@ int smil_project_loss_backward(const SmilProjArgs* a, void* stream) {
   int rc = check_proj(a);
   if (rc != SMIL_OK) return rc;
   const int threads = std::min(128, std::max(32, ((std::max(a->num_joints, a->num_views) + 31) / 32) * 32));
+  prof_begin("proj_bwd_kernel", static_cast<cudaStream_t>(stream));
   proj_bwd_kernel<<<a->batch, threads, 0, static_cast<cudaStream_t>(stream)>>>(*a);
   SMIL_LAUNCH_CHECK("proj_bwd_kernel");
   return SMIL_OK;
@@ -594,8 +695,10 @@ int smil_keypoint3d_loss_forward(const SmilKp3dArgs* a, void* stream) {
   if (!a || !a->joints || !a->target || !a->loss || !a->partials) return fail(SMIL_EINVAL, "smil_keypoint3d_loss_forward: NULL argument");
   if (a->batch <= 0 || a->num_joints <= 0) return fail(SMIL_EINVAL, "batch/num_joints must be positive");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  prof_begin("kp3d_fwd_kernel", st);
   kp3d_fwd_kernel<<<blocks_for((long long)a->batch * 32, 256), 256, 0, st>>>(*a);
   SMIL_LAUNCH_CHECK("kp3d_fwd_kernel");
+  prof_begin("kp3d_finalize_kernel", st);
   kp3d_finalize_kernel<<<1, 256, 0, st>>>(*a);
   SMIL_LAUNCH_CHECK("kp3d_finalize_kernel");
   return SMIL_OK;
@@ -603,6 +706,7 @@ int smil_keypoint3d_loss_forward(const SmilKp3dArgs* a, void* stream) {
 int smil_keypoint3d_loss_backward(const SmilKp3dArgs* a, void* stream) {
   if (!a || !a->joints || !a->target || !a->g_joints || !a->partials) return fail(SMIL_EINVAL, "smil_keypoint3d_loss_backward: NULL argument");
   if (a->batch <= 0 || a->num_joints <= 0) return fail(SMIL_EINVAL, "batch/num_joints must be positive");
+  prof_begin("kp3d_bwd_kernel", static_cast<cudaStream_t>(stream));
   kp3d_bwd_kernel<<<blocks_for((long long)a->batch * a->num_joints, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(*a);
   SMIL_LAUNCH_CHECK("kp3d_bwd_kernel");
   return SMIL_OK;

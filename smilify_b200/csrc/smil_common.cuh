@@ -32,10 +32,17 @@ inline int fail(int code, const char* fmt, ...) {
   } while (0)
 #define SMIL_LAUNCH_CHECK(name)                                                                \
   do {                                                                                         \
+    smil::prof_end();                                                                          \
     cudaError_t e__ = cudaGetLastError();                                                      \
     if (e__ != cudaSuccess)                                                                    \
       return smil::fail(SMIL_ECUDA, "launch of %s failed: %s", name, cudaGetErrorString(e__)); \
   } while (0)
+
+// ---- launch counter + optional per-kernel device timing (smil_profile_* in the C ABI) ------------
+// prof_begin() goes right before a kernel launch, SMIL_LAUNCH_CHECK() right after it.  The counter
+// is always on; the cudaEvent pair around the launch only while profiling is enabled.
+void prof_begin(const char* name, cudaStream_t st);
+void prof_end();
 
 // ---- device-resident model ------------------------------------------------------------------
 struct DevModel {
