@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define SMIL_ABI_VERSION 1
+#define SMIL_ABI_VERSION 2
 
 enum {
   SMIL_OK = 0,
@@ -109,8 +109,8 @@ typedef struct SmilModelDesc {
   const int32_t* it_v;       /* [num_items] vertex index local to the tile */
   const float* it_w;         /* [num_items] */
   const float* it_first;     /* [num_items] 1 for a vertex's first item */
-  const int32_t* sb_ptr;     /* [J+1] slots per bone */
-  const int32_t* sb_slot;    /* [num_units] */
+  const int32_t* sb_ptr;     /* [J+1] bone k owns the g_A partial slots sb_ptr[k] .. sb_ptr[k+1] */
+  const int32_t* unit_slot;  /* [num_units] slot a unit's partial is written to (bone-major numbering) */
 } SmilModelDesc;
 
 typedef struct SmilModelInfo {

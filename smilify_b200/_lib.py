@@ -11,7 +11,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsmil_b200.so")
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 c_f = C.POINTER(C.c_float)
 c_i = C.POINTER(C.c_int32)
@@ -36,7 +36,7 @@ class SmilModelDesc(C.Structure):
         ("vconst", c_f), ("ell_idx", c_i), ("ell_w", c_f),
         ("vrec", c_f), ("unit_bone", c_i), ("unit_ptr", c_i), ("unit_tile", c_i), ("tile_unit_ptr", c_i),
         ("warp_unit_ptr", c_i), ("warp_unit", c_i), ("it_v", c_i), ("it_w", c_f), ("it_first", c_f),
-        ("sb_ptr", c_i), ("sb_slot", c_i),
+        ("sb_ptr", c_i), ("unit_slot", c_i),
     ]
 
 
@@ -209,7 +209,7 @@ _DESC_F32 = ("v_template", "shapedirs", "posedirs", "J_static", "skin_w", "jc_va
              "pj_c0", "pj_cm", "vconst", "ell_w", "vrec", "it_w", "it_first")
 _DESC_I32 = ("skin_idx", "jc_ptr", "jc_vid", "jr_ptr", "jr_jid", "parents", "order", "level_ptr", "child_ptr",
              "child_idx", "pj_ptr", "pj_bone", "pj_joint", "pb_ptr", "pb_pair", "ell_idx", "unit_bone", "unit_ptr",
-             "unit_tile", "tile_unit_ptr", "warp_unit_ptr", "warp_unit", "it_v", "sb_ptr", "sb_slot")
+             "unit_tile", "tile_unit_ptr", "warp_unit_ptr", "warp_unit", "it_v", "sb_ptr", "unit_slot")
 
 
 def desc_from_tables(t: dict, device: int):

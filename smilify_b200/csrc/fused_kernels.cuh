@@ -354,7 +354,7 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
         acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], 16);
       }
       if (st == 0 && valid) {
-        float4* d = reinterpret_cast<float4*>(a.gA_slots + ((long long)b * m.num_units + u) * 12);
+        float4* d = reinterpret_cast<float4*>(a.gA_slots + ((long long)b * m.num_units + m.unit_slot[u]) * 12);
         d[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
         d[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
         d[2] = make_float4(acc[8], acc[9], acc[10], acc[11]);

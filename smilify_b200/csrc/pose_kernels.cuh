@@ -1,5 +1,5 @@
-// Rodrigues + kinematic chain, forward and backward: one group of LPS lanes per batch element,
-// the parent tree walked level by level out of shared memory.
+// Rodrigues + kinematic chain, forward and backward: ONE WARP PER BATCH ELEMENT, the parent tree
+// walked level by level out of shared memory.
 //
 // Replaces  batch_rodrigues                         /root/reference/smal_model/batch_lbs.py:31-50
 //           batch_global_rigid_transformation       /root/reference/smal_model/batch_lbs.py:75-197
@@ -7,12 +7,22 @@
 //           posed-joint regression                  /root/reference/smal_model/smal_torch.py:343-351
 // The two regressions are evaluated in closed form from the packed tables (packer.py) when the
 // call has no del_v / v_template override / pose blendshapes, so they never touch vertices.
+//
+// Why a warp per sample: at B=4096 the path has only 4096 independent samples, so the per-sample
+// work has to be spread over lanes to fill 148 SMs.  Per-joint work (Rodrigues, local transforms,
+// outputs, the Rodrigues VJP) runs lane-per-joint; the level walk runs lane-per-joint-of-the-level
+// (<= max level width lanes busy) and is kept as short as possible: the local transform
+// M_i = S_p^-1 R_i S_i and its translation are precomputed, the backward child->parent accumulation is
+// a float4 gather over records that share one layout, and the backward reads the global transforms
+// the forward saved instead of re-walking the tree.  Shared memory per sample: 32 J floats forward,
+// 48 J floats backward (J = 55: 7.1 KB / 10.6 KB -> 31 / 21 samples resident per SM).
 #pragma once
 #include "smil_common.cuh"
 
 namespace smil {
 
-constexpr int POSE_THREADS = 128;
+constexpr int POSE_WPB = 2;                 // warps (= samples) per CTA
+constexpr int POSE_THREADS = 32 * POSE_WPB;
 
 struct PoseArgs {
   int B, nb;
@@ -31,11 +41,13 @@ struct PoseArgs {
   float* newJ;    // [B][J][3] or null
   float* joints;  // [B][J][3] or null
   // backward inputs
+  const float* A_saved;   // [B][J][12] written by the forward (its 3x3 part is the global rotation) or null
   const float* gA_dense;  // [B][J][12] or null
-  const float* gA_slots;  // [B][nslots][12] or null (summed per bone through sb_ptr/sb_slot)
+  const float* gA_slots;  // [B][nslots][12] or null; the slots of bone k are sb_ptr[k] .. sb_ptr[k+1]
   int nslots;
   const float* gbt_part;  // [B][ntile][nb+3] partial (g_beta, g_trans) from the fused skin pass, or null
   int ntile;
+  int joints_in_skin;     // 1: the fused skin pass already folded Jreg g_joints into g_verts
   const float* g_joints;  // [B][J][3] or null
   const float* g_newJ;    // [B][J][3] or null (extra gradient on J_transformed)
   const float* g_Rs;      // [B][J][9] or null
@@ -50,22 +62,19 @@ struct PoseArgs {
   int beta_final;   // 1: this kernel writes the complete g_beta / g_trans (fused mode)
 };
 
-// shared-memory record layout per sample (floats)
+// shared-memory layout per sample (float offsets); every block is 16-byte aligned
 struct PoseSmem {
-  int J, nbp, lps;
-  __host__ __device__ int rrec() const { return 0; }                 // [J][12] R rows, .w = Jrest
-  __host__ __device__ int grec() const { return 12 * J; }            // [J][12] G rows, .w = Gt
-  __host__ __device__ int srec() const { return 24 * J; }            // [J][4]  s0 s1 s2 -
-  __host__ __device__ int arec() const { return 28 * J; }            // [J][4]  At -
-  __host__ __device__ int beta() const { return 32 * J; }            // [nbp]
-  __host__ __device__ int fwd_floats() const { return 32 * J + nbp; }
-  __host__ __device__ int gg() const { return fwd_floats(); }        // [J][12] gGR rows, .w = gGt
-  __host__ __device__ int contrib() const { return gg() + 12 * J; }  // [J][20] child -> parent contributions
-  __host__ __device__ int gj() const { return contrib() + 20 * J; }  // [J][4] gJrest
-  __host__ __device__ int gls() const { return gj() + 4 * J; }       // [J][4] g_logscale accumulators
-  __host__ __device__ int accb() const { return gls() + 4 * J; }     // [lps][nbp] per-lane g_beta partials
-  __host__ __device__ int red() const { return accb() + lps * nbp; }  // [lps][4] per-lane g_trans partials
-  __host__ __device__ int bwd_floats() const { return red() + lps * 4; }
+  int J, nbp;
+  __host__ __device__ int x() const { return 0; }               // [J][12] local (M | tl); bwd later: (gM | g_logscale)
+  __host__ __device__ int g() const { return 12 * J; }          // [J][12] global (GR | Gt); before the walk: Rs staging [J][9]
+  __host__ __device__ int jr() const { return 24 * J; }         // [J][4]  rest joints; bwd later: gradient on them
+  __host__ __device__ int beta() const { return 28 * J; }       // [nbp]
+  __host__ __device__ int tail() const { return 28 * J + nbp; }
+  __host__ __device__ int scale() const { return tail(); }      // [J][4] exp(log-scales), dead once the M_j are built
+  __host__ __device__ int fwd_floats() const { return tail() + 4 * J; }
+  // backward: gradient records [J][20] = (gGR | gGt)(12) (g_logscale acc, -)(4) (gJ acc, -)(4); overlays the scales
+  __host__ __device__ int rec() const { return tail(); }
+  __host__ __device__ int bwd_floats() const { return tail() + 20 * J; }
 };
 
 __device__ __forceinline__ void ld_rec(const float* rec, m3& M, f3& w) {
@@ -81,136 +90,157 @@ __device__ __forceinline__ void st_rec(float* rec, const m3& M, f3 w) {
   p[1] = make_float4(M.a[3], M.a[4], M.a[5], w.y);
   p[2] = make_float4(M.a[6], M.a[7], M.a[8], w.z);
 }
+__device__ __forceinline__ f3 rec_w(const float* rec) { return mk3(rec[3], rec[7], rec[11]); }
 
-// Forward state shared by forward and backward kernels: fills Rrec/Grec/srec/beta of one sample.
-template <int LPS>
-__device__ __forceinline__ void pose_forward_state(const DevModel& m, const PoseArgs& a, const PoseSmem& L, float* sm,
-                                                   int bb, int l) {
+// Phase A (forward and backward): beta, rest joints, rotations, scales, local transforms.
+//   X[j] = (M_j | tl_j) with M_j = S_p^-1 R_j S_j (batch_lbs.py:163-173), tl_j = J_j - J_p (+ flipped
+//   betas_trans, batch_lbs.py:148,159-160);  X[0] = (R_0 | J_0)  (the root is never scaled, :151).
+//   jr[j] = rest joint J_j.   `stage` receives Rs packed [J][9]; `sc` the scales [J][4].
+__device__ __forceinline__ void pose_local_state(const DevModel& m, const PoseArgs& a, float* X, float* jr, float* sbeta,
+                                                 float* stage, float* sc, int b, int l) {
   const int J = m.J;
-  float* Rrec = sm + L.rrec();
-  float* Grec = sm + L.grec();
-  float* srec = sm + L.srec();
-  float* sbeta = sm + L.beta();
-  for (int k = l; k < a.nb; k += LPS) sbeta[k] = a.beta[(long long)bb * a.beta_stride + k];
+  const bool rotmat = (a.flags & SMIL_F_THETA_IS_ROTMAT) != 0;
+  for (int k = l; k < a.nb; k += 32) sbeta[k] = a.beta[(long long)b * a.beta_stride + k];
+  if (rotmat) {  // [J][9] contiguous per sample -> staging, coalesced
+    const float* src = a.theta + (long long)b * a.theta_stride;
+    for (int e = l; e < 9 * J; e += 32) stage[e] = src[e];
+  }
   __syncwarp();
-  // rest joints into the .w slots of Rrec
-  for (int e = l; e < 3 * J; e += LPS) {
+  for (int e = l; e < 3 * J; e += 32) {
     float v;
     if (a.jrest_mode == 1) {
       v = m.J_static[e];
     } else if (a.jrest_mode == 2) {
-      v = a.jrest_in[(long long)bb * 3 * J + e];
+      v = a.jrest_in[(long long)b * 3 * J + e];
     } else {
       v = m.JT[e];
       for (int k = 0; k < a.nb; ++k) v = fmaf(sbeta[k], m.JS[k * 3 * J + e], v);
     }
-    int j = e / 3, c = e - 3 * j;
-    Rrec[j * 12 + 4 * c + 3] = v;
+    const int j = e / 3, c = e - 3 * j;
+    jr[j * 4 + c] = v;
   }
-  // rotations + scales
-  for (int j = l; j < J; j += LPS) {
+  for (int j = l; j < J; j += 32) {
     m3 R;
-    if (a.flags & SMIL_F_THETA_IS_ROTMAT) {
-      const float* p = a.theta + (long long)bb * a.theta_stride + j * 9;
+    if (rotmat) {
 #pragma unroll
-      for (int q = 0; q < 9; ++q) R.a[q] = p[q];
+      for (int q = 0; q < 9; ++q) R.a[q] = stage[j * 9 + q];
     } else {
-      R = rodrigues(ld3(a.theta + (long long)bb * a.theta_stride + j * 3));
-    }
-    float* r = Rrec + j * 12;
+      R = rodrigues(ld3(a.theta + (long long)b * a.theta_stride + j * 3));
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
-      r[4 * q + 0] = R.a[3 * q + 0];
-      r[4 * q + 1] = R.a[3 * q + 1];
-      r[4 * q + 2] = R.a[3 * q + 2];
+      for (int q = 0; q < 9; ++q) stage[j * 9 + q] = R.a[q];
     }
+    st_rec(X + j * 12, R, mk3(0.f, 0.f, 0.f));
     f3 s = mk3(1.f, 1.f, 1.f);
     if (a.ls) {
-      const float* p = a.ls + (long long)bb * a.ls_stride + j * 3;
+      const float* p = a.ls + (long long)b * a.ls_stride + j * 3;
       s = mk3(expf(p[0]), expf(p[1]), expf(p[2]));
     }
-    srec[j * 4 + 0] = s.x; srec[j * 4 + 1] = s.y; srec[j * 4 + 2] = s.z;
-  }
-  __syncwarp();
-  // level walk
-  if (l == 0) {
-    m3 R0; f3 J0;
-    ld_rec(Rrec, R0, J0);
-    st_rec(Grec, R0, J0);
+    sc[j * 4 + 0] = s.x; sc[j * 4 + 1] = s.y; sc[j * 4 + 2] = s.z;
   }
   __syncwarp();
   const bool prop = (a.flags & SMIL_F_PROPAGATE_SCALING) != 0;
+  for (int j = l; j < J; j += 32) {
+    m3 R; f3 dummy;
+    ld_rec(X + j * 12, R, dummy);
+    const f3 Jj = ld3(jr + j * 4);
+    if (j == 0) {
+      st_rec(X, R, Jj);
+      continue;
+    }
+    const int p = m.parents[j];
+    const f3 Jp = ld3(jr + p * 4);
+    const f3 si = ld3(sc + j * 4);
+    f3 pin = mk3(1.f, 1.f, 1.f);
+    if (!prop) { const f3 sp = ld3(sc + p * 4); pin = mk3(1.0f / sp.x, 1.0f / sp.y, 1.0f / sp.z); }
+    m3 M;
+    M.a[0] = pin.x * R.a[0] * si.x; M.a[1] = pin.x * R.a[1] * si.y; M.a[2] = pin.x * R.a[2] * si.z;
+    M.a[3] = pin.y * R.a[3] * si.x; M.a[4] = pin.y * R.a[4] * si.y; M.a[5] = pin.y * R.a[5] * si.z;
+    M.a[6] = pin.z * R.a[6] * si.x; M.a[7] = pin.z * R.a[7] * si.y; M.a[8] = pin.z * R.a[8] * si.z;
+    f3 tl = mk3(Jj.x - Jp.x, Jj.y - Jp.y, Jj.z - Jp.z);
+    if (a.bt) {
+      const float* bp = a.bt + (long long)b * a.bt_stride + j * 3;
+      tl.x += bp[0]; tl.y -= bp[1]; tl.z += bp[2];  // y flipped for Unreal data, batch_lbs.py:148
+    }
+    st_rec(X + j * 12, M, tl);
+  }
+  __syncwarp();
+}
+
+// Level walk: G[i] = (G[p].R M_i | G[p].R tl_i + G[p].t);  G[0] = X[0].
+__device__ __forceinline__ void pose_walk(const DevModel& m, const float* X, float* G, int l) {
+  if (l == 0) {
+    m3 R0; f3 J0;
+    ld_rec(X, R0, J0);
+    st_rec(G, R0, J0);
+  }
+  __syncwarp();
   for (int lev = 1; lev < m.num_levels; ++lev) {
     const int beg = m.level_ptr[lev], end = m.level_ptr[lev + 1];
-    for (int q = beg + l; q < end; q += LPS) {
+    for (int q = beg + l; q < end; q += 32) {
       const int i = m.order[q], p = m.parents[i];
-      m3 R, GRp; f3 Ji, Jp, Gtp;
-      ld_rec(Rrec + i * 12, R, Ji);
-      ld_rec(Grec + p * 12, GRp, Gtp);
-      Jp = mk3(Rrec[p * 12 + 3], Rrec[p * 12 + 7], Rrec[p * 12 + 11]);
-      f3 si = ld3(srec + i * 4), pin = mk3(1.f, 1.f, 1.f);
-      if (!prop) { f3 sp = ld3(srec + p * 4); pin = mk3(1.0f / sp.x, 1.0f / sp.y, 1.0f / sp.z); }
-      m3 M;
-      M.a[0] = pin.x * R.a[0] * si.x; M.a[1] = pin.x * R.a[1] * si.y; M.a[2] = pin.x * R.a[2] * si.z;
-      M.a[3] = pin.y * R.a[3] * si.x; M.a[4] = pin.y * R.a[4] * si.y; M.a[5] = pin.y * R.a[5] * si.z;
-      M.a[6] = pin.z * R.a[6] * si.x; M.a[7] = pin.z * R.a[7] * si.y; M.a[8] = pin.z * R.a[8] * si.z;
-      f3 tl = mk3(Ji.x - Jp.x, Ji.y - Jp.y, Ji.z - Jp.z);
-      if (a.bt) {
-        const float* bp = a.bt + (long long)bb * a.bt_stride + i * 3;
-        tl.x += bp[0]; tl.y -= bp[1]; tl.z += bp[2];  // y flipped for Unreal data, batch_lbs.py:148
-      }
-      m3 GR = matmul(GRp, M);
+      m3 M, GRp; f3 tl, Gtp;
+      ld_rec(X + i * 12, M, tl);
+      ld_rec(G + p * 12, GRp, Gtp);
+      const m3 GR = matmul(GRp, M);
       f3 Gt = mul(GRp, tl);
       Gt.x += Gtp.x; Gt.y += Gtp.y; Gt.z += Gtp.z;
-      st_rec(Grec + i * 12, GR, Gt);
+      st_rec(G + i * 12, GR, Gt);
     }
     __syncwarp();
   }
 }
 
-template <int LPS>
+// coalesced float4 copy of n floats (n % 4 == 0, both sides 16-byte aligned)
+__device__ __forceinline__ void warp_copy4(float* dst, const float* src, int n, int l) {
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  float4* d4 = reinterpret_cast<float4*>(dst);
+  for (int e = l; e < (n >> 2); e += 32) d4[e] = s4[e];
+}
+
 __global__ void __launch_bounds__(POSE_THREADS) pose_fwd_kernel(DevModel m, PoseArgs a, PoseSmem L) {
   extern __shared__ __align__(16) float smem_pose[];
-  constexpr int SPB = POSE_THREADS / LPS;
-  const int grp = threadIdx.x / LPS, l = threadIdx.x % LPS;
-  const int b = blockIdx.x * SPB + grp;
-  const bool valid = b < a.B;
-  const int bb = valid ? b : a.B - 1;
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int b = blockIdx.x * POSE_WPB + w;
+  if (b >= a.B) return;  // whole warp; only __syncwarp() below
   const int J = m.J;
-  float* sm = smem_pose + (size_t)grp * ((L.fwd_floats() + 3) & ~3);
-  pose_forward_state<LPS>(m, a, L, sm, bb, l);
-  float* Rrec = sm + L.rrec();
-  float* Grec = sm + L.grec();
-  float* Arec = sm + L.arec();
-  const float* sbeta = sm + L.beta();
-  // Rs output, coalesced
-  if (a.Rs && valid) {
+  float* sm = smem_pose + (size_t)w * ((L.fwd_floats() + 3) & ~3);
+  float* X = sm + L.x();
+  float* G = sm + L.g();
+  float* jr = sm + L.jr();
+  float* sbeta = sm + L.beta();
+  float* sc = sm + L.scale();
+  pose_local_state(m, a, X, jr, sbeta, /*stage=*/G, sc, b, l);
+  // Rs output from the packed staging copy (a sample's 9J floats are 16-byte aligned only if 9J % 4 == 0)
+  if (a.Rs) {
     float* out = a.Rs + (long long)b * 9 * J;
-    for (int e = l; e < 9 * J; e += LPS) {
-      int j = e / 9, q = e - 9 * j;
-      out[e] = Rrec[j * 12 + (q / 3) * 4 + (q % 3)];
-    }
-  }
-  // A = [GR | Gt - GR Jrest], new_J = Gt
-  for (int j = l; j < J; j += LPS) {
-    m3 GR, R; f3 Gt, Jr;
-    ld_rec(Grec + j * 12, GR, Gt);
-    Jr = mk3(Rrec[j * 12 + 3], Rrec[j * 12 + 7], Rrec[j * 12 + 11]);
-    f3 rot = mul(GR, Jr);
-    f3 At = mk3(Gt.x - rot.x, Gt.y - rot.y, Gt.z - rot.z);
-    Arec[j * 4 + 0] = At.x; Arec[j * 4 + 1] = At.y; Arec[j * 4 + 2] = At.z;
-    if (valid) {
-      if (a.A) st_rec(a.A + ((long long)b * J + j) * 12, GR, At);
-      if (a.newJ) st3(a.newJ + ((long long)b * J + j) * 3, Gt);
-      if (a.joints && a.joints_mode == 2) st3(a.joints + ((long long)b * J + j) * 3, Gt);
-    }
+    if (((9 * J) & 3) == 0) warp_copy4(out, G, 9 * J, l);
+    else for (int e = l; e < 9 * J; e += 32) out[e] = G[e];
   }
   __syncwarp();
+  pose_walk(m, X, G, l);
+  // A = [GR | Gt - GR Jrest] -> X (free after the walk), new_J = Gt
+  for (int j = l; j < J; j += 32) {
+    m3 GR; f3 Gt;
+    ld_rec(G + j * 12, GR, Gt);
+    const f3 rot = mul(GR, ld3(jr + j * 4));
+    st_rec(X + j * 12, GR, mk3(Gt.x - rot.x, Gt.y - rot.y, Gt.z - rot.z));
+  }
+  __syncwarp();
+  if (a.A) warp_copy4(a.A + (long long)b * 12 * J, X, 12 * J, l);
+  if (a.newJ || (a.joints && a.joints_mode == 2)) {
+    for (int e = l; e < 3 * J; e += 32) {
+      const int j = e / 3, c = e - 3 * j;
+      const float v = G[j * 12 + 4 * c + 3];
+      if (a.newJ) a.newJ[(long long)b * 3 * J + e] = v;
+      if (a.joints && a.joints_mode == 2) a.joints[(long long)b * 3 * J + e] = v;
+    }
+  }
   if (a.joints && a.joints_mode == 1) {
+    // joints_j = sum over coupled bones k of A_k [c0 + sum_m beta_m cm ; c0.w] + rowsum_j * trans
     f3 tr = mk3(0.f, 0.f, 0.f);
-    if (a.trans) tr = ld3(a.trans + (long long)bb * a.trans_stride);
-    for (int j = l; j < J; j += LPS) {
-      float rs = m.jreg_rowsum[j];
+    if (a.trans) tr = ld3(a.trans + (long long)b * a.trans_stride);
+    for (int j = l; j < J; j += 32) {
+      const float rs = m.jreg_rowsum[j];
       f3 acc = mk3(rs * tr.x, rs * tr.y, rs * tr.z);
       for (int pi = m.pj_ptr[j]; pi < m.pj_ptr[j + 1]; ++pi) {
         const int k = m.pj_bone[pi];
@@ -218,274 +248,259 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_fwd_kernel(DevModel m, Pose
         f3 q = mk3(c0.x, c0.y, c0.z);
         const float* cm = m.pj_cm + (long long)pi * m.nB * 3;
         for (int t = 0; t < a.nb; ++t) {
-          float bt_ = sbeta[t];
+          const float bt_ = sbeta[t];
           q.x = fmaf(bt_, cm[3 * t], q.x); q.y = fmaf(bt_, cm[3 * t + 1], q.y); q.z = fmaf(bt_, cm[3 * t + 2], q.z);
         }
-        m3 GR; f3 Gt;
-        ld_rec(Grec + k * 12, GR, Gt);
-        f3 r = mul(GR, q);
-        acc.x += fmaf(Arec[k * 4 + 0], c0.w, r.x);
-        acc.y += fmaf(Arec[k * 4 + 1], c0.w, r.y);
-        acc.z += fmaf(Arec[k * 4 + 2], c0.w, r.z);
+        m3 AR; f3 At;
+        ld_rec(X + k * 12, AR, At);
+        const f3 r = mul(AR, q);
+        acc.x += fmaf(At.x, c0.w, r.x);
+        acc.y += fmaf(At.y, c0.w, r.y);
+        acc.z += fmaf(At.z, c0.w, r.z);
       }
-      if (valid) st3(a.joints + ((long long)b * J + j) * 3, acc);
+      st3(a.joints + ((long long)b * J + j) * 3, acc);
     }
   }
 }
 
-// Backward: recompute the forward state, then walk the tree leaves -> root.  Child -> parent
-// accumulation is a deterministic gather (no atomics): every child writes an 18-float
-// contribution record, then (parent, element) tasks sum over the parent's children.
-template <int LPS>
-__global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, PoseArgs a, PoseSmem L) {
+// Backward.  Gradient records rec[j] (20 floats) share one layout between "what joint j has received"
+// and "what joint j hands to its parent", so the child -> parent accumulation is a plain float4 gather
+// in a fixed order (deterministic, no atomics):
+//   [0..11]  (gGR | gGt)   before j is processed: dL/dG_j;        after: contribution to dL/dG_parent
+//   [12..14] log-scale     before: sum of the children's d/ds_j;   after: d/ds_parent from j (non-propagating mode)
+//   [16..18] rest joint    before: dL/dJ_j so far;                 after: dL/dJ_parent from j (= -gtl_j)
+// When j is processed its final values move to X[j] = (gM_j | g_logscale_j) and jr[j] = dL/dJ_j, from where
+// the lane-per-joint epilogue produces g_theta (Rodrigues VJP), g_logscale, g_betas_trans, g_beta.
+__global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, PoseArgs a, PoseSmem L, int pairs_mode) {
   extern __shared__ __align__(16) float smem_pose[];
-  constexpr int SPB = POSE_THREADS / LPS;
-  const int grp = threadIdx.x / LPS, l = threadIdx.x % LPS;
-  const int b = blockIdx.x * SPB + grp;
-  const bool valid = b < a.B;
-  const int bb = valid ? b : a.B - 1;
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int b = blockIdx.x * POSE_WPB + w;
+  if (b >= a.B) return;
   const int J = m.J, nb = a.nb;
-  float* sm = smem_pose + (size_t)grp * ((L.bwd_floats() + 3) & ~3);
-  pose_forward_state<LPS>(m, a, L, sm, bb, l);
-  float* Rrec = sm + L.rrec();
-  float* Grec = sm + L.grec();
-  float* srec = sm + L.srec();
-  const float* sbeta = sm + L.beta();
-  float* gG = sm + L.gg();
-  float* contrib = sm + L.contrib();
-  float* gJ = sm + L.gj();
-  float* gls = sm + L.gls();
-  float* accb = sm + L.accb();
+  const int per = ((L.bwd_floats() + (pairs_mode ? 32 * L.nbp : 0)) + 3) & ~3;
+  float* sm = smem_pose + (size_t)w * per;
+  float* X = sm + L.x();
+  float* G = sm + L.g();
+  float* jr = sm + L.jr();
+  float* sbeta = sm + L.beta();
+  float* rec = sm + L.rec();
+  float* accb = sm + L.bwd_floats();  // [32][nbp], pairs mode only
   const bool prop = (a.flags & SMIL_F_PROPAGATE_SCALING) != 0;
   const bool rotmat = (a.flags & SMIL_F_THETA_IS_ROTMAT) != 0;
 
-  for (int k = 0; k < nb; ++k) accb[l * L.nbp + k] = 0.f;
-  f3 gtr = mk3(0.f, 0.f, 0.f);  // per-lane partial of g_trans from the closed-form joints
+  pose_local_state(m, a, X, jr, sbeta, /*stage=*/G, /*sc=*/rec, b, l);
+  if (a.A_saved) {
+    warp_copy4(G, a.A_saved + (long long)b * 12 * J, 12 * J, l);  // (GR | At): only GR is used below
+    __syncwarp();
+  } else {
+    pose_walk(m, X, G, l);
+  }
 
-  // ---- gather g_A per bone, add the closed-form posed-joint term, initialise gG / gJ --------------
-  for (int j = l; j < J; j += LPS) {
-    m3 gAR; f3 gAt;
-#pragma unroll
-    for (int q = 0; q < 9; ++q) gAR.a[q] = 0.f;
-    gAt = mk3(0.f, 0.f, 0.f);
-    if (a.gA_dense) {
-      m3 T; f3 w;
-      ld_rec(a.gA_dense + ((long long)bb * J + j) * 12, T, w);
-      gAR = T; gAt = w;
-    }
+  // ---- dL/dA per bone: dense buffer + slot partials of the skin pass (+ closed-form posed joints) --------
+  f3 gtr = mk3(0.f, 0.f, 0.f);
+  if (pairs_mode)
+    for (int k = 0; k < nb; ++k) accb[l * L.nbp + k] = 0.f;
+  for (int e = l; e < 3 * J; e += 32) {
+    const int j = e / 3, r = e - 3 * j;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.gA_dense) acc = reinterpret_cast<const float4*>(a.gA_dense)[(long long)b * 3 * J + e];
     if (a.gA_slots) {
+      const float4* sl = reinterpret_cast<const float4*>(a.gA_slots) + (long long)b * a.nslots * 3 + r;
       for (int si = m.sb_ptr[j]; si < m.sb_ptr[j + 1]; ++si) {
-        m3 T; f3 w;
-        ld_rec(a.gA_slots + ((long long)bb * a.nslots + m.sb_slot[si]) * 12, T, w);
-#pragma unroll
-        for (int q = 0; q < 9; ++q) gAR.a[q] += T.a[q];
-        gAt.x += w.x; gAt.y += w.y; gAt.z += w.z;
+        const float4 t = sl[si * 3];
+        acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
       }
     }
-    m3 GR; f3 Gt;
-    ld_rec(Grec + j * 12, GR, Gt);
-    if (a.joints_mode == 1 && a.g_joints) {
+    if (pairs_mode) {
+      // joints_jj = sum_k A_k [q_jk ; c0.w]: row r of dL/dA_k gets g_joints[jj][r] * [q ; c0.w]
+      const f3 GRr = ld3(G + j * 12 + 4 * r);
       for (int pq = m.pb_ptr[j]; pq < m.pb_ptr[j + 1]; ++pq) {
         const int pi = m.pb_pair[pq];
-        const int jj = m.pj_joint[pi];
-        const f3 gj = ld3(a.g_joints + ((long long)bb * J + jj) * 3);
+        const float gj = a.g_joints[((long long)b * J + m.pj_joint[pi]) * 3 + r];
         const float4 c0 = reinterpret_cast<const float4*>(m.pj_c0)[pi];
         const float* cm = m.pj_cm + (long long)pi * m.nB * 3;
         f3 q = mk3(c0.x, c0.y, c0.z);
-        f3 u = mulT(GR, gj);
         for (int t = 0; t < nb; ++t) {
-          float bt_ = sbeta[t];
+          const float bt_ = sbeta[t];
           q.x = fmaf(bt_, cm[3 * t], q.x); q.y = fmaf(bt_, cm[3 * t + 1], q.y); q.z = fmaf(bt_, cm[3 * t + 2], q.z);
-          accb[l * L.nbp + t] += u.x * cm[3 * t] + u.y * cm[3 * t + 1] + u.z * cm[3 * t + 2];
+          accb[l * L.nbp + t] += gj * (GRr.x * cm[3 * t] + GRr.y * cm[3 * t + 1] + GRr.z * cm[3 * t + 2]);
         }
-        gAR.a[0] = fmaf(gj.x, q.x, gAR.a[0]); gAR.a[1] = fmaf(gj.x, q.y, gAR.a[1]); gAR.a[2] = fmaf(gj.x, q.z, gAR.a[2]);
-        gAR.a[3] = fmaf(gj.y, q.x, gAR.a[3]); gAR.a[4] = fmaf(gj.y, q.y, gAR.a[4]); gAR.a[5] = fmaf(gj.y, q.z, gAR.a[5]);
-        gAR.a[6] = fmaf(gj.z, q.x, gAR.a[6]); gAR.a[7] = fmaf(gj.z, q.y, gAR.a[7]); gAR.a[8] = fmaf(gj.z, q.z, gAR.a[8]);
-        gAt.x = fmaf(gj.x, c0.w, gAt.x); gAt.y = fmaf(gj.y, c0.w, gAt.y); gAt.z = fmaf(gj.z, c0.w, gAt.z);
+        acc.x = fmaf(gj, q.x, acc.x); acc.y = fmaf(gj, q.y, acc.y); acc.z = fmaf(gj, q.z, acc.z);
+        acc.w = fmaf(gj, c0.w, acc.w);
       }
-    }
-    if (a.joints_mode == 1 && a.g_joints) {
       const float rs = m.jreg_rowsum[j];
-      const f3 gj = ld3(a.g_joints + ((long long)bb * J + j) * 3);
-      gtr.x = fmaf(rs, gj.x, gtr.x); gtr.y = fmaf(rs, gj.y, gtr.y); gtr.z = fmaf(rs, gj.z, gtr.z);
+      const float gjj = a.g_joints[(long long)b * 3 * J + e];
+      if (r == 0) gtr.x = fmaf(rs, gjj, gtr.x);
+      if (r == 1) gtr.y = fmaf(rs, gjj, gtr.y);
+      if (r == 2) gtr.z = fmaf(rs, gjj, gtr.z);
     }
-    // A = [GR | Gt - GR Jr]
-    const f3 Jr = mk3(Rrec[j * 12 + 3], Rrec[j * 12 + 7], Rrec[j * 12 + 11]);
+    reinterpret_cast<float4*>(rec)[j * 5 + r] = acc;
+  }
+  __syncwarp();
+  // ---- A = [GR | Gt - GR Jrest], new_J = Gt  ->  initial (gGR | gGt) and dL/dJrest ---------------------------
+  for (int j = l; j < J; j += 32) {
+    m3 gAR, GR; f3 gAt, dummy;
+    ld_rec(rec + j * 20, gAR, gAt);
+    ld_rec(G + j * 12, GR, dummy);
+    const f3 Jr = ld3(jr + j * 4);
     m3 gGR;
     gGR.a[0] = gAR.a[0] - gAt.x * Jr.x; gGR.a[1] = gAR.a[1] - gAt.x * Jr.y; gGR.a[2] = gAR.a[2] - gAt.x * Jr.z;
     gGR.a[3] = gAR.a[3] - gAt.y * Jr.x; gGR.a[4] = gAR.a[4] - gAt.y * Jr.y; gGR.a[5] = gAR.a[5] - gAt.y * Jr.z;
     gGR.a[6] = gAR.a[6] - gAt.z * Jr.x; gGR.a[7] = gAR.a[7] - gAt.z * Jr.y; gGR.a[8] = gAR.a[8] - gAt.z * Jr.z;
     f3 gGt = gAt;
     if (a.joints_mode == 2 && a.g_joints) {
-      const f3 g = ld3(a.g_joints + ((long long)bb * J + j) * 3);
+      const f3 g = ld3(a.g_joints + ((long long)b * J + j) * 3);
       gGt.x += g.x; gGt.y += g.y; gGt.z += g.z;
     }
     if (a.g_newJ) {
-      const f3 g = ld3(a.g_newJ + ((long long)bb * J + j) * 3);
+      const f3 g = ld3(a.g_newJ + ((long long)b * J + j) * 3);
       gGt.x += g.x; gGt.y += g.y; gGt.z += g.z;
     }
-    st_rec(gG + j * 12, gGR, gGt);
+    st_rec(rec + j * 20, gGR, gGt);
     const f3 r = mulT(GR, gAt);
-    gJ[j * 4 + 0] = -r.x; gJ[j * 4 + 1] = -r.y; gJ[j * 4 + 2] = -r.z;
-    gls[j * 4 + 0] = 0.f; gls[j * 4 + 1] = 0.f; gls[j * 4 + 2] = 0.f;
+    float4* tailp = reinterpret_cast<float4*>(rec + j * 20 + 12);
+    tailp[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    tailp[1] = make_float4(-r.x, -r.y, -r.z, 0.f);
   }
   __syncwarp();
-
-  // ---- leaves -> root -----------------------------------------------------------------------------
+  // ---- leaves -> root -----------------------------------------------------------------------------------
   for (int lev = m.num_levels - 1; lev >= 1; --lev) {
     const int beg = m.level_ptr[lev], end = m.level_ptr[lev + 1];
-    for (int q = beg + l; q < end; q += LPS) {
+    for (int q = beg + l; q < end; q += 32) {
       const int i = m.order[q], p = m.parents[i];
-      m3 R, GRp, gGR; f3 Ji, Gtp, gGt;
-      ld_rec(Rrec + i * 12, R, Ji);
-      ld_rec(Grec + p * 12, GRp, Gtp);
-      ld_rec(gG + i * 12, gGR, gGt);
-      const f3 Jp = mk3(Rrec[p * 12 + 3], Rrec[p * 12 + 7], Rrec[p * 12 + 11]);
-      const f3 si = ld3(srec + i * 4);
-      f3 pin = mk3(1.f, 1.f, 1.f);
-      if (!prop) { f3 sp = ld3(srec + p * 4); pin = mk3(1.0f / sp.x, 1.0f / sp.y, 1.0f / sp.z); }
-      m3 M;
-      M.a[0] = pin.x * R.a[0] * si.x; M.a[1] = pin.x * R.a[1] * si.y; M.a[2] = pin.x * R.a[2] * si.z;
-      M.a[3] = pin.y * R.a[3] * si.x; M.a[4] = pin.y * R.a[4] * si.y; M.a[5] = pin.y * R.a[5] * si.z;
-      M.a[6] = pin.z * R.a[6] * si.x; M.a[7] = pin.z * R.a[7] * si.y; M.a[8] = pin.z * R.a[8] * si.z;
-      f3 tl = mk3(Ji.x - Jp.x, Ji.y - Jp.y, Ji.z - Jp.z);
-      if (a.bt) {
-        const float* bp = a.bt + (long long)bb * a.bt_stride + i * 3;
-        tl.x += bp[0]; tl.y -= bp[1]; tl.z += bp[2];
-      }
+      m3 M, GRp, gGR; f3 tl, gGt, dummy;
+      ld_rec(X + i * 12, M, tl);
+      ld_rec(G + p * 12, GRp, dummy);
+      ld_rec(rec + i * 20, gGR, gGt);
+      const float4 lsacc = reinterpret_cast<const float4*>(rec + i * 20 + 12)[0];
+      const float4 jacc = reinterpret_cast<const float4*>(rec + i * 20 + 12)[1];
       const m3 gM = matmul_AtB(GRp, gGR);  // GRp^T gGR
       const f3 gtl = mulT(GRp, gGt);
-      // contribution to the parent
       m3 dGR = matmul_ABt(gGR, M);
       dGR.a[0] = fmaf(gGt.x, tl.x, dGR.a[0]); dGR.a[1] = fmaf(gGt.x, tl.y, dGR.a[1]); dGR.a[2] = fmaf(gGt.x, tl.z, dGR.a[2]);
       dGR.a[3] = fmaf(gGt.y, tl.x, dGR.a[3]); dGR.a[4] = fmaf(gGt.y, tl.y, dGR.a[4]); dGR.a[5] = fmaf(gGt.y, tl.z, dGR.a[5]);
       dGR.a[6] = fmaf(gGt.z, tl.x, dGR.a[6]); dGR.a[7] = fmaf(gGt.z, tl.y, dGR.a[7]); dGR.a[8] = fmaf(gGt.z, tl.z, dGR.a[8]);
-      float* cr = contrib + i * 20;
-      st_rec(cr, dGR, gGt);
+      // M = diag(1/s_p) R diag(s_i): d/dlog s_i = column sums of gM o M, d/dlog s_p = -(row sums)
+      const float e0 = gM.a[0] * M.a[0], e1 = gM.a[1] * M.a[1], e2 = gM.a[2] * M.a[2];
+      const float e3 = gM.a[3] * M.a[3], e4 = gM.a[4] * M.a[4], e5 = gM.a[5] * M.a[5];
+      const float e6 = gM.a[6] * M.a[6], e7 = gM.a[7] * M.a[7], e8 = gM.a[8] * M.a[8];
+      const f3 gls = mk3(lsacc.x + (e0 + e3 + e6), lsacc.y + (e1 + e4 + e7), lsacc.z + (e2 + e5 + e8));
       f3 dls = mk3(0.f, 0.f, 0.f);
-      if (!prop) {
-        dls.x = -pin.x * (gM.a[0] * R.a[0] * si.x + gM.a[1] * R.a[1] * si.y + gM.a[2] * R.a[2] * si.z);
-        dls.y = -pin.y * (gM.a[3] * R.a[3] * si.x + gM.a[4] * R.a[4] * si.y + gM.a[5] * R.a[5] * si.z);
-        dls.z = -pin.z * (gM.a[6] * R.a[6] * si.x + gM.a[7] * R.a[7] * si.y + gM.a[8] * R.a[8] * si.z);
-      }
-      cr[12] = dls.x; cr[13] = dls.y; cr[14] = dls.z; cr[15] = 0.f;
-      cr[16] = -gtl.x; cr[17] = -gtl.y; cr[18] = -gtl.z; cr[19] = 0.f;
-      // own gradients
-      m3 gR;
-      gR.a[0] = pin.x * gM.a[0] * si.x; gR.a[1] = pin.x * gM.a[1] * si.y; gR.a[2] = pin.x * gM.a[2] * si.z;
-      gR.a[3] = pin.y * gM.a[3] * si.x; gR.a[4] = pin.y * gM.a[4] * si.y; gR.a[5] = pin.y * gM.a[5] * si.z;
-      gR.a[6] = pin.z * gM.a[6] * si.x; gR.a[7] = pin.z * gM.a[7] * si.y; gR.a[8] = pin.z * gM.a[8] * si.z;
-      if (a.g_Rs) {
-        const float* gp = a.g_Rs + ((long long)bb * J + i) * 9;
-#pragma unroll
-        for (int t = 0; t < 9; ++t) gR.a[t] += gp[t];
-      }
-      if (a.g_Rs2) {
-        const float* gp = a.g_Rs2 + ((long long)bb * J + i) * 9;
-#pragma unroll
-        for (int t = 0; t < 9; ++t) gR.a[t] += gp[t];
-      }
-      if (valid && a.g_theta) {
-        if (rotmat) {
-          float* o = a.g_theta + ((long long)b * J + i) * 9;
-#pragma unroll
-          for (int t = 0; t < 9; ++t) o[t] = gR.a[t];
-        } else {
-          st3(a.g_theta + ((long long)b * J + i) * 3, rodrigues_vjp(ld3(a.theta + (long long)bb * a.theta_stride + i * 3), gR));
-        }
-      }
-      // own log-scale: d/ds_i of M = diag(pin) R diag(s_i)
-      gls[i * 4 + 0] += (pin.x * R.a[0] * gM.a[0] + pin.y * R.a[3] * gM.a[3] + pin.z * R.a[6] * gM.a[6]) * si.x;
-      gls[i * 4 + 1] += (pin.x * R.a[1] * gM.a[1] + pin.y * R.a[4] * gM.a[4] + pin.z * R.a[7] * gM.a[7]) * si.y;
-      gls[i * 4 + 2] += (pin.x * R.a[2] * gM.a[2] + pin.y * R.a[5] * gM.a[5] + pin.z * R.a[8] * gM.a[8]) * si.z;
-      gJ[i * 4 + 0] += gtl.x; gJ[i * 4 + 1] += gtl.y; gJ[i * 4 + 2] += gtl.z;
-      if (valid && a.g_bt) {
-        st3(a.g_bt + ((long long)b * J + i) * 3, mk3(gtl.x, -gtl.y, gtl.z));
-      }
+      if (!prop) dls = mk3(-(e0 + e1 + e2), -(e3 + e4 + e5), -(e6 + e7 + e8));
+      st_rec(X + i * 12, gM, gls);
+      jr[i * 4 + 0] = jacc.x + gtl.x; jr[i * 4 + 1] = jacc.y + gtl.y; jr[i * 4 + 2] = jacc.z + gtl.z;
+      st_rec(rec + i * 20, dGR, gGt);
+      float4* tailp = reinterpret_cast<float4*>(rec + i * 20 + 12);
+      tailp[0] = make_float4(dls.x, dls.y, dls.z, 0.f);
+      tailp[1] = make_float4(-gtl.x, -gtl.y, -gtl.z, 0.f);
     }
     __syncwarp();
-    // gather the contributions of level `lev` into their parents (level lev-1)
+    // parents (level lev-1) gather what their children just wrote; 5 float4 per record
     const int pbeg = m.level_ptr[lev - 1], pend = m.level_ptr[lev];
-    const int ntask = (pend - pbeg) * 18;
-    for (int t = l; t < ntask; t += LPS) {
-      const int pi = t / 18, e = t - pi * 18;
+    const int ntask = (pend - pbeg) * 5;
+    for (int t = l; t < ntask; t += 32) {
+      const int pi = t / 5, q5 = t - pi * 5;
       const int p = m.order[pbeg + pi];
-      // element e: 0..8 dGR, 9..11 dGt, 12..14 dls, 15..17 dJ
-      int src, dstoff;
-      float* dst;
-      if (e < 9) { src = (e / 3) * 4 + (e % 3); dst = gG + p * 12; dstoff = src; }
-      else if (e < 12) { src = (e - 9) * 4 + 3; dst = gG + p * 12; dstoff = src; }
-      else if (e < 15) { src = e; dst = gls + p * 4; dstoff = e - 12; }
-      else { src = e + 1; dst = gJ + p * 4; dstoff = e - 15; }
-      float acc = 0.f;
-      for (int ci = m.child_ptr[p]; ci < m.child_ptr[p + 1]; ++ci) acc += contrib[m.child_idx[ci] * 20 + src];
-      dst[dstoff] += acc;
+      const int c0 = m.child_ptr[p], c1 = m.child_ptr[p + 1];
+      if (c0 == c1) continue;
+      float4* dst = reinterpret_cast<float4*>(rec + p * 20) + q5;
+      float4 acc = *dst;
+      for (int ci = c0; ci < c1; ++ci) {
+        const float4 t4 = reinterpret_cast<const float4*>(rec + m.child_idx[ci] * 20)[q5];
+        acc.x += t4.x; acc.y += t4.y; acc.z += t4.z; acc.w += t4.w;
+      }
+      *dst = acc;
     }
     __syncwarp();
   }
-  // ---- root ---------------------------------------------------------------------------------------
+  // root: G_0 = (R_0 | J_0)
   if (l == 0) {
     m3 gGR; f3 gGt;
-    ld_rec(gG, gGR, gGt);
-    if (a.g_Rs) {
-      const float* gp = a.g_Rs + (long long)bb * J * 9;
-#pragma unroll
-      for (int t = 0; t < 9; ++t) gGR.a[t] += gp[t];
-    }
-    if (a.g_Rs2) {
-      const float* gp = a.g_Rs2 + (long long)bb * J * 9;
-#pragma unroll
-      for (int t = 0; t < 9; ++t) gGR.a[t] += gp[t];
-    }
-    if (valid && a.g_theta) {
-      if (rotmat) {
-        float* o = a.g_theta + (long long)b * J * 9;
-#pragma unroll
-        for (int t = 0; t < 9; ++t) o[t] = gGR.a[t];
-      } else {
-        st3(a.g_theta + (long long)b * J * 3, rodrigues_vjp(ld3(a.theta + (long long)bb * a.theta_stride), gGR));
-      }
-    }
-    gJ[0] += gGt.x; gJ[1] += gGt.y; gJ[2] += gGt.z;
-    if (valid && a.g_bt) st3(a.g_bt + (long long)b * J * 3, mk3(0.f, 0.f, 0.f));
+    ld_rec(rec, gGR, gGt);
+    const float4 lsacc = reinterpret_cast<const float4*>(rec + 12)[0];
+    const float4 jacc = reinterpret_cast<const float4*>(rec + 12)[1];
+    st_rec(X, gGR, mk3(lsacc.x, lsacc.y, lsacc.z));
+    jr[0] = jacc.x + gGt.x; jr[1] = jacc.y + gGt.y; jr[2] = jacc.z + gGt.z;
   }
   __syncwarp();
-  if (valid) {
-    if (a.g_ls) {
-      float* o = a.g_ls + (long long)b * 3 * J;
-      for (int e = l; e < 3 * J; e += LPS) { int j = e / 3; o[e] = gls[j * 4 + (e - 3 * j)]; }
+  // ---- lane-per-joint epilogue: g_theta, g_logscale, g_betas_trans -----------------------------------------
+  for (int j = l; j < J; j += 32) {
+    m3 gR; f3 gls;
+    ld_rec(X + j * 12, gR, gls);  // gM_j (root: dL/dR_0)
+    if (j > 0 && a.ls) {          // gR = diag(1/s_p) gM diag(s_j); without log-scales both are the identity
+      const float* pi_ = a.ls + (long long)b * a.ls_stride + j * 3;
+      const f3 si = mk3(expf(pi_[0]), expf(pi_[1]), expf(pi_[2]));
+      f3 pin = mk3(1.f, 1.f, 1.f);
+      if (!prop) {
+        const float* pp = a.ls + (long long)b * a.ls_stride + m.parents[j] * 3;
+        pin = mk3(1.0f / expf(pp[0]), 1.0f / expf(pp[1]), 1.0f / expf(pp[2]));
+      }
+      gR.a[0] *= pin.x * si.x; gR.a[1] *= pin.x * si.y; gR.a[2] *= pin.x * si.z;
+      gR.a[3] *= pin.y * si.x; gR.a[4] *= pin.y * si.y; gR.a[5] *= pin.y * si.z;
+      gR.a[6] *= pin.z * si.x; gR.a[7] *= pin.z * si.y; gR.a[8] *= pin.z * si.z;
     }
-    if (a.g_jrest) {
-      float* o = a.g_jrest + (long long)b * 3 * J;
-      for (int e = l; e < 3 * J; e += LPS) { int j = e / 3; o[e] = gJ[j * 4 + (e - 3 * j)]; }
+    if (a.g_Rs) {
+      const float* gp = a.g_Rs + ((long long)b * J + j) * 9;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) gR.a[t] += gp[t];
     }
-  }
-  // ---- g_beta, g_trans (fused mode: this kernel owns the final values) --------------------------
-  if (a.beta_final) {
-    // reduce the per-lane g_trans partials through shared memory (deterministic order)
-    float* red = sm + L.red();
-    red[l * 4 + 0] = gtr.x; red[l * 4 + 1] = gtr.y; red[l * 4 + 2] = gtr.z;
-    __syncwarp();
-    if (valid && a.g_beta) {
-      for (int k = l; k < nb; k += LPS) {
-        float acc = 0.f;
-        for (int t = 0; t < LPS; ++t) acc += accb[t * L.nbp + k];
-        if (a.jrest_mode == 0) {
-          const float* js = m.JS + (long long)k * 3 * J;
-          for (int j = 0; j < J; ++j)
-            acc += js[3 * j] * gJ[j * 4] + js[3 * j + 1] * gJ[j * 4 + 1] + js[3 * j + 2] * gJ[j * 4 + 2];
-        }
-        if (a.gbt_part)
-          for (int t = 0; t < a.ntile; ++t) acc += a.gbt_part[((long long)b * a.ntile + t) * (nb + 3) + k];
-        a.g_beta[(long long)b * nb + k] = acc;
+    if (a.g_Rs2) {
+      const float* gp = a.g_Rs2 + ((long long)b * J + j) * 9;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) gR.a[t] += gp[t];
+    }
+    if (a.g_theta) {
+      if (rotmat) {
+        float* o = a.g_theta + ((long long)b * J + j) * 9;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) o[t] = gR.a[t];
+      } else {
+        st3(a.g_theta + ((long long)b * J + j) * 3, rodrigues_vjp(ld3(a.theta + (long long)b * a.theta_stride + j * 3), gR));
       }
     }
-    if (valid && a.g_trans && l < 3) {
-      float acc = 0.f;
-      for (int t = 0; t < LPS; ++t) acc += red[t * 4 + l];
-      if (a.gbt_part)
-        for (int t = 0; t < a.ntile; ++t) acc += a.gbt_part[((long long)b * a.ntile + t) * (nb + 3) + nb + l];
-      a.g_trans[(long long)b * 3 + l] = acc;
+    if (a.g_ls) st3(a.g_ls + ((long long)b * J + j) * 3, gls);
+    if (a.g_bt) {
+      f3 g = mk3(0.f, 0.f, 0.f);
+      if (j > 0) g = mk3(-rec[j * 20 + 16], rec[j * 20 + 17], -rec[j * 20 + 18]);  // gtl with y flipped back
+      st3(a.g_bt + ((long long)b * J + j) * 3, g);
+    }
+  }
+  if (a.g_jrest) {
+    float* o = a.g_jrest + (long long)b * 3 * J;
+    for (int e = l; e < 3 * J; e += 32) { const int j = e / 3; o[e] = jr[j * 4 + (e - 3 * j)]; }
+  }
+  // ---- g_beta, g_trans (fused mode: this kernel owns the final values) ----------------------------------------
+  if (a.beta_final) {
+    const int ne = nb + 3;
+    float part = 0.f;  // lane k < nb+3: sum over tiles of the skin pass' partial (g_beta_k | g_trans)
+    if (a.gbt_part && l < ne)
+      for (int t = 0; t < a.ntile; ++t) part += a.gbt_part[((long long)b * a.ntile + t) * ne + l];
+    float mine = 0.f;
+    if (a.g_beta) {
+      for (int k = 0; k < nb; ++k) {
+        float s = 0.f;
+        if (a.jrest_mode == 0) {
+          const float* js = m.JS + (long long)k * 3 * J;
+          for (int e = l; e < 3 * J; e += 32) { const int j = e / 3; s = fmaf(js[e], jr[j * 4 + (e - 3 * j)], s); }
+        }
+        if (pairs_mode) s += accb[l * L.nbp + k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (l == k) mine = s;
+      }
+      if (l < nb) a.g_beta[(long long)b * nb + l] = mine + part;
+    }
+    if (a.g_trans) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        gtr.x += __shfl_xor_sync(0xffffffffu, gtr.x, o);
+        gtr.y += __shfl_xor_sync(0xffffffffu, gtr.y, o);
+        gtr.z += __shfl_xor_sync(0xffffffffu, gtr.z, o);
+      }
+      if (l >= nb && l < ne) {
+        const int c = l - nb;
+        a.g_trans[(long long)b * 3 + c] = part + (c == 0 ? gtr.x : (c == 1 ? gtr.y : gtr.z));
+      }
     }
   }
 }

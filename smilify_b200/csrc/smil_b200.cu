@@ -67,8 +67,6 @@ struct ArenaPlan {
   }
 };
 
-inline int pick_lps(int max_width) { return max_width <= 8 ? 8 : (max_width <= 16 ? 16 : 32); }
-
 inline int nbt_of(int nb) {
   static const int vals[] = {1, 2, 3, 4, 5, 6, 8, 10, 13, 16};
   for (int v : vals)
@@ -85,31 +83,23 @@ int set_smem(Kern k, size_t bytes) {
 
 // ---- pose kernel launchers ---------------------------------------------------------------------
 int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_t st) {
-  const int lps = pick_lps(m.max_width);
   PoseSmem L;
   L.J = m.J;
   L.nbp = (std::max(a.nb, 1) + 3) & ~3;
-  L.lps = lps;
-  const int spb = POSE_THREADS / lps;
-  const size_t per = (size_t)(((backward ? L.bwd_floats() : L.fwd_floats()) + 3) & ~3) * sizeof(float);
-  const size_t smem = per * spb;
-  const int grid = (a.B + spb - 1) / spb;
+  const int pairs_mode = backward && a.joints_mode == 1 && a.g_joints && !a.joints_in_skin;
+  const int fl = backward ? L.bwd_floats() + (pairs_mode ? 32 * L.nbp : 0) : L.fwd_floats();
+  const size_t smem = (size_t)((fl + 3) & ~3) * sizeof(float) * POSE_WPB;
+  const int grid = (a.B + POSE_WPB - 1) / POSE_WPB;
   int rc = SMIL_OK;
-  prof_begin(backward ? "pose_bwd_kernel" : "pose_fwd_kernel", st);
-#define SMIL_POSE_CASE(LPS)                                                           \
-  if (lps == LPS) {                                                                   \
-    if (backward) {                                                                   \
-      if ((rc = set_smem(pose_bwd_kernel<LPS>, smem)) != SMIL_OK) return rc;          \
-      pose_bwd_kernel<LPS><<<grid, POSE_THREADS, smem, st>>>(m, a, L);                \
-    } else {                                                                          \
-      if ((rc = set_smem(pose_fwd_kernel<LPS>, smem)) != SMIL_OK) return rc;          \
-      pose_fwd_kernel<LPS><<<grid, POSE_THREADS, smem, st>>>(m, a, L);                \
-    }                                                                                 \
+  if (backward) {
+    if ((rc = set_smem(pose_bwd_kernel, smem)) != SMIL_OK) return rc;
+    prof_begin("pose_bwd_kernel", st);
+    pose_bwd_kernel<<<grid, POSE_THREADS, smem, st>>>(m, a, L, pairs_mode);
+  } else {
+    if ((rc = set_smem(pose_fwd_kernel, smem)) != SMIL_OK) return rc;
+    prof_begin("pose_fwd_kernel", st);
+    pose_fwd_kernel<<<grid, POSE_THREADS, smem, st>>>(m, a, L);
   }
-  SMIL_POSE_CASE(8)
-  SMIL_POSE_CASE(16)
-  SMIL_POSE_CASE(32)
-#undef SMIL_POSE_CASE
   SMIL_LAUNCH_CHECK(backward ? "pose_bwd_kernel" : "pose_fwd_kernel");
   return SMIL_OK;
 }
@@ -345,7 +335,7 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   ap.add(s->it_w, (size_t)d.num_items, &d.it_w);
   ap.add(s->it_first, (size_t)d.num_items, &d.it_first);
   ap.add(s->sb_ptr, d.num_units ? J + 1 : 0, &d.sb_ptr);
-  ap.add(s->sb_slot, (size_t)d.num_units, &d.sb_slot);
+  ap.add(s->unit_slot, (size_t)d.num_units, &d.unit_slot);
 
   void* arena = nullptr;
   cudaError_t e = cudaMalloc(&arena, std::max<size_t>(ap.total, 256));
@@ -545,6 +535,7 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
     pa.joints_mode = p.is_static ? 2 : 1;
     pa.g_beta = g->g_beta; pa.g_trans = g->g_trans;
     pa.beta_final = 1;
+    pa.A_saved = A;
     return launch_pose(m, pa, true, st);
   }
 
@@ -596,6 +587,7 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
   pa.joints_mode = p.is_static ? 2 : 0;
   pa.g_jrest = p.is_static ? nullptr : g_jrest;
   pa.beta_final = 0;
+  pa.A_saved = A;
   if ((rc = launch_pose(m, pa, true, st)) != SMIL_OK) return rc;
   prof_begin("vshaped_grad_kernel", st);
   vshaped_grad_kernel<<<blocks_for(nbv, 256), 256, 0, st>>>(m, B, g_vp, g->g_v_shaped, p.is_static ? nullptr : g_jrest,

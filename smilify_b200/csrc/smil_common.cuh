@@ -74,7 +74,7 @@ struct DevModel {
   const float* vrec;
   const int *unit_bone, *unit_ptr, *unit_tile, *tile_unit_ptr, *warp_unit_ptr, *warp_unit, *it_v;
   const float *it_w, *it_first;
-  const int *sb_ptr, *sb_slot;
+  const int *sb_ptr, *unit_slot;
   // host copies needed by launch logic
   int h_max_units_per_tile;
   void* arena;  // single device allocation that backs every table

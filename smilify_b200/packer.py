@@ -199,7 +199,8 @@ def pack_backward_items(vt, S3, idx, val, nnz_row, J, nB, chunk=BWD_CHUNK, nwarp
     A tile is ``chunk`` consecutive vertices (the unit that is staged through shared memory by
     one bulk copy per sample).  Inside a tile, every bone with at least one item forms a *unit*;
     a unit is processed by one warp and produces one 3x4 partial of g_A written to its own
-    *slot* (no atomics, deterministic).  ``sb_*`` lists, per bone, the slots to add up."""
+    *slot* (no atomics, deterministic).  Slots are numbered bone-major (``unit_slot``), so the
+    slots of bone k are the contiguous range ``sb_ptr[k] .. sb_ptr[k+1]``."""
     V = vt.shape[0]
     ntile = (V + chunk - 1) // chunk
     # floats per vertex record {T, S_0..}: sized (and zero padded) for the kernel instance that
@@ -247,11 +248,13 @@ def pack_backward_items(vt, S3, idx, val, nnz_row, J, nB, chunk=BWD_CHUNK, nwarp
     max_tile_items = int((uptr[tup[1:]] - uptr[tup[:-1]]).max()) if ntile else 0
     ub = np.asarray(unit_bone, dtype=np.int64)
     order = np.argsort(ub, kind="stable")
+    unit_slot = np.empty(nunits, dtype=np.int64)   # slots are numbered bone-major: bone k owns
+    unit_slot[order] = np.arange(nunits)           # slots sb_ptr[k] .. sb_ptr[k+1]
     sb_ptr = np.concatenate([[0], np.cumsum(np.bincount(ub, minlength=J))])
     return dict(
         bwd_chunk=chunk, bwd_ntile=ntile, bwd_warps=nwarps, bwd_rec=rec, vrec=_f32(vrec),
         unit_bone=_i32(unit_bone), unit_ptr=_i32(unit_ptr), unit_tile=_i32(unit_tile),
         tile_unit_ptr=_i32(tile_unit_ptr), warp_unit_ptr=_i32(warp_unit_ptr), warp_unit=_i32(warp_unit),
         it_v=_i32(it_v), it_w=_f32(it_w), it_first=_f32(it_first), nunits=nunits, nitems=len(it_v),
-        sb_ptr=_i32(sb_ptr), sb_slot=_i32(order), bwd_max_tile_items=max_tile_items,
+        sb_ptr=_i32(sb_ptr), unit_slot=_i32(unit_slot), bwd_max_tile_items=max_tile_items,
     )

@@ -147,13 +147,13 @@ def fast_backward(t, beta, theta, trans, ls, bt, propagate, static, fw, g_verts,
             uvec = np.einsum("bki,bk->bi", AkR, g)
             g_beta += w * (uvec @ S_.T)
             wg = w * g
-            slots[:, u, :, :3] += wg[:, :, None] * vp[:, None, :]
-            slots[:, u, :, 3] += wg
+            slots[:, t["unit_slot"][u], :, :3] += wg[:, :, None] * vp[:, None, :]
+            slots[:, t["unit_slot"][u], :, 3] += wg
             g_trans += float(t["it_first"][it]) * g
     gA = np.zeros((B, J, 3, 4))
     for k in range(J):
         for si in range(t["sb_ptr"][k], t["sb_ptr"][k + 1]):
-            gA[:, k] += slots[:, t["sb_slot"][si]]
+            gA[:, k] += slots[:, si]
     g_newJ = None
     if static:
         g_newJ = g_joints
