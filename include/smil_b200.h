@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define SMIL_ABI_VERSION 2
+#define SMIL_ABI_VERSION 3
 
 enum {
   SMIL_OK = 0,
@@ -64,9 +64,9 @@ typedef struct SmilModelDesc {
   int32_t num_pairs;       /* (joint,bone) couplings of the closed-form posed-joint regression */
   int32_t has_static;      /* J_static present */
   int32_t fwd_chunk, fwd_nchunk, v_pad;            /* fused forward pass tiling */
-  int32_t bwd_chunk, bwd_ntile, bwd_warps, bwd_rec;/* fused backward pass tiling */
-  int32_t num_units, num_items;
-  int32_t bwd_max_tile_items;
+  int32_t bwd_chunk, bwd_ntile, bwd_warps, bwd_rec;/* fused backward pass tiling; bwd_rec = floats per item-pair record */
+  int32_t num_units, num_item_pairs;
+  int32_t bwd_max_tile_pairs;
   int32_t fused_ok;        /* K, nB, P within the fused kernels' limits */
   /* dense / generic tables */
   const float* v_template;   /* [V][3] */
@@ -98,17 +98,20 @@ typedef struct SmilModelDesc {
   const float* vconst;       /* [3+3nB][v_pad] */
   const int32_t* ell_idx;    /* [K][v_pad] */
   const float* ell_w;        /* [K][v_pad] */
-  /* fused backward pass (item-major) */
-  const float* vrec;         /* [bwd_ntile*bwd_chunk][bwd_rec] */
+  const int32_t* fwd_pos;    /* [v_pad] vertex (local to its chunk) thread t of the forward pass owns, -1 = none;
+                                vconst / ell_* are in THREAD order (packer.py: bone-sorted, bank-conflict-free) */
+  /* fused backward pass (item-major; an item is one non-zero (vertex, bone, weight) of the skinning matrix) */
+  const float* rec2;         /* [num_item_pairs][bwd_rec] two consecutive items of a unit per record, every constant
+                                as an (item, item+1) pair: T (3 pairs) | S (3*NBT pairs) | weight | first-item flag |
+                                3*local vertex (int bits) | pad; odd units end with a zero-weight twin */
   const int32_t* unit_bone;  /* [num_units] */
-  const int32_t* unit_ptr;   /* [num_units+1] into items */
+  const int32_t* unit_ptr;   /* [num_units+1] into item pairs */
   const int32_t* unit_tile;  /* [num_units] */
   const int32_t* tile_unit_ptr; /* [bwd_ntile+1] */
   const int32_t* warp_unit_ptr; /* [bwd_ntile*bwd_warps+1] */
   const int32_t* warp_unit;  /* [num_units] */
-  const int32_t* it_v;       /* [num_items] vertex index local to the tile */
-  const float* it_w;         /* [num_items] */
-  const float* it_first;     /* [num_items] 1 for a vertex's first item */
+  const int32_t* tjv_ptr;    /* [bwd_ntile+1] vertices of a tile that carry J_regressor entries ... */
+  const int32_t* tjv_v;      /* ... as indices local to the tile */
   const int32_t* sb_ptr;     /* [J+1] bone k owns the g_A partial slots sb_ptr[k] .. sb_ptr[k+1] */
   const int32_t* unit_slot;  /* [num_units] slot a unit's partial is written to (bone-major numbering) */
 } SmilModelDesc;

@@ -11,7 +11,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsmil_b200.so")
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 c_f = C.POINTER(C.c_float)
 c_i = C.POINTER(C.c_int32)
@@ -24,7 +24,7 @@ class SmilModelDesc(C.Structure):
         ("max_width", C.c_int32), ("num_pairs", C.c_int32), ("has_static", C.c_int32),
         ("fwd_chunk", C.c_int32), ("fwd_nchunk", C.c_int32), ("v_pad", C.c_int32),
         ("bwd_chunk", C.c_int32), ("bwd_ntile", C.c_int32), ("bwd_warps", C.c_int32), ("bwd_rec", C.c_int32),
-        ("num_units", C.c_int32), ("num_items", C.c_int32), ("bwd_max_tile_items", C.c_int32), ("fused_ok", C.c_int32),
+        ("num_units", C.c_int32), ("num_item_pairs", C.c_int32), ("bwd_max_tile_pairs", C.c_int32), ("fused_ok", C.c_int32),
         ("v_template", c_f), ("shapedirs", c_f), ("posedirs", c_f), ("J_static", c_f),
         ("skin_idx", c_i), ("skin_w", c_f),
         ("jc_ptr", c_i), ("jc_vid", c_i), ("jc_val", c_f),
@@ -33,9 +33,9 @@ class SmilModelDesc(C.Structure):
         ("JT", c_f), ("JS", c_f), ("jreg_rowsum", c_f),
         ("pj_ptr", c_i), ("pj_bone", c_i), ("pj_joint", c_i), ("pj_c0", c_f), ("pj_cm", c_f),
         ("pb_ptr", c_i), ("pb_pair", c_i),
-        ("vconst", c_f), ("ell_idx", c_i), ("ell_w", c_f),
-        ("vrec", c_f), ("unit_bone", c_i), ("unit_ptr", c_i), ("unit_tile", c_i), ("tile_unit_ptr", c_i),
-        ("warp_unit_ptr", c_i), ("warp_unit", c_i), ("it_v", c_i), ("it_w", c_f), ("it_first", c_f),
+        ("vconst", c_f), ("ell_idx", c_i), ("ell_w", c_f), ("fwd_pos", c_i),
+        ("rec2", c_f), ("unit_bone", c_i), ("unit_ptr", c_i), ("unit_tile", c_i), ("tile_unit_ptr", c_i),
+        ("warp_unit_ptr", c_i), ("warp_unit", c_i), ("tjv_ptr", c_i), ("tjv_v", c_i),
         ("sb_ptr", c_i), ("unit_slot", c_i),
     ]
 
@@ -206,10 +206,10 @@ def _np_ptr(a: np.ndarray, ctype):
 
 
 _DESC_F32 = ("v_template", "shapedirs", "posedirs", "J_static", "skin_w", "jc_val", "jr_val", "JT", "JS", "jreg_rowsum",
-             "pj_c0", "pj_cm", "vconst", "ell_w", "vrec", "it_w", "it_first")
+             "pj_c0", "pj_cm", "vconst", "ell_w", "rec2")
 _DESC_I32 = ("skin_idx", "jc_ptr", "jc_vid", "jr_ptr", "jr_jid", "parents", "order", "level_ptr", "child_ptr",
-             "child_idx", "pj_ptr", "pj_bone", "pj_joint", "pb_ptr", "pb_pair", "ell_idx", "unit_bone", "unit_ptr",
-             "unit_tile", "tile_unit_ptr", "warp_unit_ptr", "warp_unit", "it_v", "sb_ptr", "unit_slot")
+             "child_idx", "pj_ptr", "pj_bone", "pj_joint", "pb_ptr", "pb_pair", "ell_idx", "fwd_pos", "unit_bone", "unit_ptr",
+             "unit_tile", "tile_unit_ptr", "warp_unit_ptr", "warp_unit", "tjv_ptr", "tjv_v", "sb_ptr", "unit_slot")
 
 
 def desc_from_tables(t: dict, device: int):
@@ -224,9 +224,9 @@ def desc_from_tables(t: dict, device: int):
     d.has_static = int(js is not None and js.size > 0)
     d.fwd_chunk, d.fwd_nchunk, d.v_pad = t.get("fwd_chunk", 0), t.get("fwd_nchunk", 0), t.get("Vpad", 0)
     d.bwd_chunk, d.bwd_ntile, d.bwd_warps, d.bwd_rec = (t.get("bwd_chunk", 0), t.get("bwd_ntile", 0),
-                                                        t.get("bwd_warps", 0), t.get("bwd_rec", 0))
-    d.num_units, d.num_items = t.get("nunits", 0), t.get("nitems", 0)
-    d.bwd_max_tile_items = t.get("bwd_max_tile_items", 0)
+                                                        t.get("bwd_warps", 0), t.get("bwd_rec2", 0))
+    d.num_units, d.num_item_pairs = t.get("nunits", 0), t.get("npair_items", 0)
+    d.bwd_max_tile_pairs = t.get("bwd_max_tile_pairs", 0)
     d.fused_ok = int(t.get("fused_ok", False))
     for name in _DESC_F32:
         a = t.get(name)
@@ -234,7 +234,7 @@ def desc_from_tables(t: dict, device: int):
         keep.append(a)
         setattr(d, name, _np_ptr(a, C.c_float))
     for name in _DESC_I32:
-        a = t.get(name)
+        a = t.get("unit_pptr" if name == "unit_ptr" else name)  # the kernels index item PAIRS
         a = np.ascontiguousarray(a, dtype=np.int32) if a is not None else None
         keep.append(a)
         setattr(d, name, _np_ptr(a, C.c_int32))

@@ -52,182 +52,279 @@ __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.
 // =====================================================================================================
 // forward
 // =====================================================================================================
+// Thread = vertex, two samples per pass packed into f32x2 lanes (FFMA2: one issue slot, two samples).
+// The per-vertex constants are loop invariant and live in registers as duplicated (c,c) pairs; what
+// changes per pass -- beta, trans and the bone transforms of the sample pair -- sits in shared memory
+// pair-interleaved, so every LDS delivers (sample b, sample b+1) operands ready for FFMA2.
 constexpr int SKIN_FWD_THREADS = 256;  // == packer.FWD_CHUNK
-constexpr int SKIN_FWD_GMAX = 16;
+constexpr int SKIN_FWD_STAGES = 3;     // output staging ring (each stage: 4 rows = verts/v_shaped of 2 samples)
+constexpr int SKIN_FWD_GPMAX = 16;     // sample pairs per CTA
 
 struct SkinFwdArgs {
-  int B, nb, G;               // G samples per CTA
-  const float* beta;  long long beta_stride;
-  const float* trans; long long trans_stride;   // or null
-  const float* A;             // [B][J][12]
+  int B, nb, GP;              // GP sample pairs per group (one TMA load, GP passes)
+  int blk;                    // floats per pair block of `pp`
+  const float* pp;            // [ceil(B/2)][blk] per-pair parameter blocks written by the pose pass:
+                              //   A2 [J][12][2] | beta2 [NB2max][2] | trans2 [4][2]   (all pair-interleaved)
   float* verts;               // [B][V][3]
   float* v_shaped;            // [B][V][3]
 };
 
 __host__ __device__ inline int skin_fwd_stage_floats(int chunk) { return ((3 * chunk + 4) + 3) & ~3; }
-// beta block padded to a 16-byte multiple: the staging tiles behind it are bulk-store sources
-__host__ __device__ inline int skin_fwd_beta_floats(int G, int NBT) { return (G * NBT + 3) & ~3; }
-__host__ inline size_t skin_fwd_smem_bytes(int G, int J, int NBT, int chunk) {
-  return 16 + (size_t)G * J * 48 + (size_t)skin_fwd_beta_floats(G, NBT) * 4 + (size_t)G * 16 +
-         4ull * skin_fwd_stage_floats(chunk) * 4;
+__host__ __device__ inline int pair_block_floats(int J, int nbt_model) { return 24 * J + 2 * ((nbt_model + 1) & ~1) + 8; }
+__host__ inline size_t skin_fwd_smem_bytes(int GP, int blk, int chunk, bool direct) {
+  return 32 + 2ull * GP * blk * 4 + (direct ? 0 : (size_t)SKIN_FWD_STAGES * 4 * skin_fwd_stage_floats(chunk) * 4);
 }
 
-// Writes one staged tile (n floats starting `phase` floats into `stage`) to global `dst` (+off floats):
-// 16B-aligned body through one bulk store issued by thread 0, <=3-float head and tail with scalar stores.
-__device__ __forceinline__ void store_tile(float* __restrict__ dst, long long off, const float* stage, int phase, int n,
-                                           int tid) {
+template <int K_>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(K_) : "memory");
+}
+
+// One staged row (n floats starting `phase` floats into `stage`) -> global dst[off ..]: the 16-byte
+// aligned body leaves through one bulk store issued by lane 0, the <=3-float head / tail through scalar
+// stores by lanes 1-3 / 4-6 of the same warp.
+__device__ __forceinline__ void store_row(float* __restrict__ dst, long long off, const float* stage, int phase, int n,
+                                          int lane) {
   const int head = min(n, (4 - phase) & 3);
   const int body = ((n - head) >> 2) << 2;
-  if (tid == 0 && body > 0) bulk_s2g(dst + off + head, stage + phase + head, (uint32_t)body * 4u);
-  if (tid >= 32 && tid < 32 + head) dst[off + (tid - 32)] = stage[phase + (tid - 32)];
+  if (lane == 0 && body > 0) bulk_s2g(dst + off + head, stage + phase + head, (uint32_t)body * 4u);
+  if (lane >= 1 && lane < 1 + head) dst[off + (lane - 1)] = stage[phase + (lane - 1)];
   const int tail = n - head - body;
-  if (tid >= 64 && tid < 64 + tail) dst[off + head + body + (tid - 64)] = stage[phase + head + body + (tid - 64)];
+  if (lane >= 4 && lane < 4 + tail) dst[off + head + body + (lane - 4)] = stage[phase + head + body + (lane - 4)];
 }
 
-template <int NBT, int K>
+template <int NBT, int K, bool ALIGNED, bool DIRECT>
 __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, SkinFwdArgs a) {
+  // ALIGNED: 3V % 4 == 0, i.e. every staged row starts and ends on a 16-byte boundary of the output tensors
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int tid = threadIdx.x;
+  constexpr int C = SKIN_FWD_THREADS;
+  constexpr int SF = ((3 * C + 4) + 3) & ~3;
+  constexpr int NB2 = (NBT + 1) & ~1;                // betas per pair block, padded to whole float4s
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int chunk = blockIdx.x;
-  const int b0 = blockIdx.y * a.G;
-  const int Gn = min(a.G, a.B - b0);
-  const int J = m.J, V = m.V, C = SKIN_FWD_THREADS;
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw);
-  float* sA = reinterpret_cast<float*>(smem_raw + 16);
-  float* sBeta = sA + (size_t)a.G * J * 12;
-  float* sTrans = sBeta + skin_fwd_beta_floats(a.G, NBT);
-  float* sStage = sTrans + (size_t)a.G * 4;
-  const int SF = skin_fwd_stage_floats(C);
+  const int J = m.J, V = m.V;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);        // [2]
+  float* sBlk = reinterpret_cast<float*>(smem_raw + 32);          // [2][GP][blk]
+  float* sStage = sBlk + 2ull * a.GP * a.blk;                     // [STAGES][4][SF]
+  const int npairs = (a.B + 1) >> 1;
+  const int ngroups = (npairs + a.GP - 1) / a.GP;
 
   if (tid == 0) {
-    mbar_init(bar, 1);
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
     fence_mbar_init();
   }
   __syncthreads();
-  if (tid == 0) {
-    const uint32_t bytes = (uint32_t)Gn * J * 48u;
-    mbar_expect_tx(bar, bytes);
-    bulk_g2s(sA, a.A + (long long)b0 * J * 12, bytes, bar);
-  }
-  // per-sample scalars of the group
-  for (int i = tid; i < Gn * NBT; i += C) {
-    const int g = i / NBT, k = i - g * NBT;
-    sBeta[i] = (k < a.nb) ? a.beta[(long long)(b0 + g) * a.beta_stride + k] : 0.f;
-  }
-  for (int i = tid; i < Gn * 4; i += C) {
-    const int g = i >> 2, c = i & 3;
-    sTrans[i] = (a.trans && c < 3) ? a.trans[(long long)(b0 + g) * a.trans_stride + c] : 0.f;
-  }
-  // per-vertex constants -> registers (coalesced SoA loads; padded vertices read zeros)
+  auto issue = [&](int grp, int buf) {
+    const int p0 = grp * a.GP;
+    const uint32_t bytes = (uint32_t)min(a.GP, npairs - p0) * (uint32_t)a.blk * 4u;
+    mbar_expect_tx(&bars[buf], bytes);
+    bulk_g2s(sBlk + (size_t)buf * a.GP * a.blk, a.pp + (long long)p0 * a.blk, bytes, &bars[buf]);
+  };
+  if (tid == 0 && (int)blockIdx.y < ngroups) issue(blockIdx.y, 0);
+  // per-vertex constants -> registers as duplicated pairs (coalesced SoA loads; padded vertices read zeros)
   const int v = chunk * C + tid;
-  float T[3], S[NBT][3], w[K];
+  float2 T2[3], S2[NBT][3], w2[K];
   int bo[K];
 #pragma unroll
-  for (int c = 0; c < 3; ++c) T[c] = m.vconst[(long long)c * m.v_pad + v];
+  for (int c = 0; c < 3; ++c) {
+    const float t = m.vconst[(long long)c * m.v_pad + v];
+    T2[c] = make_float2(t, t);
+  }
 #pragma unroll
   for (int k = 0; k < NBT; ++k)
 #pragma unroll
-    for (int c = 0; c < 3; ++c) S[k][c] = (k < m.nB) ? m.vconst[(long long)(3 + 3 * k + c) * m.v_pad + v] : 0.f;
+    for (int c = 0; c < 3; ++c) {
+      const float s = (k < m.nB) ? m.vconst[(long long)(3 + 3 * k + c) * m.v_pad + v] : 0.f;
+      S2[k][c] = make_float2(s, s);
+    }
 #pragma unroll
   for (int k = 0; k < K; ++k) {
-    w[k] = (k < m.K) ? m.ell_w[(long long)k * m.v_pad + v] : 0.f;
-    bo[k] = (k < m.K) ? m.ell_idx[(long long)k * m.v_pad + v] * 12 : 0;
+    const float w = (k < m.K) ? m.ell_w[(long long)k * m.v_pad + v] : 0.f;
+    w2[k] = make_float2(w, w);
+    bo[k] = (k < m.K) ? m.ell_idx[(long long)k * m.v_pad + v] * 24 : 0;
   }
   const int nv = min(C, V - chunk * C);
   const int n = 3 * nv;
-  __syncthreads();
-  mbar_wait(bar, 0);
+  const int pos3 = 3 * m.fwd_pos[v];   // this thread's vertex, local to the chunk (packer: forward_thread_assignment)
+  const bool writer = pos3 >= 0;
+  // row shipping: warp r < 4 owns row r of a stage (0: verts b, 1: verts b+1, 2: v_shaped b, 3: v_shaped b+1)
+  const bool shipper = warp < 4;
+  const bool second = (warp & 1) != 0;
+  float* const ship_dst = (warp < 2) ? a.verts : a.v_shaped;
+  const long long off_step = 6LL * V;
+  const int NB2M = (a.blk - 24 * J - 8) >> 1;   // beta pairs per block (model-level padding)
 
-  for (int g = 0; g < Gn; ++g) {
-    float* stV = sStage + (size_t)((g & 1) * 2 + 0) * SF;
-    float* stS = sStage + (size_t)((g & 1) * 2 + 1) * SF;
-    const long long off = ((long long)(b0 + g) * V + (long long)chunk * C) * 3;
-    const int phase = (int)(off & 3);
-    // shape blend
-    float vs[3] = {T[0], T[1], T[2]};
-    const float* bp = sBeta + g * NBT;
+  int sidx = 0, it = 0;
+  for (int grp = blockIdx.y; grp < ngroups; grp += gridDim.y, ++it) {
+    const int buf = it & 1;
+    __syncthreads();  // every thread is done with the other buffer (group it-1)
+    if (tid == 0 && grp + (int)gridDim.y < ngroups) issue(grp + gridDim.y, buf ^ 1);
+    mbar_wait(&bars[buf], (uint32_t)((it >> 1) & 1));
+    const int p0 = grp * a.GP;
+    const int GPn = min(a.GP, npairs - p0);
+    long long off = ((long long)(2 * p0 + (second ? 1 : 0)) * V + (long long)chunk * C) * 3;   // this warp's row
+    long long offw = ((long long)(2 * p0) * V + (long long)chunk * C) * 3;                      // writer phases
+    const float* blkp = sBlk + (size_t)buf * a.GP * a.blk;
+    for (int g = 0; g < GPn; ++g) {
+      float* st = sStage + sidx * (4 * SF);
+      const float* Ag = blkp;
+      const float4* bp4 = reinterpret_cast<const float4*>(blkp + 24 * J);
+      const float4* tp4 = reinterpret_cast<const float4*>(blkp + 24 * J + 2 * NB2M);
+      // shape blend for both samples
+      float2 vs0 = T2[0], vs1 = T2[1], vs2 = T2[2];
 #pragma unroll
-    for (int k = 0; k < NBT; ++k) {
-      const float bk = bp[k];
-      vs[0] = fmaf(bk, S[k][0], vs[0]); vs[1] = fmaf(bk, S[k][1], vs[1]); vs[2] = fmaf(bk, S[k][2], vs[2]);
-    }
-    // skinning: sum_k w_k (A_k [vs;1])
-    float o[3] = {sTrans[g * 4 + 0], sTrans[g * 4 + 1], sTrans[g * 4 + 2]};
-    const float* Ag = sA + (size_t)g * J * 12;
+      for (int k = 0; k < NB2; k += 2) {
+        const float4 bb = bp4[k >> 1];
+        const float2 bk = make_float2(bb.x, bb.y);
+        vs0 = __ffma2_rn(bk, S2[k][0], vs0); vs1 = __ffma2_rn(bk, S2[k][1], vs1); vs2 = __ffma2_rn(bk, S2[k][2], vs2);
+        if (k + 1 < NBT) {
+          const float2 bl = make_float2(bb.z, bb.w);
+          vs0 = __ffma2_rn(bl, S2[k + 1][0], vs0); vs1 = __ffma2_rn(bl, S2[k + 1][1], vs1);
+          vs2 = __ffma2_rn(bl, S2[k + 1][2], vs2);
+        }
+      }
+      // skinning: sum_k w_k (A_k [vs;1]) + trans
+      const float4 t01 = tp4[0];
+      const float2 t2_ = *reinterpret_cast<const float2*>(tp4 + 1);
+      float2 o0 = make_float2(t01.x, t01.y), o1 = make_float2(t01.z, t01.w), o2 = t2_;
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const float4* Ak = reinterpret_cast<const float4*>(Ag + bo[k]);
-      const float4 r0 = Ak[0], r1 = Ak[1], r2 = Ak[2];
-      o[0] = fmaf(w[k], fmaf(r0.x, vs[0], fmaf(r0.y, vs[1], fmaf(r0.z, vs[2], r0.w))), o[0]);
-      o[1] = fmaf(w[k], fmaf(r1.x, vs[0], fmaf(r1.y, vs[1], fmaf(r1.z, vs[2], r1.w))), o[1]);
-      o[2] = fmaf(w[k], fmaf(r2.x, vs[0], fmaf(r2.y, vs[1], fmaf(r2.z, vs[2], r2.w))), o[2]);
+      for (int k = 0; k < K; ++k) {
+        const float4* Ak = reinterpret_cast<const float4*>(Ag + bo[k]);
+        float4 q;
+        float2 t;
+        q = Ak[1]; t = __ffma2_rn(make_float2(q.x, q.y), vs2, make_float2(q.z, q.w));
+        q = Ak[0]; t = __ffma2_rn(make_float2(q.z, q.w), vs1, t); t = __ffma2_rn(make_float2(q.x, q.y), vs0, t);
+        o0 = __ffma2_rn(w2[k], t, o0);
+        q = Ak[3]; t = __ffma2_rn(make_float2(q.x, q.y), vs2, make_float2(q.z, q.w));
+        q = Ak[2]; t = __ffma2_rn(make_float2(q.z, q.w), vs1, t); t = __ffma2_rn(make_float2(q.x, q.y), vs0, t);
+        o1 = __ffma2_rn(w2[k], t, o1);
+        q = Ak[5]; t = __ffma2_rn(make_float2(q.x, q.y), vs2, make_float2(q.z, q.w));
+        q = Ak[4]; t = __ffma2_rn(make_float2(q.z, q.w), vs1, t); t = __ffma2_rn(make_float2(q.x, q.y), vs0, t);
+        o2 = __ffma2_rn(w2[k], t, o2);
+      }
+      if (DIRECT) {
+        // straight from registers: 12-byte pieces at a 12-byte stride; a warp covers 384 contiguous bytes per tensor row
+        if (writer) {
+          float* d = a.verts + offw + pos3;
+          d[0] = o0.x; d[1] = o1.x; d[2] = o2.x;
+          float* e = a.v_shaped + offw + pos3;
+          e[0] = vs0.x; e[1] = vs1.x; e[2] = vs2.x;
+          if (2 * (p0 + g) + 1 < a.B) {
+            d += 3LL * V; e += 3LL * V;
+            d[0] = o0.y; d[1] = o1.y; d[2] = o2.y;
+            e[0] = vs0.y; e[1] = vs1.y; e[2] = vs2.y;
+          }
+        }
+      } else {
+      if (writer) {
+        float* r = st + pos3;
+        int ph0 = 0, ph1 = 0;
+        if (!ALIGNED) { ph0 = (int)(offw & 3); ph1 = (int)((offw + 3LL * V) & 3); }
+        r[ph0 + 0] = o0.x;  r[ph0 + 1] = o1.x;  r[ph0 + 2] = o2.x;                         // verts, sample b
+        r[SF + ph1 + 0] = o0.y;  r[SF + ph1 + 1] = o1.y;  r[SF + ph1 + 2] = o2.y;          // verts, sample b+1
+        r[2 * SF + ph0 + 0] = vs0.x; r[2 * SF + ph0 + 1] = vs1.x; r[2 * SF + ph0 + 2] = vs2.x;  // v_shaped, b
+        r[3 * SF + ph1 + 0] = vs0.y; r[3 * SF + ph1 + 1] = vs1.y; r[3 * SF + ph1 + 2] = vs2.y;  // v_shaped, b+1
+      }
+      fence_proxy_async();
+      // the stage the NEXT pass writes was last read by the stores of pass (now)+1-STAGES
+      if (shipper && lane == 0) bulk_wait_read<SKIN_FWD_STAGES - 2>();
+      __syncthreads();
+      if (shipper) {
+        if (!second || 2 * (p0 + g) + 1 < a.B) {
+          const float* src = st + warp * SF;
+          if (ALIGNED) {
+            if (lane == 0) bulk_s2g(ship_dst + off, src, (uint32_t)n * 4u);
+          } else {
+            store_row(ship_dst, off, src, (int)(off & 3), n, lane);
+          }
+        }
+        if (lane == 0) bulk_commit();
+      }
+      }
+      off += off_step;
+      offw += off_step;
+      blkp += a.blk;
+      sidx = (sidx + 1 == SKIN_FWD_STAGES) ? 0 : sidx + 1;
     }
-    if (tid < nv) {
-      stV[phase + 3 * tid + 0] = o[0]; stV[phase + 3 * tid + 1] = o[1]; stV[phase + 3 * tid + 2] = o[2];
-      stS[phase + 3 * tid + 0] = vs[0]; stS[phase + 3 * tid + 1] = vs[1]; stS[phase + 3 * tid + 2] = vs[2];
-    }
-    fence_proxy_async();
-    if (tid == 0) bulk_wait_read0();  // stores of sample g-1 have drained their staging buffer
-    __syncthreads();
-    store_tile(a.verts, off, stV, phase, n, tid);
-    store_tile(a.v_shaped, off, stS, phase, n, tid);
-    if (tid == 0) bulk_commit();
   }
-  if (tid == 0) bulk_wait_read0();
+  if (!DIRECT && shipper && lane == 0) bulk_wait_read<0>();
 }
 
 // =====================================================================================================
 // backward
 // =====================================================================================================
+// Item-major, lane = sample (8 samples x 4 item streams per warp), two items per step packed into f32x2
+// lanes: the item-pair records hold every constant as an (item i, item i+1) pair, the per-sample operands
+// (bone rotation, betas) are duplicated into (x,x) register pairs once per unit / group.  All reductions
+// over vertices are private register accumulations; the two halves of a pair and the four streams are
+// folded once per unit.  Before the items are walked, the tile's share of Jreg g_joints is added to the
+// staged g_verts rows (joints = Jreg^T verts, smal_torch.py:348-351), so the posed-joint regression needs
+// no backward of its own.
 constexpr int SKIN_BWD_G = 8;       // samples per warp pass (lane & 7)
-constexpr int SKIN_BWD_STREAMS = 4; // item streams per warp (lane >> 3)
+constexpr int SKIN_BWD_STREAMS = 4; // item-pair streams per warp (lane >> 3)
 
 struct SkinBwdArgs {
   int B, nb;
   int groups_per_cta;        // consecutive sample groups processed by one CTA
-  int max_tile_items;        // smem sizing
+  int max_tile_pairs;        // smem sizing
   const float* beta;  long long beta_stride;
-  const float* A;            // [B][J][12]
+  const float* pp; int blk;  // per-pair parameter blocks of the forward (A2 [J][12][2] first), blk floats each
   const float* g_verts;      // [B][V][3]
+  const float* g_joints;     // [B][J][3] folded into the tile through the joint regressor, or null
+  int max_jv, max_je;        // smem sizing of the tile's joint-regressor slice
   long long total_floats;    // B*V*3
   float* gA_slots;           // [B][num_units][12]
   float* gbt_part;           // [B][ntile][nb+3]
 };
 
+__host__ __device__ inline int skin_bwd_rec_floats(int NBT) { return (6 + 6 * NBT + 8 + 3) & ~3; }
 __host__ __device__ inline int skin_bwd_row_floats(int chunk) {
   int r = 3 * chunk + 4;             // +4: alignment slack for the 16-byte superset load
   return r + ((36 - (r & 31)) & 31);  // == 4 (mod 32): the 8 sample rows of a stream hit distinct banks
 }
-__host__ inline size_t skin_bwd_smem_bytes(int chunk, int rec, int max_items, int NBT) {
-  size_t fl = (size_t)chunk * rec + 2ull * SKIN_BWD_G * skin_bwd_row_floats(chunk) + 3ull * ((max_items + 3) & ~3) +
-              4ull * SKIN_BWD_G * (NBT + 4);
+constexpr int SKIN_BWD_MAXU = 64;   // units per tile the shared descriptor table holds (packer keeps tiles below it)
+__host__ inline size_t skin_bwd_smem_bytes(int chunk, int rec, int max_pairs, int NBT, int J, int max_jv, int max_je) {
+  size_t fl = (size_t)max_pairs * rec + 2ull * SKIN_BWD_G * skin_bwd_row_floats(chunk) + 4ull * SKIN_BWD_G * (NBT + 4) +
+              4ull * SKIN_BWD_MAXU + 2ull * SKIN_BWD_G * ((3 * J + 3) & ~3) + 4ull * ((max_jv + 3) & ~3) +
+              2ull * ((max_je + 3) & ~3);
   return 32 + fl * 4;
 }
+
+__device__ __forceinline__ float2 dup2(float x) { return make_float2(x, x); }
 
 template <int NBT>
 __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
+  constexpr int NQ = (6 + 6 * NBT + 3) / 4;   // float4 loads that cover T and the NBT used shape directions
+  const int REC = m.bwd_rec;                  // record stride and tail offset follow the MODEL's beta count
+  const int TAIL = m.bwd_tail;                // float offset of (w | first | 3*lv) inside a record
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane & (SKIN_BWD_G - 1), st = lane >> 3;
   const int ti = blockIdx.x;
-  const int C = m.bwd_chunk, V = m.V, J = m.J, rec = m.bwd_rec;
+  const int C = m.bwd_chunk, V = m.V, J = m.J;
   const int RF = skin_bwd_row_floats(C);
-  const int MI = (a.max_tile_items + 3) & ~3;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);  // [2]
-  float* sRec = reinterpret_cast<float*>(smem_raw + 32);   // [C][rec]
-  float* sRows = sRec + (size_t)C * rec;                   // [2][G][RF]
-  float* sItW = sRows + 2ull * SKIN_BWD_G * RF;            // [MI]
-  float* sItF = sItW + MI;                                 // [MI]
-  int* sItV = reinterpret_cast<int*>(sItF + MI);           // [MI]
-  float* sRed = reinterpret_cast<float*>(sItV + MI);       // [4 warps][G][NBT+4]
+  float* sRec = reinterpret_cast<float*>(smem_raw + 32);   // [max_pairs][REC]
+  float* sRows = sRec + (size_t)a.max_tile_pairs * REC;    // [2][G][RF]
+  float* sRed = sRows + 2ull * SKIN_BWD_G * RF;            // [4 warps][G][NBT+4]
+  int4* sUnit = reinterpret_cast<int4*>(sRed + 4ull * SKIN_BWD_G * (NBT + 4));   // [MAXU] (bone*24, first pair, end pair, slot)
+  const int GJF = (3 * J + 3) & ~3;
+  float* sGJ = reinterpret_cast<float*>(sUnit + SKIN_BWD_MAXU);                  // [2][G][GJF] g_joints of a group
+  int4* sJV = reinterpret_cast<int4*>(sGJ + 2ull * SKIN_BWD_G * GJF);            // [max_jv] (3*lv, first entry, end entry, -)
+  int2* sJE = reinterpret_cast<int2*>(sJV + ((a.max_jv + 3) & ~3));              // [max_je] (3*joint, weight bits)
 
   const int u_beg = m.tile_unit_ptr[ti], u_end = m.tile_unit_ptr[ti + 1];
-  const int it_base = m.unit_ptr[u_beg], it_cnt = m.unit_ptr[u_end] - it_base;
+  const int pr_base = m.unit_ptr[u_beg], pr_cnt = m.unit_ptr[u_end] - pr_base;
   const int nv = min(C, V - ti * C);
   const int n = 3 * nv;
   const int ngroups = (a.B + SKIN_BWD_G - 1) / SKIN_BWD_G;
   const int grp0 = blockIdx.y * a.groups_per_cta;
   const int grp1 = min(ngroups, grp0 + a.groups_per_cta);
+  const int wu_base = m.warp_unit_ptr[ti * m.bwd_warps];
+  const int wu_beg = m.warp_unit_ptr[ti * m.bwd_warps + warp] - wu_base;
+  const int wu_end = m.warp_unit_ptr[ti * m.bwd_warps + warp + 1] - wu_base;
+  const int jv_beg = m.tjv_ptr[ti], jv_cnt = a.g_joints ? m.tjv_ptr[ti + 1] - jv_beg : 0;
 
   if (tid == 0) {
     mbar_init(&bars[0], 1);
@@ -236,15 +333,44 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
   }
   // tile constants -> shared memory (once per CTA, reused by every sample group)
   {
-    const float4* src = reinterpret_cast<const float4*>(m.vrec + (long long)ti * C * rec);
+    const float4* src = reinterpret_cast<const float4*>(m.rec2 + (long long)pr_base * REC);
     float4* dst = reinterpret_cast<float4*>(sRec);
-    for (int i = tid; i < C * rec / 4; i += 128) dst[i] = src[i];
-    for (int i = tid; i < it_cnt; i += 128) {
-      sItV[i] = m.it_v[it_base + i];
-      sItW[i] = m.it_w[it_base + i];
-      sItF[i] = m.it_first[it_base + i];
+    for (int i = tid; i < pr_cnt * (REC >> 2); i += 128) dst[i] = src[i];
+    for (int i = tid; i < u_end - u_beg; i += 128) {   // unit descriptors in the order the warps walk them
+      const int u = m.warp_unit[wu_base + i];
+      sUnit[i] = make_int4(m.unit_bone[u] * 24, m.unit_ptr[u] - pr_base, m.unit_ptr[u + 1] - pr_base, m.unit_slot[u]);
+    }
+    if (jv_cnt > 0) {   // the tile's slice of the joint regressor (CSR by vertex)
+      const int e_base = m.jr_ptr[ti * C];
+      for (int i = tid; i < jv_cnt; i += 128) {
+        const int lv = m.tjv_v[jv_beg + i], vg = ti * C + lv;
+        sJV[i] = make_int4(3 * lv, m.jr_ptr[vg] - e_base, m.jr_ptr[vg + 1] - e_base, 0);
+      }
+      const int e_cnt = m.jr_ptr[ti * C + nv] - e_base;
+      for (int i = tid; i < e_cnt; i += 128) sJE[i] = make_int2(3 * m.jr_jid[e_base + i], __float_as_int(m.jr_val[e_base + i]));
     }
   }
+  // g_joints of a sample group: coalesced loads into registers one group ahead, parked in shared memory
+  constexpr int GJ_PER = 12;  // floats per thread: 8 samples x 3J <= 128 * 12  (J <= 64)
+  float gj_next[GJ_PER];
+  auto gj_fetch = [&](int grp) {
+    const int b0 = grp * SKIN_BWD_G;
+    const int cnt = min(SKIN_BWD_G, a.B - b0) * 3 * J;
+    const float* src = a.g_joints + (long long)b0 * 3 * J;
+#pragma unroll
+    for (int q = 0; q < GJ_PER; ++q) {
+      const int i = tid + q * 128;
+      gj_next[q] = (i < cnt) ? src[i] : 0.f;
+    }
+  };
+  auto gj_park = [&](int buf) {
+#pragma unroll
+    for (int q = 0; q < GJ_PER; ++q) {
+      const int i = tid + q * 128;
+      if (i < SKIN_BWD_G * 3 * J) sGJ[((size_t)buf * SKIN_BWD_G + i / (3 * J)) * GJF + i % (3 * J)] = gj_next[q];
+    }
+  };
+  if (jv_cnt > 0 && grp0 < grp1) { gj_fetch(grp0); gj_park(0); if (grp0 + 1 < grp1) gj_fetch(grp0 + 1); }
   __syncthreads();
 
   // producer: one bulk copy per sample row (16-byte aligned superset of the tile's float range)
@@ -274,7 +400,14 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
     if (grp0 + 1 < grp1) issue(grp0 + 1, 1);
   }
 
-  const int wu_beg = m.warp_unit_ptr[ti * m.bwd_warps + warp], wu_end = m.warp_unit_ptr[ti * m.bwd_warps + warp + 1];
+  // betas of the group's samples, fetched one group ahead
+  float beta_next[NBT];
+  auto beta_fetch = [&](int grp) {
+    const int bs = min(grp * SKIN_BWD_G + g, a.B - 1);
+#pragma unroll
+    for (int k = 0; k < NBT; ++k) beta_next[k] = (k < a.nb) ? a.beta[(long long)bs * a.beta_stride + k] : 0.f;
+  };
+  if (grp0 < grp1) beta_fetch(grp0);
 
   for (int grp = grp0; grp < grp1; ++grp) {
     const int stage = (grp - grp0) & 1;
@@ -294,78 +427,117 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
         for (long long e = len - 4; e < ph + n; ++e) row[e] = a.g_verts[off - ph + e];
       }
     }
-    __syncthreads();
-
-    float beta[NBT];
-#pragma unroll
-    for (int k = 0; k < NBT; ++k) beta[k] = (k < a.nb) ? a.beta[(long long)bb * a.beta_stride + k] : 0.f;
-    float gb[NBT];
-#pragma unroll
-    for (int k = 0; k < NBT; ++k) gb[k] = 0.f;
-    float gtx = 0.f, gty = 0.f, gtz = 0.f;
-    const long long off = ((long long)bb * V + (long long)ti * C) * 3;
-    const float* row = sRows + ((size_t)stage * SKIN_BWD_G + g) * RF + (int)(off & 3);
-
-    for (int wu = wu_beg; wu < wu_end; ++wu) {
-      const int u = m.warp_unit[wu];
-      const int bone = m.unit_bone[u];
-      const int i0 = m.unit_ptr[u] - it_base, i1 = m.unit_ptr[u + 1] - it_base;
-      const float4* Ak = reinterpret_cast<const float4*>(a.A + ((long long)bb * J + bone) * 12);
-      const float4 r0 = Ak[0], r1 = Ak[1], r2 = Ak[2];
-      float acc[12];
-#pragma unroll
-      for (int q = 0; q < 12; ++q) acc[q] = 0.f;
-      for (int it = i0 + st; it < i1; it += SKIN_BWD_STREAMS) {
-        const int lv = sItV[it];
-        const float w = sItW[it], fw = sItF[it];
-        const float gx = row[3 * lv], gy = row[3 * lv + 1], gz = row[3 * lv + 2];
-        // vertex record {T, S_0.. S_NBT-1} as 16-byte broadcast loads (address is uniform per stream)
-        constexpr int RECV = (3 + 3 * NBT + 3) / 4;
-        float rc[4 * RECV];
-        {
-          const float4* rc4 = reinterpret_cast<const float4*>(sRec + (size_t)lv * rec);
-#pragma unroll
-          for (int q = 0; q < RECV; ++q) {
-            const float4 t4 = rc4[q];
-            rc[4 * q] = t4.x; rc[4 * q + 1] = t4.y; rc[4 * q + 2] = t4.z; rc[4 * q + 3] = t4.w;
-          }
+    if (jv_cnt > 0) {
+      __syncthreads();  // fix-up above visible before rows are modified
+      // g_verts[v] += sum_j Jreg[v,j] g_joints[j]   (thread = (vertex with entries, sample of the group))
+      const float* gjs = sGJ + (size_t)stage * SKIN_BWD_G * GJF;
+      for (int i = tid; i < jv_cnt * SKIN_BWD_G; i += 128) {
+        const int gg = i & (SKIN_BWD_G - 1);
+        const int bs = b0 + gg;
+        if (bs >= a.B) continue;
+        const int4 jv = sJV[i >> 3];
+        const long long off = ((long long)bs * V + (long long)ti * C) * 3;
+        float* p = sRows + ((size_t)stage * SKIN_BWD_G + gg) * RF + (int)(off & 3) + jv.x;
+        float x = p[0], y = p[1], z = p[2];
+        for (int e = jv.y; e < jv.z; ++e) {
+          const int2 je = sJE[e];
+          const float* gj = gjs + gg * GJF + je.x;
+          const float w = __int_as_float(je.y);
+          x = fmaf(w, gj[0], x); y = fmaf(w, gj[1], y); z = fmaf(w, gj[2], z);
         }
-        float vx = rc[0], vy = rc[1], vz = rc[2];
-        // u = A_k.R^T g
-        const float ux = fmaf(r0.x, gx, fmaf(r1.x, gy, r2.x * gz));
-        const float uy = fmaf(r0.y, gx, fmaf(r1.y, gy, r2.y * gz));
-        const float uz = fmaf(r0.z, gx, fmaf(r1.z, gy, r2.z * gz));
-        const float wux = w * ux, wuy = w * uy, wuz = w * uz;
-#pragma unroll
-        for (int k = 0; k < NBT; ++k) {
-          const float sx = rc[3 + 3 * k], sy = rc[4 + 3 * k], sz = rc[5 + 3 * k];
-          vx = fmaf(beta[k], sx, vx); vy = fmaf(beta[k], sy, vy); vz = fmaf(beta[k], sz, vz);
-          gb[k] = fmaf(wux, sx, fmaf(wuy, sy, fmaf(wuz, sz, gb[k])));
-        }
-        const float wx = w * gx, wy = w * gy, wz = w * gz;
-        acc[0] = fmaf(wx, vx, acc[0]); acc[1] = fmaf(wx, vy, acc[1]); acc[2] = fmaf(wx, vz, acc[2]); acc[3] += wx;
-        acc[4] = fmaf(wy, vx, acc[4]); acc[5] = fmaf(wy, vy, acc[5]); acc[6] = fmaf(wy, vz, acc[6]); acc[7] += wy;
-        acc[8] = fmaf(wz, vx, acc[8]); acc[9] = fmaf(wz, vy, acc[9]); acc[10] = fmaf(wz, vz, acc[10]); acc[11] += wz;
-        gtx = fmaf(fw, gx, gtx); gty = fmaf(fw, gy, gty); gtz = fmaf(fw, gz, gtz);
-      }
-#pragma unroll
-      for (int q = 0; q < 12; ++q) {
-        acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], 8);
-        acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], 16);
-      }
-      if (st == 0 && valid) {
-        float4* d = reinterpret_cast<float4*>(a.gA_slots + ((long long)b * m.num_units + m.unit_slot[u]) * 12);
-        d[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-        d[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
-        d[2] = make_float4(acc[8], acc[9], acc[10], acc[11]);
+        p[0] = x; p[1] = y; p[2] = z;
       }
     }
-    // g_beta / g_trans partials of this tile: streams -> warp -> CTA, fixed order
+    __syncthreads();
+
+    float2 beta2[NBT];
+#pragma unroll
+    for (int k = 0; k < NBT; ++k) beta2[k] = dup2(beta_next[k]);
+    if (grp + 1 < grp1) beta_fetch(grp + 1);
+    float2 gb2[NBT];
+#pragma unroll
+    for (int k = 0; k < NBT; ++k) gb2[k] = make_float2(0.f, 0.f);
+    float2 gt0 = make_float2(0.f, 0.f), gt1 = gt0, gt2 = gt0;
+    const long long off = ((long long)bb * V + (long long)ti * C) * 3;
+    const float* row = sRows + ((size_t)stage * SKIN_BWD_G + g) * RF + (int)(off & 3);
+    const float* Ab = a.pp + (long long)(bb >> 1) * a.blk + (bb & 1);
+
+    float rn[9];   // rotation of the NEXT unit's bone for this lane's sample (prefetched under the current unit's items)
+    auto r_fetch = [&](int wu) {
+      const float* Ak = Ab + sUnit[wu].x;
+      rn[0] = Ak[0]; rn[1] = Ak[2]; rn[2] = Ak[4]; rn[3] = Ak[8]; rn[4] = Ak[10]; rn[5] = Ak[12];
+      rn[6] = Ak[16]; rn[7] = Ak[18]; rn[8] = Ak[20];
+    };
+    if (wu_beg < wu_end) r_fetch(wu_beg);
+    for (int wu = wu_beg; wu < wu_end; ++wu) {
+      const int4 ud = sUnit[wu];
+      const int i0 = ud.y, i1 = ud.z;
+      // rotation part of this sample's bone transform, duplicated into (x,x) pairs
+      const float2 r00 = dup2(rn[0]), r01 = dup2(rn[1]), r02 = dup2(rn[2]);
+      const float2 r10 = dup2(rn[3]), r11 = dup2(rn[4]), r12 = dup2(rn[5]);
+      const float2 r20 = dup2(rn[6]), r21 = dup2(rn[7]), r22 = dup2(rn[8]);
+      if (wu + 1 < wu_end) r_fetch(wu + 1);
+      float2 acc[12];
+#pragma unroll
+      for (int q = 0; q < 12; ++q) acc[q] = make_float2(0.f, 0.f);
+      for (int it = i0 + st; it < i1; it += SKIN_BWD_STREAMS) {
+        const float4* rc4 = reinterpret_cast<const float4*>(sRec + (size_t)it * REC);
+        float2 P[2 * NQ];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+          const float4 t4 = rc4[q];
+          P[2 * q] = make_float2(t4.x, t4.y);
+          P[2 * q + 1] = make_float2(t4.z, t4.w);
+        }
+        const float2* tl = reinterpret_cast<const float2*>(sRec + (size_t)it * REC + TAIL);
+        const float2 w2 = tl[0], fw2 = tl[1], lvp = tl[2];
+        const int lv0 = __float_as_int(lvp.x), lv1 = __float_as_int(lvp.y);
+        const float2 gx = make_float2(row[lv0], row[lv1]);
+        const float2 gy = make_float2(row[lv0 + 1], row[lv1 + 1]);
+        const float2 gz = make_float2(row[lv0 + 2], row[lv1 + 2]);
+        const float2 wx = __fmul2_rn(w2, gx), wy = __fmul2_rn(w2, gy), wz = __fmul2_rn(w2, gz);
+        // u = A_k.R^T (w g)
+        const float2 ux = __ffma2_rn(r00, wx, __ffma2_rn(r10, wy, __fmul2_rn(r20, wz)));
+        const float2 uy = __ffma2_rn(r01, wx, __ffma2_rn(r11, wy, __fmul2_rn(r21, wz)));
+        const float2 uz = __ffma2_rn(r02, wx, __ffma2_rn(r12, wy, __fmul2_rn(r22, wz)));
+        float2 vx = P[0], vy = P[1], vz = P[2];
+#pragma unroll
+        for (int k = 0; k < NBT; ++k) {
+          const float2 sx = P[3 + 3 * k], sy = P[4 + 3 * k], sz = P[5 + 3 * k];
+          vx = __ffma2_rn(beta2[k], sx, vx); vy = __ffma2_rn(beta2[k], sy, vy); vz = __ffma2_rn(beta2[k], sz, vz);
+          gb2[k] = __ffma2_rn(ux, sx, __ffma2_rn(uy, sy, __ffma2_rn(uz, sz, gb2[k])));
+        }
+        acc[0] = __ffma2_rn(wx, vx, acc[0]); acc[1] = __ffma2_rn(wx, vy, acc[1]); acc[2] = __ffma2_rn(wx, vz, acc[2]);
+        acc[3] = __fadd2_rn(acc[3], wx);
+        acc[4] = __ffma2_rn(wy, vx, acc[4]); acc[5] = __ffma2_rn(wy, vy, acc[5]); acc[6] = __ffma2_rn(wy, vz, acc[6]);
+        acc[7] = __fadd2_rn(acc[7], wy);
+        acc[8] = __ffma2_rn(wz, vx, acc[8]); acc[9] = __ffma2_rn(wz, vy, acc[9]); acc[10] = __ffma2_rn(wz, vz, acc[10]);
+        acc[11] = __fadd2_rn(acc[11], wz);
+        gt0 = __ffma2_rn(fw2, gx, gt0); gt1 = __ffma2_rn(fw2, gy, gt1); gt2 = __ffma2_rn(fw2, gz, gt2);
+      }
+      float s[12];
+#pragma unroll
+      for (int q = 0; q < 12; ++q) {
+        s[q] = acc[q].x + acc[q].y;
+        s[q] += __shfl_xor_sync(0xffffffffu, s[q], 8);
+        s[q] += __shfl_xor_sync(0xffffffffu, s[q], 16);
+      }
+      if (st == 0 && valid) {
+        float4* d = reinterpret_cast<float4*>(a.gA_slots + ((long long)b * m.num_units + ud.w) * 12);
+        d[0] = make_float4(s[0], s[1], s[2], s[3]);
+        d[1] = make_float4(s[4], s[5], s[6], s[7]);
+        d[2] = make_float4(s[8], s[9], s[10], s[11]);
+      }
+    }
+    // g_beta / g_trans partials of this tile: pair halves -> streams -> warp -> CTA, fixed order
+    float gb[NBT];
 #pragma unroll
     for (int k = 0; k < NBT; ++k) {
+      gb[k] = gb2[k].x + gb2[k].y;
       gb[k] += __shfl_xor_sync(0xffffffffu, gb[k], 8);
       gb[k] += __shfl_xor_sync(0xffffffffu, gb[k], 16);
     }
+    float gtx = gt0.x + gt0.y, gty = gt1.x + gt1.y, gtz = gt2.x + gt2.y;
     gtx += __shfl_xor_sync(0xffffffffu, gtx, 8);  gtx += __shfl_xor_sync(0xffffffffu, gtx, 16);
     gty += __shfl_xor_sync(0xffffffffu, gty, 8);  gty += __shfl_xor_sync(0xffffffffu, gty, 16);
     gtz += __shfl_xor_sync(0xffffffffu, gtz, 8);  gtz += __shfl_xor_sync(0xffffffffu, gtz, 16);
@@ -377,16 +549,20 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
     }
     __syncthreads();  // all warps done with this stage's rows and sRed complete
     if (tid == 0 && grp + 2 < grp1) issue(grp + 2, stage);
+    if (jv_cnt > 0) {
+      if (grp + 1 < grp1) gj_park(stage ^ 1);   // visible to the next group after its first __syncthreads
+      if (grp + 2 < grp1) gj_fetch(grp + 2);
+    }
     {
       const int ne = a.nb + 3;
       for (int i = tid; i < SKIN_BWD_G * ne; i += 128) {
         const int gg = i / ne, e = i - gg * ne;
         const int src = (e < a.nb) ? e : NBT + (e - a.nb);
         if (b0 + gg < a.B) {
-          float s = 0.f;
+          float sum = 0.f;
 #pragma unroll
-          for (int wv = 0; wv < 4; ++wv) s += sRed[((size_t)wv * SKIN_BWD_G + gg) * (NBT + 4) + src];
-          a.gbt_part[((long long)(b0 + gg) * m.bwd_ntile + ti) * ne + e] = s;
+          for (int wv = 0; wv < 4; ++wv) sum += sRed[((size_t)wv * SKIN_BWD_G + gg) * (NBT + 4) + src];
+          a.gbt_part[((long long)(b0 + gg) * m.bwd_ntile + ti) * ne + e] = sum;
         }
       }
     }

@@ -85,6 +85,16 @@ __global__ void lbs_fwd_kernel(DevModel m, int B, const float* __restrict__ A, c
   verts[i * 3] = ox; verts[i * 3 + 1] = oy; verts[i * 3 + 2] = oz;
 }
 
+// A[b][j][e] = pp[b/2][(j*12+e)*2 + b%2]: the fused forward saves the bone transforms pair-interleaved; the unfused
+// backward (taken when the call carries an upstream gradient on v_shaped) wants them plain.
+__global__ void deinterleave_A_kernel(int B, int J, int blk, const float* __restrict__ pp, float* __restrict__ A) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long per = 12LL * J;
+  if (i >= (long long)B * per) return;
+  const long long b = i / per, e = i - b * per;
+  A[i] = pp[(b >> 1) * blk + 2 * e + (b & 1)];
+}
+
 // ---- backward -------------------------------------------------------------------------------------
 // g = g_verts[b,v] (+ sum_e jr_val * g_joints[b, jr_jid]);  g_vp = sum_k w A_k.R^T g;
 // gA[b,k] += w g (x) [v_posed;1]  (atomics);  g_trans[b] += g (atomics, block-reduced first)

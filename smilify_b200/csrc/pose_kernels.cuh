@@ -38,10 +38,14 @@ struct PoseArgs {
   // forward outputs
   float* Rs;      // [B][J][9] or null
   float* A;       // [B][J][12] (3x4 row-major) or null
+  float* pp;      // [ceil(B/2)][pp_blk] per-pair parameter blocks for the fused skinning passes, or null:
+                  //   A2 [J][12][2] | beta2 [NB2][2] | trans2 [4][2], every entry interleaved (sample 2p, sample 2p+1)
+  int pp_blk;     // floats per block (fused_kernels.cuh::pair_block_floats)
   float* newJ;    // [B][J][3] or null
   float* joints;  // [B][J][3] or null
   // backward inputs
   const float* A_saved;   // [B][J][12] written by the forward (its 3x3 part is the global rotation) or null
+  const float* pp_saved;  // the pair blocks the forward wrote (A2 part is read) or null
   const float* gA_dense;  // [B][J][12] or null
   const float* gA_slots;  // [B][nslots][12] or null; the slots of bone k are sb_ptr[k] .. sb_ptr[k+1]
   int nslots;
@@ -200,8 +204,9 @@ __device__ __forceinline__ void warp_copy4(float* dst, const float* src, int n, 
 __global__ void __launch_bounds__(POSE_THREADS) pose_fwd_kernel(DevModel m, PoseArgs a, PoseSmem L) {
   extern __shared__ __align__(16) float smem_pose[];
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  const int b = blockIdx.x * POSE_WPB + w;
-  if (b >= a.B) return;  // whole warp; only __syncwarp() below
+  const int b_raw = blockIdx.x * POSE_WPB + w;
+  const bool live = b_raw < a.B;           // an odd batch leaves the last CTA's second warp without a sample:
+  const int b = live ? b_raw : a.B - 1;    // it recomputes the last one and writes nothing per-sample
   const int J = m.J;
   float* sm = smem_pose + (size_t)w * ((L.fwd_floats() + 3) & ~3);
   float* X = sm + L.x();
@@ -211,7 +216,7 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_fwd_kernel(DevModel m, Pose
   float* sc = sm + L.scale();
   pose_local_state(m, a, X, jr, sbeta, /*stage=*/G, sc, b, l);
   // Rs output from the packed staging copy (a sample's 9J floats are 16-byte aligned only if 9J % 4 == 0)
-  if (a.Rs) {
+  if (a.Rs && live) {
     float* out = a.Rs + (long long)b * 9 * J;
     if (((9 * J) & 3) == 0) warp_copy4(out, G, 9 * J, l);
     else for (int e = l; e < 9 * J; e += 32) out[e] = G[e];
@@ -226,7 +231,29 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_fwd_kernel(DevModel m, Pose
     st_rec(X + j * 12, GR, mk3(Gt.x - rot.x, Gt.y - rot.y, Gt.z - rot.z));
   }
   __syncwarp();
-  if (a.A) warp_copy4(a.A + (long long)b * 12 * J, X, 12 * J, l);
+  if (a.A && live) warp_copy4(a.A + (long long)b * 12 * J, X, 12 * J, l);
+  if (a.pp) {
+    // both samples of the CTA's pair, interleaved element by element: (X0[e], X1[e], X0[e+1], X1[e+1]) per float4
+    static_assert(POSE_WPB == 2, "a CTA is one sample pair");
+    __syncthreads();
+    const int wstride = (L.fwd_floats() + 3) & ~3;
+    const float* X0 = smem_pose + L.x();
+    const float* X1 = smem_pose + wstride + L.x();
+    float* blk = a.pp + (long long)blockIdx.x * a.pp_blk;
+    float4* out = reinterpret_cast<float4*>(blk);
+    for (int i = threadIdx.x; i < 6 * J; i += POSE_THREADS) out[i] = make_float4(X0[2 * i], X1[2 * i], X0[2 * i + 1], X1[2 * i + 1]);
+    const int nb2 = (a.pp_blk - 24 * J - 8) >> 1;
+    for (int i = threadIdx.x; i < 2 * nb2; i += POSE_THREADS) {
+      const int k = i >> 1, h = i & 1;
+      blk[24 * J + i] = (k < a.nb) ? smem_pose[h * wstride + L.beta() + k] : 0.f;
+    }
+    for (int i = threadIdx.x; i < 8; i += POSE_THREADS) {
+      const int c = i >> 1, h = i & 1;
+      const int bs = min(blockIdx.x * 2 + h, a.B - 1);
+      blk[24 * J + 2 * nb2 + i] = (a.trans && c < 3) ? a.trans[(long long)bs * a.trans_stride + c] : 0.f;
+    }
+  }
+  if (!live) return;
   if (a.newJ || (a.joints && a.joints_mode == 2)) {
     for (int e = l; e < 3 * J; e += 32) {
       const int j = e / 3, c = e - 3 * j;
@@ -291,6 +318,10 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
   pose_local_state(m, a, X, jr, sbeta, /*stage=*/G, /*sc=*/rec, b, l);
   if (a.A_saved) {
     warp_copy4(G, a.A_saved + (long long)b * 12 * J, 12 * J, l);  // (GR | At): only GR is used below
+    __syncwarp();
+  } else if (a.pp_saved) {
+    const float* src = a.pp_saved + (long long)(b >> 1) * a.pp_blk + (b & 1);
+    for (int e = l; e < 12 * J; e += 32) G[e] = src[2 * e];
     __syncwarp();
   } else {
     pose_walk(m, X, G, l);

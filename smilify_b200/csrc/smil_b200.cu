@@ -1,6 +1,7 @@
 // C-ABI entry points of the B200-native SMAL/SMIL hot path (see include/smil_b200.h).
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -shared -Xcompiler -fPIC
 #include <atomic>
+#include <cstdlib>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -23,6 +24,9 @@ namespace {
 struct ProfSlot { const char* name; cudaEvent_t beg, end; };
 std::atomic<long long> g_launches{0};
 std::atomic<int> g_prof_on{0};
+int g_fwd_gp = 0;   // tuning override (SMIL_FWD_GP): sample pairs per TMA group of the fused forward pass
+int g_fwd_direct = 0;  // tuning override (SMIL_FWD_DIRECT): register -> global stores instead of the TMA staging ring
+int g_fwd_cps = 0;  // tuning override (SMIL_FWD_CPS): resident CTAs per SM the forward grid is sized for
 std::mutex g_prof_mu;
 std::vector<ProfSlot> g_prof_slots;   // event pairs, created by smil_profile_enable
 size_t g_prof_used = 0;
@@ -105,16 +109,33 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
 }
 
 // ---- fused skin launchers ----------------------------------------------------------------------
-template <int NBT, int K>
-int launch_skin_fwd_inst(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
-  const size_t smem = skin_fwd_smem_bytes(a.G, m.J, NBT, SKIN_FWD_THREADS);
-  int rc = set_smem(skin_fwd_kernel<NBT, K>, smem);
+template <int NBT, int K, bool ALIGNED, bool DIRECT>
+int launch_skin_fwd_inst2(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
+  const size_t smem = skin_fwd_smem_bytes(a.GP, a.blk, SKIN_FWD_THREADS, DIRECT);
+  int rc = set_smem(skin_fwd_kernel<NBT, K, ALIGNED, DIRECT>, smem);
   if (rc != SMIL_OK) return rc;
-  dim3 grid(m.fwd_nchunk, (a.B + a.G - 1) / a.G);
+  // persistent CTAs: as many per vertex chunk as fit the machine in one wave; each walks its share of the pair groups
+  static thread_local size_t occ_smem = 0;
+  static thread_local int occ = 0;
+  if (occ_smem != smem) {
+    SMIL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, skin_fwd_kernel<NBT, K, ALIGNED, DIRECT>, SKIN_FWD_THREADS, smem));
+    occ_smem = smem;
+  }
+  const int ngroups = ((a.B + 1) / 2 + a.GP - 1) / a.GP;
+  const int cps = g_fwd_cps > 0 ? std::min(g_fwd_cps, std::max(occ, 1)) : std::max(occ, 1);
+  const int Y = std::max(1, std::min(ngroups, (m.sm_count * cps) / std::max(m.fwd_nchunk, 1)));
+  dim3 grid(m.fwd_nchunk, Y);
   prof_begin("skin_fwd_kernel", st);
-  skin_fwd_kernel<NBT, K><<<grid, SKIN_FWD_THREADS, smem, st>>>(m, a);
+  skin_fwd_kernel<NBT, K, ALIGNED, DIRECT><<<grid, SKIN_FWD_THREADS, smem, st>>>(m, a);
   SMIL_LAUNCH_CHECK("skin_fwd_kernel");
   return SMIL_OK;
+}
+template <int NBT, int K>
+int launch_skin_fwd_inst(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
+  // rows are 16-byte aligned in the output tensors iff 3V % 4 == 0 (chunks are 256 vertices = 3072 bytes)
+  if (g_fwd_direct) return launch_skin_fwd_inst2<NBT, K, false, true>(m, a, st);
+  if ((3 * m.V) % 4 == 0) return launch_skin_fwd_inst2<NBT, K, true, false>(m, a, st);
+  return launch_skin_fwd_inst2<NBT, K, false, false>(m, a, st);
 }
 template <int NBT>
 int launch_skin_fwd_k(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
@@ -140,7 +161,7 @@ int launch_skin_fwd(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
 
 template <int NBT>
 int launch_skin_bwd_inst(const DevModel& m, const SkinBwdArgs& a, cudaStream_t st) {
-  const size_t smem = skin_bwd_smem_bytes(m.bwd_chunk, m.bwd_rec, a.max_tile_items, NBT);
+  const size_t smem = skin_bwd_smem_bytes(m.bwd_chunk, m.bwd_rec, a.max_tile_pairs, NBT, m.J, a.max_jv, a.max_je);
   int rc = set_smem(skin_bwd_kernel<NBT>, smem);
   if (rc != SMIL_OK) return rc;
   const int ngroups = (a.B + SKIN_BWD_G - 1) / SKIN_BWD_G;
@@ -193,7 +214,12 @@ int make_plan(const DevModel& m, const SmilFwdArgs& f, Plan* p) {
   return SMIL_OK;
 }
 
-size_t saved_bytes_for(const DevModel& m, int B) { return align_up((size_t)B * m.J * 12 * 4, 256) + (size_t)B * m.J * 3 * 4; }
+// saved = bone transforms (fused path: pair-interleaved, ceil(B/2) pairs; generic path: [B][J][12]) + rest joints
+int pair_blk(const DevModel& m) { return pair_block_floats(m.J, std::max(nbt_of(m.nB), 1)); }
+size_t saved_A_bytes(const DevModel& m, int B) {
+  return align_up((size_t)((B + 1) / 2) * std::max(pair_blk(m), 24 * m.J) * 4, 256);
+}
+size_t saved_bytes_for(const DevModel& m, int B) { return saved_A_bytes(m, B) + (size_t)B * m.J * 3 * 4; }
 
 PoseArgs base_pose_args(const DevModel& m, const SmilFwdArgs& f, const Plan& p) {
   PoseArgs a;
@@ -284,12 +310,24 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   d.has_static = s->has_static && s->J_static;
   d.fwd_chunk = s->fwd_chunk; d.fwd_nchunk = s->fwd_nchunk; d.v_pad = s->v_pad;
   d.bwd_chunk = s->bwd_chunk; d.bwd_ntile = s->bwd_ntile; d.bwd_warps = s->bwd_warps; d.bwd_rec = s->bwd_rec;
-  d.num_units = s->num_units; d.num_items = s->num_items;
-  d.h_max_units_per_tile = s->bwd_max_tile_items;
+  d.num_units = s->num_units; d.num_item_pairs = s->num_item_pairs;
+  d.h_max_tile_pairs = s->bwd_max_tile_pairs;
+  d.bwd_tail = 6 + 6 * std::max(nbt_of(d.nB), 1);
+  d.h_max_jv = d.h_max_je = d.h_max_tile_units = 0;
+  if (s->tjv_ptr && s->jr_ptr && s->tile_unit_ptr && s->bwd_chunk > 0)
+    for (int t = 0; t < s->bwd_ntile; ++t) {
+      const int v0 = t * s->bwd_chunk, v1 = std::min(s->num_verts, v0 + s->bwd_chunk);
+      d.h_max_jv = std::max(d.h_max_jv, s->tjv_ptr[t + 1] - s->tjv_ptr[t]);
+      d.h_max_je = std::max(d.h_max_je, s->jr_ptr[v1] - s->jr_ptr[v0]);
+      d.h_max_tile_units = std::max(d.h_max_tile_units, s->tile_unit_ptr[t + 1] - s->tile_unit_ptr[t]);
+    }
   d.fused_ok = s->fused_ok && d.V > 0 && s->fwd_chunk == SKIN_FWD_THREADS && s->bwd_warps == 4 && d.K <= 4 &&
                nbt_of(d.nB) > 0 && d.P == 0 && (s->bwd_chunk % 32) == 0 &&
-               s->bwd_rec >= 4 * ((3 + 3 * nbt_of(d.nB) + 3) / 4);
+               s->bwd_rec == skin_bwd_rec_floats(nbt_of(d.nB)) && d.J <= 64 && d.h_max_tile_units <= SKIN_BWD_MAXU;
   d.device = s->device;
+  if (const char* e = getenv("SMIL_FWD_GP")) g_fwd_gp = atoi(e);
+  if (const char* e = getenv("SMIL_FWD_CPS")) g_fwd_cps = atoi(e);
+  if (const char* e = getenv("SMIL_FWD_DIRECT")) g_fwd_direct = atoi(e);
   SMIL_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, s->device));
 
   const size_t V = d.V, J = d.J, nB = d.nB, K = d.K, np = std::max(d.npairs, 1);
@@ -324,16 +362,16 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   ap.add(s->vconst, (3 + 3 * nB) * (size_t)d.v_pad, &d.vconst);
   ap.add(s->ell_idx, K * (size_t)d.v_pad, &d.ell_idx);
   ap.add(s->ell_w, K * (size_t)d.v_pad, &d.ell_w);
-  ap.add(s->vrec, (size_t)d.bwd_ntile * d.bwd_chunk * d.bwd_rec, &d.vrec);
+  ap.add(s->fwd_pos, (size_t)d.v_pad, &d.fwd_pos);
+  ap.add(s->rec2, (size_t)d.num_item_pairs * d.bwd_rec, &d.rec2);
   ap.add(s->unit_bone, (size_t)d.num_units, &d.unit_bone);
   ap.add(s->unit_ptr, d.num_units ? (size_t)d.num_units + 1 : 0, &d.unit_ptr);
   ap.add(s->unit_tile, (size_t)d.num_units, &d.unit_tile);
   ap.add(s->tile_unit_ptr, d.num_units ? (size_t)d.bwd_ntile + 1 : 0, &d.tile_unit_ptr);
   ap.add(s->warp_unit_ptr, d.num_units ? (size_t)d.bwd_ntile * d.bwd_warps + 1 : 0, &d.warp_unit_ptr);
   ap.add(s->warp_unit, (size_t)d.num_units, &d.warp_unit);
-  ap.add(s->it_v, (size_t)d.num_items, &d.it_v);
-  ap.add(s->it_w, (size_t)d.num_items, &d.it_w);
-  ap.add(s->it_first, (size_t)d.num_items, &d.it_first);
+  ap.add(s->tjv_ptr, d.num_units ? (size_t)d.bwd_ntile + 1 : 0, &d.tjv_ptr);
+  ap.add(s->tjv_v, d.num_units ? (size_t)std::max(d.jreg_nnz, 1) : 0, &d.tjv_v);
   ap.add(s->sb_ptr, d.num_units ? J + 1 : 0, &d.sb_ptr);
   ap.add(s->unit_slot, (size_t)d.num_units, &d.unit_slot);
 
@@ -398,7 +436,7 @@ size_t smil_bwd_scratch_bytes(const SmilModel* model, const SmilBwdArgs* g) {
   const size_t vb = align_up(B * m.V * 3 * 4, 256);
   const size_t fused = align_up(B * std::max(m.num_units, 1) * 48, 256) +
                        align_up(B * std::max(m.bwd_ntile, 1) * (m.nB + 3) * 4, 256);
-  const size_t generic = 3 * vb + align_up(B * m.J * 48, 256) + align_up(B * m.J * 36, 256) +
+  const size_t generic = 3 * vb + 2 * align_up(B * m.J * 48, 256) + align_up(B * m.J * 36, 256) +
                          align_up(B * m.J * 12, 256) + align_up(B * 12, 256);
   return std::max(fused, generic) + 256;
 }
@@ -418,11 +456,13 @@ int smil_forward(const SmilModel* model, const SmilFwdArgs* f, void* stream) {
   if (((uintptr_t)f->verts | (uintptr_t)f->v_shaped | (uintptr_t)f->saved) & 15)
     return fail(SMIL_EINVAL, "verts, v_shaped and saved must be 16-byte aligned");
   float* A = static_cast<float*>(f->saved);
-  float* jrest = reinterpret_cast<float*>(static_cast<char*>(f->saved) + align_up((size_t)B * m.J * 48, 256));
+  float* jrest = reinterpret_cast<float*>(static_cast<char*>(f->saved) + saved_A_bytes(m, B));
 
   PoseArgs pa = base_pose_args(m, *f, p);
   pa.Rs = p.rotmat ? nullptr : f->Rs;
-  pa.A = A;
+  pa.A = p.fused ? nullptr : A;
+  pa.pp = p.fused ? A : nullptr;
+  pa.pp_blk = pair_blk(m);
   pa.newJ = f->J_transformed;
   pa.joints = f->joints;
 
@@ -432,12 +472,9 @@ int smil_forward(const SmilModel* model, const SmilFwdArgs* f, void* stream) {
     if (!p.joints_only) {
       SkinFwdArgs sa;
       sa.B = B; sa.nb = f->num_betas_used;
-      const long long ctas_wanted = 4LL * m.sm_count * 4;
-      long long G = ((long long)B * m.fwd_nchunk) / ctas_wanted;
-      sa.G = (int)std::min<long long>(SKIN_FWD_GMAX, std::max<long long>(1, G));
-      sa.beta = f->beta; sa.beta_stride = f->beta_stride;
-      sa.trans = f->trans; sa.trans_stride = f->trans_stride;
-      sa.A = A; sa.verts = f->verts; sa.v_shaped = f->v_shaped;
+      sa.GP = g_fwd_gp > 0 ? std::min(g_fwd_gp, SKIN_FWD_GPMAX) : 4;
+      sa.blk = pair_blk(m);
+      sa.pp = A; sa.verts = f->verts; sa.v_shaped = f->v_shaped;
       if ((rc = launch_skin_fwd(m, sa, st)) != SMIL_OK) return rc;
     }
     return SMIL_OK;
@@ -501,7 +538,7 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
   if (!f->saved || f->saved_bytes < saved_bytes_for(m, B)) return fail(SMIL_ENOMEM, "saved buffer too small");
   if (!g->scratch || g->scratch_bytes < smil_bwd_scratch_bytes(model, g)) return fail(SMIL_ENOMEM, "backward scratch too small");
   const float* A = static_cast<const float*>(f->saved);
-  const float* jrest = reinterpret_cast<const float*>(static_cast<const char*>(f->saved) + align_up((size_t)B * m.J * 48, 256));
+  const float* jrest = reinterpret_cast<const float*>(static_cast<const char*>(f->saved) + saved_A_bytes(m, B));
   char* sc = static_cast<char*>(g->scratch);
   const bool fused = p.fused && !g->g_v_shaped && !g->g_del_v;
 
@@ -523,19 +560,22 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
       const int ngroups = (B + SKIN_BWD_G - 1) / SKIN_BWD_G;
       long long gpc = ((long long)ngroups * m.bwd_ntile) / (6LL * m.sm_count);
       sa.groups_per_cta = (int)std::min<long long>(32, std::max<long long>(1, gpc));
-      sa.max_tile_items = m.h_max_units_per_tile;
+      sa.max_tile_pairs = m.h_max_tile_pairs;
       sa.beta = f->beta; sa.beta_stride = f->beta_stride;
-      sa.A = A; sa.g_verts = g->g_verts;
+      sa.pp = A; sa.blk = pair_blk(m); sa.g_verts = g->g_verts;
+      sa.g_joints = p.is_static ? nullptr : g->g_joints;
+      sa.max_jv = m.h_max_jv; sa.max_je = m.h_max_je;
       sa.total_floats = (long long)B * m.V * 3;
       sa.gA_slots = slots; sa.gbt_part = part;
       if ((rc = launch_skin_bwd(m, sa, st)) != SMIL_OK) return rc;
       pa.gA_slots = slots; pa.nslots = m.num_units;
       pa.gbt_part = part; pa.ntile = m.bwd_ntile;
+      pa.joints_in_skin = 1;  // the skin pass folded Jreg g_joints into its g_verts tiles
     }
     pa.joints_mode = p.is_static ? 2 : 1;
     pa.g_beta = g->g_beta; pa.g_trans = g->g_trans;
     pa.beta_final = 1;
-    pa.A_saved = A;
+    pa.pp_saved = A; pa.pp_blk = pair_blk(m);
     return launch_pose(m, pa, true, st);
   }
 
@@ -555,8 +595,15 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
   float* gA = reinterpret_cast<float*>(sc + 3 * vb);
   float* gRs2 = reinterpret_cast<float*>(reinterpret_cast<char*>(gA) + align_up((size_t)B * m.J * 48, 256));
   float* g_jrest = reinterpret_cast<float*>(reinterpret_cast<char*>(gRs2) + align_up((size_t)B * m.J * 36, 256));
-  float* g_trans = g->g_trans ? g->g_trans
-                              : reinterpret_cast<float*>(reinterpret_cast<char*>(g_jrest) + align_up((size_t)B * m.J * 12, 256));
+  float* g_trans_scr = reinterpret_cast<float*>(reinterpret_cast<char*>(g_jrest) + align_up((size_t)B * m.J * 12, 256));
+  float* g_trans = g->g_trans ? g->g_trans : g_trans_scr;
+  if (p.fused) {  // the forward of this call was fused and saved the transforms pair-interleaved
+    float* A_plain = reinterpret_cast<float*>(reinterpret_cast<char*>(g_trans_scr) + align_up((size_t)B * 12, 256));
+    prof_begin("deinterleave_A_kernel", st);
+    deinterleave_A_kernel<<<blocks_for((long long)B * m.J * 12, 256), 256, 0, st>>>(B, m.J, pair_blk(m), A, A_plain);
+    SMIL_LAUNCH_CHECK("deinterleave_A_kernel");
+    A = A_plain;
+  }
   const long long nbv = (long long)B * m.V;
   const float* v_posed = v_shaped;
   const float* Rs = p.rotmat ? f->theta : f->Rs;

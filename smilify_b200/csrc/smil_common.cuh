@@ -49,7 +49,7 @@ struct DevModel {
   int V, J, nB, P, K;
   int jreg_nnz, num_levels, max_width, npairs, has_static;
   int fwd_chunk, fwd_nchunk, v_pad;
-  int bwd_chunk, bwd_ntile, bwd_warps, bwd_rec, num_units, num_items;
+  int bwd_chunk, bwd_ntile, bwd_warps, bwd_rec, bwd_tail, num_units, num_item_pairs;
   int fused_ok;
   int device;
   int sm_count;
@@ -71,12 +71,12 @@ struct DevModel {
   const float* vconst;
   const int* ell_idx;
   const float* ell_w;
-  const float* vrec;
-  const int *unit_bone, *unit_ptr, *unit_tile, *tile_unit_ptr, *warp_unit_ptr, *warp_unit, *it_v;
-  const float *it_w, *it_first;
+  const int* fwd_pos;
+  const float* rec2;
+  const int *unit_bone, *unit_ptr, *unit_tile, *tile_unit_ptr, *warp_unit_ptr, *warp_unit, *tjv_ptr, *tjv_v;
   const int *sb_ptr, *unit_slot;
   // host copies needed by launch logic
-  int h_max_units_per_tile;
+  int h_max_tile_pairs, h_max_jv, h_max_je, h_max_tile_units;
   void* arena;  // single device allocation that backs every table
 };
 

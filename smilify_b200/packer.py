@@ -176,21 +176,125 @@ def pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J
     # ---- fused forward skinning pass: per-vertex constants, SoA over a padded vertex axis -----
     nchunk = (V + FWD_CHUNK - 1) // FWD_CHUNK
     Vpad = nchunk * FWD_CHUNK
+    fwd_pos, owner = forward_thread_assignment(idx, val, nnz_row, V, FWD_CHUNK)
+    has = owner >= 0
     nconst = 3 + 3 * nB
     vconst = np.zeros((nconst, Vpad), dtype=np.float32)
-    vconst[:3, :V] = vt.T
-    vconst[3:, :V] = S3.transpose(0, 2, 1).reshape(3 * nB, V)      # row 3+3m+c = S_m[:,c]
+    vconst[:3, has] = vt.T[:, owner[has]]
+    vconst[3:, has] = S3.transpose(0, 2, 1).reshape(3 * nB, V)[:, owner[has]]      # row 3+3m+c = S_m[:,c]
     ell_i = np.zeros((K, Vpad), dtype=np.int32)
     ell_w = np.zeros((K, Vpad), dtype=np.float32)
-    ell_i[:, :V] = idx.T
-    ell_w[:, :V] = val.T
+    ell_i[:, has] = idx.T[:, owner[has]]
+    ell_w[:, has] = val.T[:, owner[has]]
+    # an empty skinning slot may name any bone (its weight is 0): name the vertex' first bone, so that the
+    # slot's shared-memory read hits an address the warp already touches
+    for k in range(1, K):
+        empty = has & (ell_w[k] == 0)
+        ell_i[k, empty] = ell_i[0, empty]
     t.update(fwd_chunk=FWD_CHUNK, fwd_nchunk=nchunk, Vpad=Vpad, vconst=_f32(vconst), ell_idx=_i32(ell_i),
-             ell_w=_f32(ell_w))
+             ell_w=_f32(ell_w), fwd_pos=_i32(fwd_pos))
 
     # ---- fused backward pass: item-major tables ------------------------------------------------
     t.update(pack_backward_items(vt, S3, idx, val, nnz_row, J, nB))
+    # vertices of every backward tile that carry joint-regressor entries (the backward folds
+    # Jreg g_joints into the staged g_verts tile: joints = Jreg^T verts, smal_torch.py:348-351)
+    nt = t["bwd_ntile"]
+    has_j = np.diff(t["jr_ptr"]) > 0
+    tjv_ptr, tjv_v = [0], []
+    for ti in range(nt):
+        v0, v1 = ti * BWD_CHUNK, min(V, (ti + 1) * BWD_CHUNK)
+        tjv_v.extend((np.nonzero(has_j[v0:v1])[0]).tolist())
+        tjv_ptr.append(len(tjv_v))
+    t["tjv_ptr"] = _i32(tjv_ptr)
+    t["tjv_v"] = _i32(tjv_v + [0] * (max(t["jreg_nnz"], 1) - len(tjv_v)))  # padded to the size the library copies
     t["fused_ok"] = bool(K <= MAX_FUSED_K and nbt_of(nB) > 0 and P == 0)
     return t
+
+
+def forward_thread_assignment(idx, val, nnz_row, V, chunk):
+    """Which vertex each thread of the fused forward pass owns.
+
+    A CTA covers ``chunk`` consecutive vertices; inside it the mapping thread -> vertex is free
+    because the results are staged in shared memory before they leave.  Two things are wanted:
+      * the threads of a warp should name as few distinct bones as possible: the bone transforms are
+        read from shared memory with per-thread addresses, and lanes that share an address share
+        the wavefront;
+      * the staging stores ``stage[3*pos + c]`` must stay bank-conflict free: the 32 positions of a
+        warp have to be distinct modulo 32.
+    So every residue class ``pos % 32`` hands exactly one vertex to each warp; within a class the
+    vertices are sorted by their bones and dealt to the warps in that order (vertices of the same
+    bone quantile meet in the same warp).
+
+    Returns ``fwd_pos[Vpad]`` (vertex index local to the chunk owned by thread t, -1 = none) and
+    ``owner[Vpad]`` (the same as a global vertex index)."""
+    nchunk = (V + chunk - 1) // chunk
+    nwarp = chunk // 32
+    K = idx.shape[1]
+    pos = np.full(nchunk * chunk, -1, dtype=np.int64)
+
+    def bones(v):
+        b0 = int(idx[v, 0])
+        b1 = int(idx[v, 1]) if K > 1 and nnz_row[v] > 1 else b0
+        return b0, b1
+
+    for c in range(nchunk):
+        v0, v1 = c * chunk, min(V, (c + 1) * chunk)
+        # grid[w][r] = vertex (or -1); start: every residue class sorted by bones and dealt to the warps in order
+        grid = [[-1] * 32 for _ in range(nwarp)]
+        for r in range(32):
+            vs = sorted(range(v0 + r, v1, 32), key=lambda v: bones(v) + (v,))
+            for w, v in enumerate(vs):
+                grid[w][r] = v
+        # local search: swap two warps' vertices of one residue class while that concentrates bones
+        # (score = sum over warps, slots and bones of count^2; both slots weigh the same)
+        cnt = [[dict(), dict()] for _ in range(nwarp)]
+        for w in range(nwarp):
+            for v in grid[w]:
+                if v >= 0:
+                    for s, b in enumerate(bones(v)):
+                        cnt[w][s][b] = cnt[w][s].get(b, 0) + 1
+
+        def gain_move(w, v, sign):
+            # change of the score when vertex v is added to (sign=+1) / removed from (sign=-1) warp w
+            g = 0
+            if v < 0:
+                return 0
+            for s, b in enumerate(bones(v)):
+                n = cnt[w][s].get(b, 0)
+                g += (2 * n + 1) if sign > 0 else (1 - 2 * n)
+            return g
+
+        def apply(w, v, sign):
+            if v < 0:
+                return
+            for s, b in enumerate(bones(v)):
+                cnt[w][s][b] = cnt[w][s].get(b, 0) + sign
+
+        for _sweep in range(12):
+            improved = False
+            for r in range(32):
+                for wa in range(nwarp):
+                    for wb in range(wa + 1, nwarp):
+                        va, vb = grid[wa][r], grid[wb][r]
+                        if va == vb or (va >= 0 and vb >= 0 and bones(va) == bones(vb)):
+                            continue
+                        g = gain_move(wa, va, -1) + gain_move(wb, vb, -1)
+                        apply(wa, va, -1); apply(wb, vb, -1)
+                        g += gain_move(wa, vb, +1) + gain_move(wb, va, +1)
+                        if g > 0:
+                            apply(wa, vb, +1); apply(wb, va, +1)
+                            grid[wa][r], grid[wb][r] = vb, va
+                            improved = True
+                        else:
+                            apply(wa, va, +1); apply(wb, vb, +1)
+            if not improved:
+                break
+        for w in range(nwarp):
+            for r in range(32):
+                if grid[w][r] >= 0:
+                    pos[c * chunk + w * 32 + r] = grid[w][r] - v0
+    owner = np.where(pos >= 0, pos + (np.arange(nchunk * chunk) // chunk) * chunk, -1)
+    return pos, owner
 
 
 def pack_backward_items(vt, S3, idx, val, nnz_row, J, nB, chunk=BWD_CHUNK, nwarps=BWD_WARPS):
@@ -251,7 +355,41 @@ def pack_backward_items(vt, S3, idx, val, nnz_row, J, nB, chunk=BWD_CHUNK, nwarp
     unit_slot = np.empty(nunits, dtype=np.int64)   # slots are numbered bone-major: bone k owns
     unit_slot[order] = np.arange(nunits)           # slots sb_ptr[k] .. sb_ptr[k+1]
     sb_ptr = np.concatenate([[0], np.cumsum(np.bincount(ub, minlength=J))])
+    # ---- item-PAIR records for the f32x2 kernel: two consecutive items of a unit share one record, so that
+    # every constant arrives as an (item i, item i+1) register pair.  Units with an odd item count get a
+    # zero-weight twin of their last item.  Record = T (3 pairs) | S (3*NBT pairs) | w | first | 3*lv (int bits) | pad.
+    nbt = max(nbt_of(nB), 1) if nbt_of(nB) > 0 else nB
+    rec2 = (6 + 6 * nbt + 8 + 3) // 4 * 4
+    recs, unit_pptr = [], [0]
+    Sv = S3.transpose(1, 0, 2)  # (V, nB, 3)
+    for u in range(nunits):
+        base = unit_tile[u] * chunk
+        its = list(range(unit_ptr[u], unit_ptr[u + 1]))
+        if len(its) % 2:
+            its.append(-its[-1] - 1)  # zero-weight twin
+        for a_, b_ in zip(its[0::2], its[1::2]):
+            r = np.zeros(rec2, dtype=np.float32)
+            for h, it in enumerate((a_, b_)):
+                twin = it < 0
+                it = -it - 1 if twin else it
+                lv = it_v[it]
+                v = base + lv
+                r[0 + h], r[2 + h], r[4 + h] = vt[v]
+                for m in range(nB):
+                    for c in range(3):
+                        r[6 + (m * 3 + c) * 2 + h] = Sv[v, m, c]
+                o = 6 + 6 * nbt
+                r[o + h] = 0.0 if twin else it_w[it]
+                r[o + 2 + h] = 0.0 if twin else it_first[it]
+                r[o + 4 + h] = np.int32(3 * lv).view(np.float32)
+            recs.append(r)
+        unit_pptr.append(len(recs))
+    rec2_arr = np.stack(recs) if recs else np.zeros((0, rec2), np.float32)
+    upp = np.asarray(unit_pptr, dtype=np.int64)
+    max_tile_pairs = int((upp[tup[1:]] - upp[tup[:-1]]).max()) if ntile else 0
     return dict(
+        rec2=_f32(rec2_arr), bwd_rec2=rec2, unit_pptr=_i32(unit_pptr), npair_items=len(recs),
+        bwd_max_tile_pairs=max_tile_pairs,
         bwd_chunk=chunk, bwd_ntile=ntile, bwd_warps=nwarps, bwd_rec=rec, vrec=_f32(vrec),
         unit_bone=_i32(unit_bone), unit_ptr=_i32(unit_ptr), unit_tile=_i32(unit_tile),
         tile_unit_ptr=_i32(tile_unit_ptr), warp_unit_ptr=_i32(warp_unit_ptr), warp_unit=_i32(warp_unit),
