@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define SMIL_ABI_VERSION 3
+#define SMIL_ABI_VERSION 4
 
 enum {
   SMIL_OK = 0,
@@ -94,6 +94,8 @@ typedef struct SmilModelDesc {
   const float* pj_cm;        /* [np][nB][3] */
   const int32_t* pb_ptr;     /* [J+1] the same pairs grouped by bone */
   const int32_t* pb_pair;    /* [np] */
+  const float* pbrec;        /* [np padded to 32][(6+3nB) padded to 4] the pairs bone-sorted, one record each:
+                                bone (int bits, -1 = padding) | joint (int bits) | c0[4] | cm[nB][3] */
   /* fused forward pass */
   const float* vconst;       /* [3+3nB][v_pad] */
   const int32_t* ell_idx;    /* [K][v_pad] */

@@ -11,7 +11,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsmil_b200.so")
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 c_f = C.POINTER(C.c_float)
 c_i = C.POINTER(C.c_int32)
@@ -32,7 +32,7 @@ class SmilModelDesc(C.Structure):
         ("parents", c_i), ("order", c_i), ("level_ptr", c_i), ("child_ptr", c_i), ("child_idx", c_i),
         ("JT", c_f), ("JS", c_f), ("jreg_rowsum", c_f),
         ("pj_ptr", c_i), ("pj_bone", c_i), ("pj_joint", c_i), ("pj_c0", c_f), ("pj_cm", c_f),
-        ("pb_ptr", c_i), ("pb_pair", c_i),
+        ("pb_ptr", c_i), ("pb_pair", c_i), ("pbrec", c_f),
         ("vconst", c_f), ("ell_idx", c_i), ("ell_w", c_f), ("fwd_pos", c_i),
         ("rec2", c_f), ("unit_bone", c_i), ("unit_ptr", c_i), ("unit_tile", c_i), ("tile_unit_ptr", c_i),
         ("warp_unit_ptr", c_i), ("warp_unit", c_i), ("tjv_ptr", c_i), ("tjv_v", c_i),
@@ -206,7 +206,7 @@ def _np_ptr(a: np.ndarray, ctype):
 
 
 _DESC_F32 = ("v_template", "shapedirs", "posedirs", "J_static", "skin_w", "jc_val", "jr_val", "JT", "JS", "jreg_rowsum",
-             "pj_c0", "pj_cm", "vconst", "ell_w", "rec2")
+             "pj_c0", "pj_cm", "pbrec", "vconst", "ell_w", "rec2")
 _DESC_I32 = ("skin_idx", "jc_ptr", "jc_vid", "jr_ptr", "jr_jid", "parents", "order", "level_ptr", "child_ptr",
              "child_idx", "pj_ptr", "pj_bone", "pj_joint", "pb_ptr", "pb_pair", "ell_idx", "fwd_pos", "unit_bone", "unit_ptr",
              "unit_tile", "tile_unit_ptr", "warp_unit_ptr", "warp_unit", "tjv_ptr", "tjv_v", "sb_ptr", "unit_slot")

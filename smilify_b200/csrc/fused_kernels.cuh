@@ -266,13 +266,10 @@ constexpr int SKIN_BWD_STREAMS = 4; // item-pair streams per warp (lane >> 3)
 
 struct SkinBwdArgs {
   int B, nb;
-  int groups_per_cta;        // consecutive sample groups processed by one CTA
   int max_tile_pairs;        // smem sizing
   const float* beta;  long long beta_stride;
   const float* pp; int blk;  // per-pair parameter blocks of the forward (A2 [J][12][2] first), blk floats each
   const float* g_verts;      // [B][V][3]
-  const float* g_joints;     // [B][J][3] folded into the tile through the joint regressor, or null
-  int max_jv, max_je;        // smem sizing of the tile's joint-regressor slice
   long long total_floats;    // B*V*3
   float* gA_slots;           // [B][num_units][12]
   float* gbt_part;           // [B][ntile][nb+3]
@@ -284,16 +281,15 @@ __host__ __device__ inline int skin_bwd_row_floats(int chunk) {
   return r + ((36 - (r & 31)) & 31);  // == 4 (mod 32): the 8 sample rows of a stream hit distinct banks
 }
 constexpr int SKIN_BWD_MAXU = 64;   // units per tile the shared descriptor table holds (packer keeps tiles below it)
-__host__ inline size_t skin_bwd_smem_bytes(int chunk, int rec, int max_pairs, int NBT, int J, int max_jv, int max_je) {
-  size_t fl = (size_t)max_pairs * rec + 2ull * SKIN_BWD_G * skin_bwd_row_floats(chunk) + 4ull * SKIN_BWD_G * (NBT + 4) +
-              4ull * SKIN_BWD_MAXU + 2ull * SKIN_BWD_G * ((3 * J + 3) & ~3) + 4ull * ((max_jv + 3) & ~3) +
-              2ull * ((max_je + 3) & ~3);
+__host__ inline size_t skin_bwd_smem_bytes(int chunk, int rec, int max_pairs, int NBT, int stages) {
+  size_t fl = (size_t)max_pairs * rec + (size_t)stages * SKIN_BWD_G * skin_bwd_row_floats(chunk) +
+              4ull * SKIN_BWD_G * (NBT + 4) + 4ull * SKIN_BWD_MAXU;
   return 32 + fl * 4;
 }
 
 __device__ __forceinline__ float2 dup2(float x) { return make_float2(x, x); }
 
-template <int NBT>
+template <int NBT, int STAGES>
 __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int NQ = (6 + 6 * NBT + 3) / 4;   // float4 loads that cover T and the NBT used shape directions
@@ -307,24 +303,18 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);  // [2]
   float* sRec = reinterpret_cast<float*>(smem_raw + 32);   // [max_pairs][REC]
   float* sRows = sRec + (size_t)a.max_tile_pairs * REC;    // [2][G][RF]
-  float* sRed = sRows + 2ull * SKIN_BWD_G * RF;            // [4 warps][G][NBT+4]
+  float* sRed = sRows + (size_t)STAGES * SKIN_BWD_G * RF;  // [4 warps][G][NBT+4]
   int4* sUnit = reinterpret_cast<int4*>(sRed + 4ull * SKIN_BWD_G * (NBT + 4));   // [MAXU] (bone*24, first pair, end pair, slot)
-  const int GJF = (3 * J + 3) & ~3;
-  float* sGJ = reinterpret_cast<float*>(sUnit + SKIN_BWD_MAXU);                  // [2][G][GJF] g_joints of a group
-  int4* sJV = reinterpret_cast<int4*>(sGJ + 2ull * SKIN_BWD_G * GJF);            // [max_jv] (3*lv, first entry, end entry, -)
-  int2* sJE = reinterpret_cast<int2*>(sJV + ((a.max_jv + 3) & ~3));              // [max_je] (3*joint, weight bits)
 
   const int u_beg = m.tile_unit_ptr[ti], u_end = m.tile_unit_ptr[ti + 1];
   const int pr_base = m.unit_ptr[u_beg], pr_cnt = m.unit_ptr[u_end] - pr_base;
   const int nv = min(C, V - ti * C);
   const int n = 3 * nv;
   const int ngroups = (a.B + SKIN_BWD_G - 1) / SKIN_BWD_G;
-  const int grp0 = blockIdx.y * a.groups_per_cta;
-  const int grp1 = min(ngroups, grp0 + a.groups_per_cta);
+  const int gstep = gridDim.y;   // persistent over sample groups: blockIdx.y, blockIdx.y + gridDim.y, ...
   const int wu_base = m.warp_unit_ptr[ti * m.bwd_warps];
   const int wu_beg = m.warp_unit_ptr[ti * m.bwd_warps + warp] - wu_base;
   const int wu_end = m.warp_unit_ptr[ti * m.bwd_warps + warp + 1] - wu_base;
-  const int jv_beg = m.tjv_ptr[ti], jv_cnt = a.g_joints ? m.tjv_ptr[ti + 1] - jv_beg : 0;
 
   if (tid == 0) {
     mbar_init(&bars[0], 1);
@@ -340,37 +330,7 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
       const int u = m.warp_unit[wu_base + i];
       sUnit[i] = make_int4(m.unit_bone[u] * 24, m.unit_ptr[u] - pr_base, m.unit_ptr[u + 1] - pr_base, m.unit_slot[u]);
     }
-    if (jv_cnt > 0) {   // the tile's slice of the joint regressor (CSR by vertex)
-      const int e_base = m.jr_ptr[ti * C];
-      for (int i = tid; i < jv_cnt; i += 128) {
-        const int lv = m.tjv_v[jv_beg + i], vg = ti * C + lv;
-        sJV[i] = make_int4(3 * lv, m.jr_ptr[vg] - e_base, m.jr_ptr[vg + 1] - e_base, 0);
-      }
-      const int e_cnt = m.jr_ptr[ti * C + nv] - e_base;
-      for (int i = tid; i < e_cnt; i += 128) sJE[i] = make_int2(3 * m.jr_jid[e_base + i], __float_as_int(m.jr_val[e_base + i]));
-    }
   }
-  // g_joints of a sample group: coalesced loads into registers one group ahead, parked in shared memory
-  constexpr int GJ_PER = 12;  // floats per thread: 8 samples x 3J <= 128 * 12  (J <= 64)
-  float gj_next[GJ_PER];
-  auto gj_fetch = [&](int grp) {
-    const int b0 = grp * SKIN_BWD_G;
-    const int cnt = min(SKIN_BWD_G, a.B - b0) * 3 * J;
-    const float* src = a.g_joints + (long long)b0 * 3 * J;
-#pragma unroll
-    for (int q = 0; q < GJ_PER; ++q) {
-      const int i = tid + q * 128;
-      gj_next[q] = (i < cnt) ? src[i] : 0.f;
-    }
-  };
-  auto gj_park = [&](int buf) {
-#pragma unroll
-    for (int q = 0; q < GJ_PER; ++q) {
-      const int i = tid + q * 128;
-      if (i < SKIN_BWD_G * 3 * J) sGJ[((size_t)buf * SKIN_BWD_G + i / (3 * J)) * GJF + i % (3 * J)] = gj_next[q];
-    }
-  };
-  if (jv_cnt > 0 && grp0 < grp1) { gj_fetch(grp0); gj_park(0); if (grp0 + 1 < grp1) gj_fetch(grp0 + 1); }
   __syncthreads();
 
   // producer: one bulk copy per sample row (16-byte aligned superset of the tile's float range)
@@ -396,8 +356,8 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
     }
   };
   if (tid == 0) {
-    if (grp0 < grp1) issue(grp0, 0);
-    if (grp0 + 1 < grp1) issue(grp0 + 1, 1);
+    if ((int)blockIdx.y < ngroups) issue(blockIdx.y, 0);
+    if (STAGES > 1 && (int)blockIdx.y + gstep < ngroups) issue(blockIdx.y + gstep, 1);
   }
 
   // betas of the group's samples, fetched one group ahead
@@ -407,11 +367,12 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
 #pragma unroll
     for (int k = 0; k < NBT; ++k) beta_next[k] = (k < a.nb) ? a.beta[(long long)bs * a.beta_stride + k] : 0.f;
   };
-  if (grp0 < grp1) beta_fetch(grp0);
+  if ((int)blockIdx.y < ngroups) beta_fetch(blockIdx.y);
 
-  for (int grp = grp0; grp < grp1; ++grp) {
-    const int stage = (grp - grp0) & 1;
-    const uint32_t parity = ((grp - grp0) >> 1) & 1;
+  int itn = 0;
+  for (int grp = blockIdx.y; grp < ngroups; grp += gstep, ++itn) {
+    const int stage = (STAGES > 1) ? (itn & 1) : 0;
+    const uint32_t parity = (STAGES > 1) ? ((itn >> 1) & 1) : (itn & 1);
     const int b0 = grp * SKIN_BWD_G;
     const int b = b0 + g;
     const bool valid = b < a.B;
@@ -427,33 +388,12 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
         for (long long e = len - 4; e < ph + n; ++e) row[e] = a.g_verts[off - ph + e];
       }
     }
-    if (jv_cnt > 0) {
-      __syncthreads();  // fix-up above visible before rows are modified
-      // g_verts[v] += sum_j Jreg[v,j] g_joints[j]   (thread = (vertex with entries, sample of the group))
-      const float* gjs = sGJ + (size_t)stage * SKIN_BWD_G * GJF;
-      for (int i = tid; i < jv_cnt * SKIN_BWD_G; i += 128) {
-        const int gg = i & (SKIN_BWD_G - 1);
-        const int bs = b0 + gg;
-        if (bs >= a.B) continue;
-        const int4 jv = sJV[i >> 3];
-        const long long off = ((long long)bs * V + (long long)ti * C) * 3;
-        float* p = sRows + ((size_t)stage * SKIN_BWD_G + gg) * RF + (int)(off & 3) + jv.x;
-        float x = p[0], y = p[1], z = p[2];
-        for (int e = jv.y; e < jv.z; ++e) {
-          const int2 je = sJE[e];
-          const float* gj = gjs + gg * GJF + je.x;
-          const float w = __int_as_float(je.y);
-          x = fmaf(w, gj[0], x); y = fmaf(w, gj[1], y); z = fmaf(w, gj[2], z);
-        }
-        p[0] = x; p[1] = y; p[2] = z;
-      }
-    }
     __syncthreads();
 
     float2 beta2[NBT];
 #pragma unroll
     for (int k = 0; k < NBT; ++k) beta2[k] = dup2(beta_next[k]);
-    if (grp + 1 < grp1) beta_fetch(grp + 1);
+    if (grp + gstep < ngroups) beta_fetch(grp + gstep);
     float2 gb2[NBT];
 #pragma unroll
     for (int k = 0; k < NBT; ++k) gb2[k] = make_float2(0.f, 0.f);
@@ -548,11 +488,7 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
       r[NBT] = gtx; r[NBT + 1] = gty; r[NBT + 2] = gtz;
     }
     __syncthreads();  // all warps done with this stage's rows and sRed complete
-    if (tid == 0 && grp + 2 < grp1) issue(grp + 2, stage);
-    if (jv_cnt > 0) {
-      if (grp + 1 < grp1) gj_park(stage ^ 1);   // visible to the next group after its first __syncthreads
-      if (grp + 2 < grp1) gj_fetch(grp + 2);
-    }
+    if (tid == 0 && grp + STAGES * gstep < ngroups) issue(grp + STAGES * gstep, stage);
     {
       const int ne = a.nb + 3;
       for (int i = tid; i < SKIN_BWD_G * ne; i += 128) {

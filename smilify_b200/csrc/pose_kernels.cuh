@@ -35,6 +35,8 @@ struct PoseArgs {
   const float* ls;    long long ls_stride;
   const float* bt;    long long bt_stride;
   const float* jrest_in;  // [B][J][3]
+  float* jrest_out;       // [B][J][3] forward: the rest joints it used, kept for the backward (or null)
+  int jrest_closed;       // backward: the rest joints were JT + beta JS, so dL/dbeta gets JS . dL/dJrest
   // forward outputs
   float* Rs;      // [B][J][9] or null
   float* A;       // [B][J][12] (3x4 row-major) or null
@@ -215,6 +217,10 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_fwd_kernel(DevModel m, Pose
   float* sbeta = sm + L.beta();
   float* sc = sm + L.scale();
   pose_local_state(m, a, X, jr, sbeta, /*stage=*/G, sc, b, l);
+  if (a.jrest_out && live) {
+    float* o = a.jrest_out + (long long)b * 3 * J;
+    for (int e = l; e < 3 * J; e += 32) o[e] = jr[e + e / 3];
+  }
   // Rs output from the packed staging copy (a sample's 9J floats are 16-byte aligned only if 9J % 4 == 0)
   if (a.Rs && live) {
     float* out = a.Rs + (long long)b * 9 * J;
@@ -304,14 +310,14 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
   const int b = blockIdx.x * POSE_WPB + w;
   if (b >= a.B) return;
   const int J = m.J, nb = a.nb;
-  const int per = ((L.bwd_floats() + (pairs_mode ? 32 * L.nbp : 0)) + 3) & ~3;
+  const int per = ((L.bwd_floats() + 32 * L.nbp) + 3) & ~3;
   float* sm = smem_pose + (size_t)w * per;
   float* X = sm + L.x();
   float* G = sm + L.g();
   float* jr = sm + L.jr();
   float* sbeta = sm + L.beta();
   float* rec = sm + L.rec();
-  float* accb = sm + L.bwd_floats();  // [32][nbp], pairs mode only
+  float* accb = sm + L.bwd_floats();  // [32][nbp] lane-private dL/dbeta partials
   const bool prop = (a.flags & SMIL_F_PROPAGATE_SCALING) != 0;
   const bool rotmat = (a.flags & SMIL_F_THETA_IS_ROTMAT) != 0;
 
@@ -329,8 +335,7 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
 
   // ---- dL/dA per bone: dense buffer + slot partials of the skin pass (+ closed-form posed joints) --------
   f3 gtr = mk3(0.f, 0.f, 0.f);
-  if (pairs_mode)
-    for (int k = 0; k < nb; ++k) accb[l * L.nbp + k] = 0.f;
+  for (int k = 0; k < nb; ++k) accb[l * L.nbp + k] = 0.f;
   for (int e = l; e < 3 * J; e += 32) {
     const int j = e / 3, r = e - 3 * j;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -342,23 +347,7 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
         acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
       }
     }
-    if (pairs_mode) {
-      // joints_jj = sum_k A_k [q_jk ; c0.w]: row r of dL/dA_k gets g_joints[jj][r] * [q ; c0.w]
-      const f3 GRr = ld3(G + j * 12 + 4 * r);
-      for (int pq = m.pb_ptr[j]; pq < m.pb_ptr[j + 1]; ++pq) {
-        const int pi = m.pb_pair[pq];
-        const float gj = a.g_joints[((long long)b * J + m.pj_joint[pi]) * 3 + r];
-        const float4 c0 = reinterpret_cast<const float4*>(m.pj_c0)[pi];
-        const float* cm = m.pj_cm + (long long)pi * m.nB * 3;
-        f3 q = mk3(c0.x, c0.y, c0.z);
-        for (int t = 0; t < nb; ++t) {
-          const float bt_ = sbeta[t];
-          q.x = fmaf(bt_, cm[3 * t], q.x); q.y = fmaf(bt_, cm[3 * t + 1], q.y); q.z = fmaf(bt_, cm[3 * t + 2], q.z);
-          accb[l * L.nbp + t] += gj * (GRr.x * cm[3 * t] + GRr.y * cm[3 * t + 1] + GRr.z * cm[3 * t + 2]);
-        }
-        acc.x = fmaf(gj, q.x, acc.x); acc.y = fmaf(gj, q.y, acc.y); acc.z = fmaf(gj, q.z, acc.z);
-        acc.w = fmaf(gj, c0.w, acc.w);
-      }
+    if (pairs_mode) {  // joints_j = ... + rowsum_j * trans
       const float rs = m.jreg_rowsum[j];
       const float gjj = a.g_joints[(long long)b * 3 * J + e];
       if (r == 0) gtr.x = fmaf(rs, gjj, gtr.x);
@@ -368,6 +357,54 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
     reinterpret_cast<float4*>(rec)[j * 5 + r] = acc;
   }
   __syncwarp();
+  if (pairs_mode) {
+    // closed-form posed joints, joints_j = sum_k A_k [q_jk ; c0w_jk] with q_jk = c0_jk + sum_m beta_m cm_jkm:
+    // lane per (joint, bone) pair in bone-sorted order, dL/dA_k = sum_j g_joints_j (x) [q_jk ; c0w_jk] by a
+    // segmented shuffle reduction over the lanes that share a bone (fixed order, no atomics).
+    const int RP = m.pbrec_floats;
+    for (int s0 = 0; s0 < m.npairs_pad; s0 += 32) {
+      const float* pr = m.pbrec + (long long)(s0 + l) * RP;
+      const int bone = __float_as_int(pr[0]);
+      const bool real = bone >= 0;
+      const int kb = real ? bone : 0;
+      f3 gj = mk3(0.f, 0.f, 0.f);
+      if (real) gj = ld3(a.g_joints + ((long long)b * J + __float_as_int(pr[1])) * 3);
+      const float* Gk = G + kb * 12;
+      const f3 tg = mk3(fmaf(Gk[0], gj.x, fmaf(Gk[4], gj.y, Gk[8] * gj.z)), fmaf(Gk[1], gj.x, fmaf(Gk[5], gj.y, Gk[9] * gj.z)),
+                        fmaf(Gk[2], gj.x, fmaf(Gk[6], gj.y, Gk[10] * gj.z)));   // GR_k^T g_joints_j
+      f3 q = mk3(pr[2], pr[3], pr[4]);
+      const float c0w = pr[5];
+      for (int t = 0; t < nb; ++t) {
+        const float cx = pr[6 + 3 * t], cy = pr[7 + 3 * t], cz = pr[8 + 3 * t], bt_ = sbeta[t];
+        q.x = fmaf(bt_, cx, q.x); q.y = fmaf(bt_, cy, q.y); q.z = fmaf(bt_, cz, q.z);
+        accb[l * L.nbp + t] += fmaf(tg.x, cx, fmaf(tg.y, cy, tg.z * cz));
+      }
+      float v[12];
+      v[0] = gj.x * q.x; v[1] = gj.x * q.y; v[2] = gj.x * q.z; v[3] = gj.x * c0w;
+      v[4] = gj.y * q.x; v[5] = gj.y * q.y; v[6] = gj.y * q.z; v[7] = gj.y * c0w;
+      v[8] = gj.z * q.x; v[9] = gj.z * q.y; v[10] = gj.z * q.z; v[11] = gj.z * c0w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int ob = __shfl_down_sync(0xffffffffu, bone, d);
+        const bool same = (l + d < 32) && ob == bone;
+#pragma unroll
+        for (int i = 0; i < 12; ++i) {
+          const float o = __shfl_down_sync(0xffffffffu, v[i], d);
+          if (same) v[i] += o;
+        }
+      }
+      const int pb_ = __shfl_up_sync(0xffffffffu, bone, 1);
+      if (real && (l == 0 || pb_ != bone)) {   // first lane of a bone's run holds the run's sum
+        float4* d4 = reinterpret_cast<float4*>(rec + bone * 20);
+        float4 t0 = d4[0], t1 = d4[1], t2 = d4[2];
+        t0.x += v[0]; t0.y += v[1]; t0.z += v[2]; t0.w += v[3];
+        t1.x += v[4]; t1.y += v[5]; t1.z += v[6]; t1.w += v[7];
+        t2.x += v[8]; t2.y += v[9]; t2.z += v[10]; t2.w += v[11];
+        d4[0] = t0; d4[1] = t1; d4[2] = t2;
+      }
+      __syncwarp();
+    }
+  }
   // ---- A = [GR | Gt - GR Jrest], new_J = Gt  ->  initial (gGR | gGt) and dL/dJrest ---------------------------
   for (int j = l; j < J; j += 32) {
     m3 gAR, GR; f3 gAt, dummy;
@@ -508,13 +545,14 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
       for (int t = 0; t < a.ntile; ++t) part += a.gbt_part[((long long)b * a.ntile + t) * ne + l];
     float mine = 0.f;
     if (a.g_beta) {
-      for (int k = 0; k < nb; ++k) {
-        float s = 0.f;
-        if (a.jrest_mode == 0) {
-          const float* js = m.JS + (long long)k * 3 * J;
-          for (int e = l; e < 3 * J; e += 32) { const int j = e / 3; s = fmaf(js[e], jr[j * 4 + (e - 3 * j)], s); }
+      if (a.jrest_closed) {   // rest joints JT + beta JS: dL/dbeta_k += JS_k . dL/dJrest, all k in one pass over the joints
+        for (int e = l; e < 3 * J; e += 32) {
+          const float gje = jr[e + e / 3];
+          for (int k = 0; k < nb; ++k) accb[l * L.nbp + k] = fmaf(m.JS[(long long)k * 3 * J + e], gje, accb[l * L.nbp + k]);
         }
-        if (pairs_mode) s += accb[l * L.nbp + k];
+      }
+      for (int k = 0; k < nb; ++k) {
+        float s = accb[l * L.nbp + k];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
         if (l == k) mine = s;

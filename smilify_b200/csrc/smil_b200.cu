@@ -26,6 +26,8 @@ std::atomic<long long> g_launches{0};
 std::atomic<int> g_prof_on{0};
 int g_fwd_gp = 0;   // tuning override (SMIL_FWD_GP): sample pairs per TMA group of the fused forward pass
 int g_fwd_direct = 0;  // tuning override (SMIL_FWD_DIRECT): register -> global stores instead of the TMA staging ring
+int g_bwd_stages = 1;  // SMIL_BWD_STAGES: 1 = single-buffered g_verts rows (more CTAs per SM), 2 = double-buffered
+int g_bwd_cps = 0;     // SMIL_BWD_CPS
 int g_fwd_cps = 0;  // tuning override (SMIL_FWD_CPS): resident CTAs per SM the forward grid is sized for
 std::mutex g_prof_mu;
 std::vector<ProfSlot> g_prof_slots;   // event pairs, created by smil_profile_enable
@@ -91,7 +93,7 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
   L.J = m.J;
   L.nbp = (std::max(a.nb, 1) + 3) & ~3;
   const int pairs_mode = backward && a.joints_mode == 1 && a.g_joints && !a.joints_in_skin;
-  const int fl = backward ? L.bwd_floats() + (pairs_mode ? 32 * L.nbp : 0) : L.fwd_floats();
+  const int fl = backward ? L.bwd_floats() + 32 * L.nbp : L.fwd_floats();
   const size_t smem = (size_t)((fl + 3) & ~3) * sizeof(float) * POSE_WPB;
   const int grid = (a.B + POSE_WPB - 1) / POSE_WPB;
   int rc = SMIL_OK;
@@ -122,7 +124,7 @@ int launch_skin_fwd_inst2(const DevModel& m, const SkinFwdArgs& a, cudaStream_t 
     occ_smem = smem;
   }
   const int ngroups = ((a.B + 1) / 2 + a.GP - 1) / a.GP;
-  const int cps = g_fwd_cps > 0 ? std::min(g_fwd_cps, std::max(occ, 1)) : std::max(occ, 1);
+  const int cps = std::min(g_fwd_cps > 0 ? g_fwd_cps : 3, std::max(occ, 1));
   const int Y = std::max(1, std::min(ngroups, (m.sm_count * cps) / std::max(m.fwd_nchunk, 1)));
   dim3 grid(m.fwd_nchunk, Y);
   prof_begin("skin_fwd_kernel", st);
@@ -159,17 +161,31 @@ int launch_skin_fwd(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
   return fail(SMIL_EUNSUPPORTED, "fused forward: %d betas not covered", a.nb);
 }
 
-template <int NBT>
-int launch_skin_bwd_inst(const DevModel& m, const SkinBwdArgs& a, cudaStream_t st) {
-  const size_t smem = skin_bwd_smem_bytes(m.bwd_chunk, m.bwd_rec, a.max_tile_pairs, NBT, m.J, a.max_jv, a.max_je);
-  int rc = set_smem(skin_bwd_kernel<NBT>, smem);
+template <int NBT, int STAGES>
+int launch_skin_bwd_inst2(const DevModel& m, const SkinBwdArgs& a, cudaStream_t st) {
+  const size_t smem = skin_bwd_smem_bytes(m.bwd_chunk, m.bwd_rec, a.max_tile_pairs, NBT, STAGES);
+  int rc = set_smem(skin_bwd_kernel<NBT, STAGES>, smem);
   if (rc != SMIL_OK) return rc;
+  static thread_local size_t occ_smem = 0;
+  static thread_local int occ = 0;
+  if (occ_smem != smem) {
+    SMIL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, skin_bwd_kernel<NBT, STAGES>, 128, smem));
+    occ_smem = smem;
+  }
+  // persistent CTAs: one wave; every CTA keeps its tile's constants and walks its share of the sample groups
   const int ngroups = (a.B + SKIN_BWD_G - 1) / SKIN_BWD_G;
-  dim3 grid(m.bwd_ntile, (ngroups + a.groups_per_cta - 1) / a.groups_per_cta);
+  const int cps = g_bwd_cps > 0 ? std::min(g_bwd_cps, std::max(occ, 1)) : std::max(occ, 1);
+  const int Y = std::max(1, std::min(ngroups, (m.sm_count * cps) / std::max(m.bwd_ntile, 1)));
+  dim3 grid(m.bwd_ntile, Y);
   prof_begin("skin_bwd_kernel", st);
-  skin_bwd_kernel<NBT><<<grid, 128, smem, st>>>(m, a);
+  skin_bwd_kernel<NBT, STAGES><<<grid, 128, smem, st>>>(m, a);
   SMIL_LAUNCH_CHECK("skin_bwd_kernel");
   return SMIL_OK;
+}
+template <int NBT>
+int launch_skin_bwd_inst(const DevModel& m, const SkinBwdArgs& a, cudaStream_t st) {
+  if (g_bwd_stages == 1) return launch_skin_bwd_inst2<NBT, 1>(m, a, st);
+  return launch_skin_bwd_inst2<NBT, 2>(m, a, st);
 }
 int launch_skin_bwd(const DevModel& m, const SkinBwdArgs& a, cudaStream_t st) {
   switch (nbt_of(a.nb)) {
@@ -327,6 +343,8 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   d.device = s->device;
   if (const char* e = getenv("SMIL_FWD_GP")) g_fwd_gp = atoi(e);
   if (const char* e = getenv("SMIL_FWD_CPS")) g_fwd_cps = atoi(e);
+  if (const char* e = getenv("SMIL_BWD_STAGES")) g_bwd_stages = atoi(e);
+  if (const char* e = getenv("SMIL_BWD_CPS")) g_bwd_cps = atoi(e);
   if (const char* e = getenv("SMIL_FWD_DIRECT")) g_fwd_direct = atoi(e);
   SMIL_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, s->device));
 
@@ -359,6 +377,9 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   ap.add(s->pj_cm, V ? np * std::max<size_t>(nB, 1) * 3 : 0, &d.pj_cm);
   ap.add(s->pb_ptr, V ? J + 1 : 0, &d.pb_ptr);
   ap.add(s->pb_pair, V ? np : 0, &d.pb_pair);
+  d.pbrec_floats = (6 + 3 * d.nB + 3) / 4 * 4;
+  d.npairs_pad = (d.npairs + 31) / 32 * 32;
+  ap.add(s->pbrec, (V && s->pbrec) ? (size_t)std::max(d.npairs_pad, 1) * d.pbrec_floats : 0, &d.pbrec);
   ap.add(s->vconst, (3 + 3 * nB) * (size_t)d.v_pad, &d.vconst);
   ap.add(s->ell_idx, K * (size_t)d.v_pad, &d.ell_idx);
   ap.add(s->ell_w, K * (size_t)d.v_pad, &d.ell_w);
@@ -468,11 +489,12 @@ int smil_forward(const SmilModel* model, const SmilFwdArgs* f, void* stream) {
 
   if (p.fused) {
     pa.joints_mode = p.is_static ? 2 : 1;
+    if (!p.is_static) pa.jrest_out = jrest;   // the backward reads the rest joints back instead of re-deriving them
     if ((rc = launch_pose(m, pa, false, st)) != SMIL_OK) return rc;
     if (!p.joints_only) {
       SkinFwdArgs sa;
       sa.B = B; sa.nb = f->num_betas_used;
-      sa.GP = g_fwd_gp > 0 ? std::min(g_fwd_gp, SKIN_FWD_GPMAX) : 4;
+      sa.GP = g_fwd_gp > 0 ? std::min(g_fwd_gp, SKIN_FWD_GPMAX) : 2;
       sa.blk = pair_blk(m);
       sa.pp = A; sa.verts = f->verts; sa.v_shaped = f->v_shaped;
       if ((rc = launch_skin_fwd(m, sa, st)) != SMIL_OK) return rc;
@@ -557,24 +579,20 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
       if (((uintptr_t)g->g_verts) & 15) return fail(SMIL_EINVAL, "g_verts must be 16-byte aligned");
       SkinBwdArgs sa;
       sa.B = B; sa.nb = nb;
-      const int ngroups = (B + SKIN_BWD_G - 1) / SKIN_BWD_G;
-      long long gpc = ((long long)ngroups * m.bwd_ntile) / (6LL * m.sm_count);
-      sa.groups_per_cta = (int)std::min<long long>(32, std::max<long long>(1, gpc));
       sa.max_tile_pairs = m.h_max_tile_pairs;
       sa.beta = f->beta; sa.beta_stride = f->beta_stride;
       sa.pp = A; sa.blk = pair_blk(m); sa.g_verts = g->g_verts;
-      sa.g_joints = p.is_static ? nullptr : g->g_joints;
-      sa.max_jv = m.h_max_jv; sa.max_je = m.h_max_je;
       sa.total_floats = (long long)B * m.V * 3;
       sa.gA_slots = slots; sa.gbt_part = part;
       if ((rc = launch_skin_bwd(m, sa, st)) != SMIL_OK) return rc;
       pa.gA_slots = slots; pa.nslots = m.num_units;
       pa.gbt_part = part; pa.ntile = m.bwd_ntile;
-      pa.joints_in_skin = 1;  // the skin pass folded Jreg g_joints into its g_verts tiles
     }
     pa.joints_mode = p.is_static ? 2 : 1;
     pa.g_beta = g->g_beta; pa.g_trans = g->g_trans;
     pa.beta_final = 1;
+    pa.jrest_closed = p.jrest_mode == 0;
+    if (p.jrest_mode == 0) pa.jrest_mode = 2;   // rest joints saved by the forward
     pa.pp_saved = A; pa.pp_blk = pair_blk(m);
     return launch_pose(m, pa, true, st);
   }

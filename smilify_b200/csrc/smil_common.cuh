@@ -68,6 +68,8 @@ struct DevModel {
   const int *pj_ptr, *pj_bone, *pj_joint;
   const float *pj_c0, *pj_cm;
   const int *pb_ptr, *pb_pair;
+  const float* pbrec;
+  int pbrec_floats, npairs_pad;
   const float* vconst;
   const int* ell_idx;
   const float* ell_w;

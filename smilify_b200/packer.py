@@ -172,6 +172,20 @@ def pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J
     t["pb_ptr"] = _i32(np.concatenate([[0], np.cumsum(np.bincount(np.asarray(pj_bone, dtype=np.int64), minlength=J))])
                        if npairs else np.zeros(J + 1))
     t["pb_pair"] = _i32(pb) if npairs else np.zeros(1, np.int32)
+    # the same pairs once more, bone-sorted and 32-padded, one contiguous record each, for the backward's
+    # lane-per-pair pass: (bone | joint | c0[4] | cm[nB][3] | pad); padding records carry bone -1
+    rp = (6 + 3 * nB + 3) // 4 * 4
+    npad = (npairs + 31) // 32 * 32
+    pbrec = np.zeros((max(npad, 1), rp), dtype=np.float32)
+    pbrec[:, 0] = np.int32(-1).view(np.float32)
+    for s_, pi in enumerate(pb):
+        pbrec[s_, 0] = np.int32(pj_bone[pi]).view(np.float32)
+        pbrec[s_, 1] = np.int32(pj_joint[pi]).view(np.float32)
+        pbrec[s_, 2:6] = pj_c0[pi]
+        pbrec[s_, 6:6 + 3 * nB] = np.asarray(pj_cm[pi], dtype=np.float32).reshape(-1)
+    t["pbrec"] = _f32(pbrec)
+    t["pbrec_floats"] = rp
+    t["npairs_pad"] = npad
 
     # ---- fused forward skinning pass: per-vertex constants, SoA over a padded vertex axis -----
     nchunk = (V + FWD_CHUNK - 1) // FWD_CHUNK
