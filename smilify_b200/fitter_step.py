@@ -1,0 +1,126 @@
+"""Multi-GPU shared-parameter fitting step (BASELINE configs[3]).
+
+``SMALFitter`` (/root/reference/smal_fitter/fitter.py:150-296) optimises per-frame parameters
+(``global_rotation``, ``joint_rotations``, ``trans``) together with parameters shared by every
+frame of the sequence: ONE ``betas`` vector that is ``expand``-ed over the frames (fitter.py:244),
+the camera ``fov`` (fitter.py:231) and, when enabled, shared ``log_beta_scales`` / ``betas_trans``
+(fitter.py:183-189).  Frames are independent through the SMAL call and the joint loss, so the
+frames are sharded contiguously over the ranks (one process per GPU) and the ONLY exchange is the
+gradient of the shared parameters: they are packed into one fp32 buffer (nB + 1 (+ 6J) floats =
+24 B ... 1.4 KB) and summed with a single ``all_reduce`` per optimiser step (NCCL over
+NVLink/NVSwitch on GPUs, gloo in the CPU tests).  Per-frame parameters never leave their rank.
+
+Nothing here launches kernels itself: the SMAL forward/backward and the loss are the C-ABI CUDA
+path (``smal_torch.SMAL``, ``losses.fitter_joint_loss``); the step function is injectable so the
+world-size-2 gloo tests can drive the same host logic with a CPU stand-in.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def shard_range(num_frames: int, rank: int, world: int):
+    """Contiguous frame shard of ``rank`` (the first ``num_frames % world`` ranks get one extra)."""
+    if not (0 <= rank < world):
+        raise ValueError("rank %d outside [0,%d)" % (rank, world))
+    base, extra = divmod(num_frames, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def pack_grads(tensors: Sequence[Optional[torch.Tensor]], like: Sequence[torch.Tensor]) -> torch.Tensor:
+    """Flatten the gradients of the shared parameters into one fp32 buffer (``None`` -> zeros)."""
+    parts = []
+    for g, p in zip(tensors, like):
+        parts.append(torch.zeros(p.numel(), dtype=torch.float32, device=p.device) if g is None
+                     else g.detach().reshape(-1).to(torch.float32))
+    return torch.cat(parts) if parts else torch.zeros(0)
+
+
+def unpack_grads(buf: torch.Tensor, like: Sequence[torch.Tensor]):
+    out, o = [], 0
+    for p in like:
+        n = p.numel()
+        out.append(buf[o:o + n].reshape(p.shape).to(p.dtype))
+        o += n
+    return out
+
+
+def allreduce_shared_grads(shared: Sequence[torch.Tensor], group=None) -> int:
+    """Sum ``p.grad`` of every shared parameter over the ranks with ONE collective.
+    Returns the number of bytes in the packed buffer (0 when not distributed)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return 0
+    buf = pack_grads([p.grad for p in shared], shared)
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+    for p, g in zip(shared, unpack_grads(buf, shared)):
+        p.grad = g.clone() if p.grad is None else p.grad.copy_(g)
+    return buf.numel() * 4
+
+
+class ShardedFitterStep:
+    """One optimisation step of a frame-sharded joint fit.
+
+    ``frame_params``  dict name -> per-frame leaf tensor of THIS rank's shard, shape (n_local, ...)
+    ``shared_params`` dict name -> leaf tensor replicated on every rank (``betas`` (nB,), ``fov`` (1,), ...)
+    ``loss_fn(frame_params, shared_params) -> scalar``  the *sum* over the local frames of the
+        per-frame loss terms (so that the global objective is ``sum_ranks loss / num_frames_total``,
+        i.e. the same ``mean`` the single-process fitter takes, fitter.py:296).
+    """
+
+    def __init__(self, frame_params: Dict[str, torch.Tensor], shared_params: Dict[str, torch.Tensor],
+                 loss_fn: Callable[[Dict[str, torch.Tensor], Dict[str, torch.Tensor]], torch.Tensor],
+                 num_frames_total: int, group=None):
+        self.frame_params, self.shared_params = frame_params, shared_params
+        self.loss_fn, self.group = loss_fn, group
+        self.num_frames_total = int(num_frames_total)
+        self.collective_bytes = 0
+
+    def __call__(self) -> torch.Tensor:
+        """Backward through the local shard, then the one packed all-reduce.  Returns the GLOBAL loss
+        (identical on every rank); gradients are left in ``.grad`` of every leaf."""
+        for p in list(self.frame_params.values()) + list(self.shared_params.values()):
+            p.grad = None
+        local = self.loss_fn(self.frame_params, self.shared_params) / self.num_frames_total
+        local.backward()
+        shared = list(self.shared_params.values())
+        distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1
+        if not distributed:
+            return local.detach()
+        # the loss value rides in the same buffer: still ONE collective per step
+        buf = torch.cat([pack_grads([p.grad for p in shared], shared), local.detach().reshape(1).to(torch.float32)])
+        dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=self.group)
+        self.collective_bytes = buf.numel() * 4
+        for p, g in zip(shared, unpack_grads(buf[:-1], shared)):
+            p.grad = g.clone() if p.grad is None else p.grad.copy_(g)
+        return buf[-1].clone()
+
+
+def smal_joint_loss_fn(model, cam_R, cam_T, target_yx, visibility, joint_ids=None, image_size=512, w_j2d=1.0,
+                       propagate_scaling=False, get_skin=False):
+    """``loss_fn`` for :class:`ShardedFitterStep` built from the CUDA path: SMAL forward (joints) +
+    the fitter's 2-D joint loss (fitter.py:262-296).  ``frame_params``: ``global_rotation`` (n,3),
+    ``joint_rotations`` (n,J-1,3), ``trans`` (n,3);  ``shared_params``: ``betas`` (nB,), ``fov`` (1,),
+    optional ``log_beta_scales`` / ``betas_trans`` (1,J,3).  Returns the SUM over the local frames."""
+    from . import losses
+
+    def fn(fp, sp):
+        n = fp["trans"].shape[0]
+        theta = torch.cat([fp["global_rotation"].unsqueeze(1), fp["joint_rotations"]], dim=1)
+        ls = sp["log_beta_scales"].expand(n, -1, -1) if "log_beta_scales" in sp else None
+        bt = sp["betas_trans"].expand(n, -1, -1) if "betas_trans" in sp else None
+        out = model(sp["betas"].unsqueeze(0).expand(n, -1), theta, betas_logscale=ls, betas_trans=bt,
+                    propagate_scaling=propagate_scaling, get_skin=get_skin)   # get_skin=True also poses the mesh (fitter.py:262)
+        joints = out[1] if get_skin else out
+        joints = joints + fp["trans"].unsqueeze(1)                     # p3d_renderer.py:131
+        if joint_ids is not None:
+            joints = joints[:, joint_ids]                              # fitter.py:283
+        loss, _ = losses.fitter_joint_loss(joints, cam_R, cam_T, sp["fov"].expand(n), target_yx, visibility,
+                                           w_j2d=w_j2d, image_size=image_size)
+        # fitter_joint_loss is a mean over n*Jc*2 elements: turn it back into the per-frame sum
+        return loss * n
+
+    return fn

@@ -247,3 +247,26 @@ def singleview_keypoint_loss(joints, cam_R, cam_T, fov, target, visibility, join
 def keypoint3d_loss(joints, target, visibility=None, joint_weights=None, sample_mask=None):
     """``_compute_batch_keypoint_3d_loss`` (smil_image_regressor.py:3334-3407)."""
     return Keypoint3dLossFunction.apply(_f(joints), _f(target), _f(visibility), _f(joint_weights), _f(sample_mask))
+
+
+def pca_joint_values(scale_weights, trans_weights, scaledirs, transdirs, translation_factor=0.01, min_scale=1e-4):
+    """``_transform_separate_pca_weights_to_joint_values`` (smil_image_regressor.py:1166-1232): PCA weights
+    (B,C) -> ``(log_beta_scales, betas_trans)`` (B,J,3) that feed ``SMAL(..., betas_logscale=, betas_trans=)``.
+    ``scaledirs`` / ``transdirs`` are (J,3,C) as the reference caches them (the pickle stores (C,J,3)).
+    Stays in torch: two tiny einsums whose outputs are kernel inputs."""
+    B = scale_weights.shape[0]
+    if scaledirs is None or transdirs is None:
+        J = 0 if scaledirs is None and transdirs is None else (scaledirs if scaledirs is not None else transdirs).shape[0]
+        z = torch.zeros(B, J, 3, device=scale_weights.device)
+        return z, z.clone()
+    scale = torch.clamp(1.0 + torch.einsum("jck,bk->bjc", scaledirs, scale_weights), min=min_scale)
+    log_beta_scales = torch.log(scale)
+    if trans_weights is not None:
+        betas_trans = torch.einsum("jck,bk->bjc", transdirs, trans_weights) * translation_factor
+    else:
+        betas_trans = torch.zeros(B, scaledirs.shape[0], 3, device=scale_weights.device)
+    if not torch.isfinite(log_beta_scales).all():
+        log_beta_scales = torch.nan_to_num(log_beta_scales, nan=0.0, posinf=0.0, neginf=-10.0)
+    if trans_weights is not None and not torch.isfinite(betas_trans).all():
+        betas_trans = torch.nan_to_num(betas_trans, nan=0.0, posinf=0.0, neginf=0.0)
+    return log_beta_scales, betas_trans

@@ -1,0 +1,164 @@
+"""Frame-sharded shared-parameter step.
+
+CPU (gloo, world size 2): the host logic -- contiguous shards, ONE packed all-reduce carrying the
+shared gradients and the loss -- reproduces the single-process gradients, with the oracle standing
+in for the CUDA call.  GPU: the same step driven by the CUDA path equals the oracle's gradients."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import projection_oracle as PO
+from oracle import smal_oracle as SO
+from smilify_b200 import fitter_step as FS
+from smilify_b200 import losses as L
+from tests import rigs
+
+N_FRAMES = 11  # odd on purpose: ragged shards (6 + 5)
+
+
+def _problem(dd, n, seed=3, dtype=torch.float64):
+    rs = np.random.RandomState(seed)
+    J = np.asarray(dd["weights"]).shape[1]
+    nB = np.asarray(dd["shapedirs"]).shape[-1]
+    t = lambda a: torch.from_numpy(np.asarray(a)).to(dtype)
+    frame = dict(global_rotation=t(rs.normal(0, 0.3, (n, 3))), joint_rotations=t(rs.normal(0, 0.3, (n, J - 1, 3))),
+                 trans=t(rs.normal(0, 0.1, (n, 3))))
+    shared = dict(betas=t(rs.normal(0, 0.5, (nB,))), fov=t([60.0]))
+    R, T = PO.look_at_default(2.7, dtype=dtype)
+    target = t(rs.uniform(0, 512, (n, J, 2)))
+    vis = t(rs.uniform(size=(n, J)) < 0.8)
+    return frame, shared, R, T, target, vis
+
+
+def _oracle_loss_fn(model, R, T, target, vis):
+    def fn(fp, sp):
+        n = fp["trans"].shape[0]
+        theta = torch.cat([fp["global_rotation"].unsqueeze(1), fp["joint_rotations"]], dim=1)
+        _, joints, _, _ = SO.smal_forward(model, sp["betas"].unsqueeze(0).expand(n, -1), theta)
+        loss, _ = PO.fitter_joint_loss(joints, fp["trans"], R, T, sp["fov"].expand(n), target, vis, 1.0, 512.0)
+        return loss * n
+    return fn
+
+
+def _single_process_reference(dd, dtype=torch.float64):
+    frame, shared, R, T, target, vis = _problem(dd, N_FRAMES, dtype=dtype)
+    model = SO.build_model(dd, dtype=dtype)
+    fp = {k: v.clone().requires_grad_(True) for k, v in frame.items()}
+    sp = {k: v.clone().requires_grad_(True) for k, v in shared.items()}
+    step = FS.ShardedFitterStep(fp, sp, _oracle_loss_fn(model, R, T, target, vis), N_FRAMES)
+    loss = step()
+    return loss, {k: v.grad.clone() for k, v in fp.items()}, {k: v.grad.clone() for k, v in sp.items()}
+
+
+def _worker(rank, world, port, out_q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(1)
+        dd = rigs.get_rig("syn_k3")
+        frame, shared, R, T, target, vis = _problem(dd, N_FRAMES)
+        lo, hi = FS.shard_range(N_FRAMES, rank, world)
+        model = SO.build_model(dd, dtype=torch.float64)
+        fp = {k: v[lo:hi].clone().requires_grad_(True) for k, v in frame.items()}
+        sp = {k: v.clone().requires_grad_(True) for k, v in shared.items()}
+        step = FS.ShardedFitterStep(fp, sp, _oracle_loss_fn(model, R, T, target[lo:hi], vis[lo:hi]), N_FRAMES)
+        loss = step()
+        out_q.put((rank, lo, hi, float(loss), {k: v.grad.numpy() for k, v in fp.items()},
+                   {k: v.grad.numpy() for k, v in sp.items()}, step.collective_bytes))
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_shard_range_covers_everything():
+    for n in (1, 7, 8, 65536):
+        for w in (1, 2, 3, 8):
+            spans = [FS.shard_range(n, r, w) for r in range(w)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = [b - a for a, b in spans]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        FS.shard_range(4, 2, 2)
+
+
+def test_pack_roundtrip_and_none():
+    like = [torch.zeros(5), torch.zeros(1), torch.zeros(1, 4, 3)]
+    g = [torch.arange(5.0), None, torch.ones(1, 4, 3)]
+    buf = FS.pack_grads(g, like)
+    assert buf.shape == (18,) and buf.dtype == torch.float32
+    out = FS.unpack_grads(buf, like)
+    assert torch.equal(out[0], g[0]) and torch.equal(out[1], torch.zeros(1)) and out[2].shape == (1, 4, 3)
+
+
+@pytest.mark.timeout(300)
+def test_gloo_world2_matches_single_process():
+    dd = rigs.get_rig("syn_k3")
+    ref_loss, ref_fg, ref_sg = _single_process_reference(dd)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    nB = ref_sg["betas"].numel()
+    for rank, lo, hi, loss, fg, sg, nbytes in res:
+        assert nbytes == 4 * (nB + 1 + 1)            # betas + fov + the loss value: ONE small buffer
+        assert abs(loss - float(ref_loss)) <= 1e-6 * abs(float(ref_loss))      # fp32 buffer
+        for k in fg:                                                           # per-frame grads never left the rank
+            np.testing.assert_allclose(fg[k], ref_fg[k][lo:hi].numpy(), rtol=1e-9, atol=1e-12)
+        for k in sg:
+            np.testing.assert_allclose(sg[k], ref_sg[k].numpy(), rtol=2e-6, atol=1e-9)
+
+
+def test_pca_joint_values_matches_oracle():
+    rs = np.random.RandomState(0)
+    J, C, B = 9, 4, 6
+    sd, td = torch.from_numpy(rs.normal(0, 0.3, (J, 3, C))), torch.from_numpy(rs.normal(0, 0.3, (J, 3, C)))
+    sw, tw = torch.from_numpy(rs.normal(0, 2.0, (B, C))), torch.from_numpy(rs.normal(0, 1.0, (B, C)))
+    a = L.pca_joint_values(sw, tw, sd, td)
+    b = SO.pca_weights_to_joint_values(sd, td, sw, tw)
+    assert torch.allclose(a[0], b[0]) and torch.allclose(a[1], b[1])
+    assert (sd * 0 + 1).sum() > 0 and torch.isfinite(a[0]).all()   # the clamp kept log() finite
+    z = L.pca_joint_values(sw, None, sd, td)
+    assert torch.count_nonzero(z[1]) == 0
+
+
+@pytest.mark.gpu
+def test_cuda_step_matches_oracle():
+    import smilify_b200
+    from smilify_b200.smal_torch import SMAL
+
+    dd = rigs.get_rig("stick")
+    ref_loss, ref_fg, ref_sg = _single_process_reference(dd)
+    smilify_b200.configure(rigs.REAL_RIGS["stick"])
+    dev = torch.device("cuda:0")
+    model = SMAL(dev)
+    frame, shared, R, T, target, vis = _problem(dd, N_FRAMES, dtype=torch.float32)
+    fp = {k: v.to(dev).requires_grad_(True) for k, v in frame.items()}
+    sp = {k: v.to(dev).requires_grad_(True) for k, v in shared.items()}
+    fn = FS.smal_joint_loss_fn(model, R.to(dev), T.to(dev), target.to(dev), vis.to(dev))
+    loss = FS.ShardedFitterStep(fp, sp, fn, N_FRAMES)()
+    tol = 1e-5
+    assert abs(float(loss) - float(ref_loss)) <= tol * abs(float(ref_loss))
+    for k in fp:
+        r = ref_fg[k].float()
+        assert float((fp[k].grad.cpu() - r).abs().max()) <= tol * float(r.abs().max()), k
+    for k in sp:
+        r = ref_sg[k].float()
+        assert float((sp[k].grad.cpu() - r).abs().max()) <= tol * float(r.abs().max()), k
