@@ -106,7 +106,8 @@ __device__ __forceinline__ void pose_local_state(const DevModel& m, const PoseAr
                                                  float* stage, float* sc, int b, int l) {
   const int J = m.J;
   const bool rotmat = (a.flags & SMIL_F_THETA_IS_ROTMAT) != 0;
-  for (int k = l; k < a.nb; k += 32) sbeta[k] = a.beta[(long long)b * a.beta_stride + k];
+  const int nbp = (max(a.nb, 1) + 3) & ~3;   // == PoseSmem::nbp: the padding reads as zero betas
+  for (int k = l; k < nbp; k += 32) sbeta[k] = (k < a.nb) ? a.beta[(long long)b * a.beta_stride + k] : 0.f;
   if (rotmat) {  // [J][9] contiguous per sample -> staging, coalesced
     const float* src = a.theta + (long long)b * a.theta_stride;
     for (int e = l; e < 9 * J; e += 32) stage[e] = src[e];
@@ -120,7 +121,14 @@ __device__ __forceinline__ void pose_local_state(const DevModel& m, const PoseAr
       v = a.jrest_in[(long long)b * 3 * J + e];
     } else {
       v = m.JT[e];
-      for (int k = 0; k < a.nb; ++k) v = fmaf(sbeta[k], m.JS[k * 3 * J + e], v);
+      for (int k = 0; k < a.nb; k += 4) {   // four table loads in flight per step (the tables sit in L1/L2)
+        const float j0 = m.JS[k * 3 * J + e];
+        const float j1 = (k + 1 < a.nb) ? m.JS[(k + 1) * 3 * J + e] : 0.f;
+        const float j2 = (k + 2 < a.nb) ? m.JS[(k + 2) * 3 * J + e] : 0.f;
+        const float j3 = (k + 3 < a.nb) ? m.JS[(k + 3) * 3 * J + e] : 0.f;
+        const float4 bb = reinterpret_cast<const float4*>(sbeta)[k >> 2];
+        v = fmaf(bb.x, j0, v); v = fmaf(bb.y, j1, v); v = fmaf(bb.z, j2, v); v = fmaf(bb.w, j3, v);
+      }
     }
     const int j = e / 3, c = e - 3 * j;
     jr[j * 4 + c] = v;
@@ -269,30 +277,48 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_fwd_kernel(DevModel m, Pose
     }
   }
   if (a.joints && a.joints_mode == 1) {
-    // joints_j = sum over coupled bones k of A_k [c0 + sum_m beta_m cm ; c0.w] + rowsum_j * trans
+    // joints_j = sum over coupled bones k of A_k [c0 + sum_m beta_m cm ; c0.w] + rowsum_j * trans, lane per
+    // (joint, bone) pair over the joint-sorted records (coalesced float4 table loads); the pairs of one joint
+    // are neighbouring lanes, folded by a segmented shuffle sum, run heads accumulate into sc (dead scales).
     f3 tr = mk3(0.f, 0.f, 0.f);
     if (a.trans) tr = ld3(a.trans + (long long)b * a.trans_stride);
     for (int j = l; j < J; j += 32) {
       const float rs = m.jreg_rowsum[j];
-      f3 acc = mk3(rs * tr.x, rs * tr.y, rs * tr.z);
-      for (int pi = m.pj_ptr[j]; pi < m.pj_ptr[j + 1]; ++pi) {
-        const int k = m.pj_bone[pi];
-        const float4 c0 = reinterpret_cast<const float4*>(m.pj_c0)[pi];
-        f3 q = mk3(c0.x, c0.y, c0.z);
-        const float* cm = m.pj_cm + (long long)pi * m.nB * 3;
-        for (int t = 0; t < a.nb; ++t) {
-          const float bt_ = sbeta[t];
-          q.x = fmaf(bt_, cm[3 * t], q.x); q.y = fmaf(bt_, cm[3 * t + 1], q.y); q.z = fmaf(bt_, cm[3 * t + 2], q.z);
-        }
-        m3 AR; f3 At;
-        ld_rec(X + k * 12, AR, At);
-        const f3 r = mul(AR, q);
-        acc.x += fmaf(At.x, c0.w, r.x);
-        acc.y += fmaf(At.y, c0.w, r.y);
-        acc.z += fmaf(At.z, c0.w, r.z);
-      }
-      st3(a.joints + ((long long)b * J + j) * 3, acc);
+      sc[j * 4 + 0] = rs * tr.x; sc[j * 4 + 1] = rs * tr.y; sc[j * 4 + 2] = rs * tr.z;
     }
+    __syncwarp();
+    const int NQ = m.pr_nq;
+    for (int s0 = 0; s0 < m.npairs_pad; s0 += 32) {
+      const float4* R4 = m.pjrec4 + (size_t)(s0 >> 5) * NQ * 32 + l;
+      const float4 h = R4[0], c0 = R4[32];
+      const int bone = __float_as_int(h.x), joint = __float_as_int(h.y);
+      f3 q = mk3(c0.x, c0.y, c0.z);
+      for (int t4 = 0; 4 * t4 < a.nb; ++t4) {
+        const float4 cx = R4[(2 + 3 * t4) * 32], cy = R4[(3 + 3 * t4) * 32], cz = R4[(4 + 3 * t4) * 32];
+        const float4 bb = reinterpret_cast<const float4*>(sbeta)[t4];
+        q.x = fmaf(bb.x, cx.x, fmaf(bb.y, cx.y, fmaf(bb.z, cx.z, fmaf(bb.w, cx.w, q.x))));
+        q.y = fmaf(bb.x, cy.x, fmaf(bb.y, cy.y, fmaf(bb.z, cy.z, fmaf(bb.w, cy.w, q.y))));
+        q.z = fmaf(bb.x, cz.x, fmaf(bb.y, cz.y, fmaf(bb.z, cz.z, fmaf(bb.w, cz.w, q.z))));
+      }
+      m3 AR; f3 At;
+      ld_rec(X + max(bone, 0) * 12, AR, At);
+      const f3 r = mul(AR, q);
+      float vx = fmaf(At.x, h.z, r.x), vy = fmaf(At.y, h.z, r.y), vz = fmaf(At.z, h.z, r.z);
+      if (bone < 0) { vx = 0.f; vy = 0.f; vz = 0.f; }
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int oj = __shfl_down_sync(0xffffffffu, joint, d);
+        const float ox = __shfl_down_sync(0xffffffffu, vx, d), oy = __shfl_down_sync(0xffffffffu, vy, d),
+                    oz = __shfl_down_sync(0xffffffffu, vz, d);
+        if ((l + d < 32) && oj == joint) { vx += ox; vy += oy; vz += oz; }
+      }
+      const int pjn = __shfl_up_sync(0xffffffffu, joint, 1);
+      if (bone >= 0 && (l == 0 || pjn != joint)) {   // one run head per joint and pass
+        sc[joint * 4 + 0] += vx; sc[joint * 4 + 1] += vy; sc[joint * 4 + 2] += vz;
+      }
+      __syncwarp();
+    }
+    for (int e = l; e < 3 * J; e += 32) a.joints[(long long)b * 3 * J + e] = sc[e + e / 3];
   }
 }
 
@@ -310,14 +336,16 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
   const int b = blockIdx.x * POSE_WPB + w;
   if (b >= a.B) return;
   const int J = m.J, nb = a.nb;
-  const int per = ((L.bwd_floats() + 32 * L.nbp) + 3) & ~3;
+  const int per = (L.bwd_floats() + 3) & ~3;
   float* sm = smem_pose + (size_t)w * per;
   float* X = sm + L.x();
   float* G = sm + L.g();
   float* jr = sm + L.jr();
   float* sbeta = sm + L.beta();
   float* rec = sm + L.rec();
-  float* accb = sm + L.bwd_floats();  // [32][nbp] lane-private dL/dbeta partials
+  float gbeta[16];   // lane-private dL/dbeta partials (the fused path serves nb <= 16)
+#pragma unroll
+  for (int k = 0; k < 16; ++k) gbeta[k] = 0.f;
   const bool prop = (a.flags & SMIL_F_PROPAGATE_SCALING) != 0;
   const bool rotmat = (a.flags & SMIL_F_THETA_IS_ROTMAT) != 0;
 
@@ -335,14 +363,25 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
 
   // ---- dL/dA per bone: dense buffer + slot partials of the skin pass (+ closed-form posed joints) --------
   f3 gtr = mk3(0.f, 0.f, 0.f);
-  for (int k = 0; k < nb; ++k) accb[l * L.nbp + k] = 0.f;
   for (int e = l; e < 3 * J; e += 32) {
     const int j = e / 3, r = e - 3 * j;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (a.gA_dense) acc = reinterpret_cast<const float4*>(a.gA_dense)[(long long)b * 3 * J + e];
     if (a.gA_slots) {
       const float4* sl = reinterpret_cast<const float4*>(a.gA_slots) + (long long)b * a.nslots * 3 + r;
-      for (int si = m.sb_ptr[j]; si < m.sb_ptr[j + 1]; ++si) {
+      int si = m.sb_ptr[j];
+      const int se = m.sb_ptr[j + 1];
+      for (; si + 3 < se; si += 4) {   // four independent loads in flight (the slots live in L2 / HBM)
+        const float4 t0 = sl[si * 3], t1 = sl[si * 3 + 3], t2 = sl[si * 3 + 6], t3 = sl[si * 3 + 9];
+        acc.x += (t0.x + t1.x) + (t2.x + t3.x); acc.y += (t0.y + t1.y) + (t2.y + t3.y);
+        acc.z += (t0.z + t1.z) + (t2.z + t3.z); acc.w += (t0.w + t1.w) + (t2.w + t3.w);
+      }
+      if (si + 1 < se) {
+        const float4 t0 = sl[si * 3], t1 = sl[si * 3 + 3];
+        acc.x += t0.x + t1.x; acc.y += t0.y + t1.y; acc.z += t0.z + t1.z; acc.w += t0.w + t1.w;
+        si += 2;
+      }
+      if (si < se) {
         const float4 t = sl[si * 3];
         acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
       }
@@ -361,23 +400,33 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
     // closed-form posed joints, joints_j = sum_k A_k [q_jk ; c0w_jk] with q_jk = c0_jk + sum_m beta_m cm_jkm:
     // lane per (joint, bone) pair in bone-sorted order, dL/dA_k = sum_j g_joints_j (x) [q_jk ; c0w_jk] by a
     // segmented shuffle reduction over the lanes that share a bone (fixed order, no atomics).
-    const int RP = m.pbrec_floats;
+    const int NQ = m.pr_nq;
     for (int s0 = 0; s0 < m.npairs_pad; s0 += 32) {
-      const float* pr = m.pbrec + (long long)(s0 + l) * RP;
-      const int bone = __float_as_int(pr[0]);
+      const float4* R4 = m.pbrec4 + (size_t)(s0 >> 5) * NQ * 32 + l;   // coalesced float4 table loads
+      const float4 h = R4[0], c0 = R4[32];
+      const int bone = __float_as_int(h.x);
       const bool real = bone >= 0;
       const int kb = real ? bone : 0;
       f3 gj = mk3(0.f, 0.f, 0.f);
-      if (real) gj = ld3(a.g_joints + ((long long)b * J + __float_as_int(pr[1])) * 3);
+      if (real) gj = ld3(a.g_joints + ((long long)b * J + __float_as_int(h.y)) * 3);
       const float* Gk = G + kb * 12;
       const f3 tg = mk3(fmaf(Gk[0], gj.x, fmaf(Gk[4], gj.y, Gk[8] * gj.z)), fmaf(Gk[1], gj.x, fmaf(Gk[5], gj.y, Gk[9] * gj.z)),
                         fmaf(Gk[2], gj.x, fmaf(Gk[6], gj.y, Gk[10] * gj.z)));   // GR_k^T g_joints_j
-      f3 q = mk3(pr[2], pr[3], pr[4]);
-      const float c0w = pr[5];
-      for (int t = 0; t < nb; ++t) {
-        const float cx = pr[6 + 3 * t], cy = pr[7 + 3 * t], cz = pr[8 + 3 * t], bt_ = sbeta[t];
-        q.x = fmaf(bt_, cx, q.x); q.y = fmaf(bt_, cy, q.y); q.z = fmaf(bt_, cz, q.z);
-        accb[l * L.nbp + t] += fmaf(tg.x, cx, fmaf(tg.y, cy, tg.z * cz));
+      f3 q = mk3(c0.x, c0.y, c0.z);
+      const float c0w = h.z;
+#pragma unroll
+      for (int t4 = 0; t4 < 4; ++t4) {
+        if (4 * t4 < nb) {
+          const float4 cx = R4[(2 + 3 * t4) * 32], cy = R4[(3 + 3 * t4) * 32], cz = R4[(4 + 3 * t4) * 32];
+          const float4 bb = reinterpret_cast<const float4*>(sbeta)[t4];
+          q.x = fmaf(bb.x, cx.x, fmaf(bb.y, cx.y, fmaf(bb.z, cx.z, fmaf(bb.w, cx.w, q.x))));
+          q.y = fmaf(bb.x, cy.x, fmaf(bb.y, cy.y, fmaf(bb.z, cy.z, fmaf(bb.w, cy.w, q.y))));
+          q.z = fmaf(bb.x, cz.x, fmaf(bb.y, cz.y, fmaf(bb.z, cz.z, fmaf(bb.w, cz.w, q.z))));
+          gbeta[4 * t4 + 0] += fmaf(tg.x, cx.x, fmaf(tg.y, cy.x, tg.z * cz.x));
+          gbeta[4 * t4 + 1] += fmaf(tg.x, cx.y, fmaf(tg.y, cy.y, tg.z * cz.y));
+          gbeta[4 * t4 + 2] += fmaf(tg.x, cx.z, fmaf(tg.y, cy.z, tg.z * cz.z));
+          gbeta[4 * t4 + 3] += fmaf(tg.x, cx.w, fmaf(tg.y, cy.w, tg.z * cz.w));
+        }
       }
       float v[12];
       v[0] = gj.x * q.x; v[1] = gj.x * q.y; v[2] = gj.x * q.z; v[3] = gj.x * c0w;
@@ -548,14 +597,19 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
       if (a.jrest_closed) {   // rest joints JT + beta JS: dL/dbeta_k += JS_k . dL/dJrest, all k in one pass over the joints
         for (int e = l; e < 3 * J; e += 32) {
           const float gje = jr[e + e / 3];
-          for (int k = 0; k < nb; ++k) accb[l * L.nbp + k] = fmaf(m.JS[(long long)k * 3 * J + e], gje, accb[l * L.nbp + k]);
+#pragma unroll
+          for (int k = 0; k < 16; ++k)
+            if (k < nb) gbeta[k] = fmaf(m.JS[(long long)k * 3 * J + e], gje, gbeta[k]);
         }
       }
-      for (int k = 0; k < nb; ++k) {
-        float s = accb[l * L.nbp + k];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (l == k) mine = s;
+      for (int k = 0; k < 16; ++k) {
+        if (k < nb) {
+          float s = gbeta[k];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+          if (l == k) mine = s;
+        }
       }
       if (l < nb) a.g_beta[(long long)b * nb + l] = mine + part;
     }

@@ -1,7 +1,9 @@
 // C-ABI entry points of the B200-native SMAL/SMIL hot path (see include/smil_b200.h).
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -shared -Xcompiler -fPIC
+#include <algorithm>
 #include <atomic>
 #include <cstdlib>
+#include <cstring>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -93,7 +95,7 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
   L.J = m.J;
   L.nbp = (std::max(a.nb, 1) + 3) & ~3;
   const int pairs_mode = backward && a.joints_mode == 1 && a.g_joints && !a.joints_in_skin;
-  const int fl = backward ? L.bwd_floats() + 32 * L.nbp : L.fwd_floats();
+  const int fl = backward ? L.bwd_floats() : L.fwd_floats();
   const size_t smem = (size_t)((fl + 3) & ~3) * sizeof(float) * POSE_WPB;
   const int grid = (a.B + POSE_WPB - 1) / POSE_WPB;
   int rc = SMIL_OK;
@@ -375,10 +377,42 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   ap.add(s->pj_joint, V ? np : 0, &d.pj_joint);
   ap.add(s->pj_c0, V ? np * 4 : 0, &d.pj_c0);
   ap.add(s->pj_cm, V ? np * std::max<size_t>(nB, 1) * 3 : 0, &d.pj_cm);
+  d.nbp4 = (std::max(d.nB, 1) + 3) & ~3;
+  d.pr_nq = 2 + 3 * d.nbp4 / 4;
+  d.npairs_pad = (d.npairs + 31) / 32 * 32;
+  std::vector<float> pjrec4, pbrec4;
+  if (V && d.npairs > 0 && s->pj_bone && s->pj_joint && s->pj_c0 && s->pj_cm) {
+    // order[] = position -> pair index; joint-sorted is the order the packer emits, bone-sorted is a stable sort of it
+    std::vector<int> by_joint(d.npairs), by_bone(d.npairs);
+    for (int i = 0; i < d.npairs; ++i) by_joint[i] = by_bone[i] = i;
+    std::stable_sort(by_bone.begin(), by_bone.end(), [&](int x, int y) { return s->pj_bone[x] < s->pj_bone[y]; });
+    auto fill = [&](const std::vector<int>& order, std::vector<float>& out) {
+      const size_t nq = d.pr_nq;
+      out.assign((size_t)d.npairs_pad * nq * 4, 0.f);
+      for (int pos = 0; pos < d.npairs_pad; ++pos) {
+        float* base = out.data() + ((size_t)(pos / 32) * nq * 32 + (pos % 32)) * 4;   // float4 q of this lane: base + q*128
+        int bone = -1, joint = 0;
+        if (pos < d.npairs) {
+          const int pi = order[pos];
+          bone = s->pj_bone[pi]; joint = s->pj_joint[pi];
+          base[2] = s->pj_c0[pi * 4 + 3];
+          for (int c = 0; c < 3; ++c) base[128 + c] = s->pj_c0[pi * 4 + c];
+          for (size_t t = 0; t < nB; ++t)
+            for (size_t c = 0; c < 3; ++c)
+              base[(2 + 3 * (t / 4) + c) * 128 + (t % 4)] = s->pj_cm[((size_t)pi * nB + t) * 3 + c];
+        }
+        memcpy(base + 0, &bone, 4);
+        memcpy(base + 1, &joint, 4);
+      }
+    };
+    fill(by_joint, pjrec4);
+    fill(by_bone, pbrec4);
+    ap.add(reinterpret_cast<const float4*>(pjrec4.data()), pjrec4.size() / 4, &d.pjrec4);
+    ap.add(reinterpret_cast<const float4*>(pbrec4.data()), pbrec4.size() / 4, &d.pbrec4);
+  }
   ap.add(s->pb_ptr, V ? J + 1 : 0, &d.pb_ptr);
   ap.add(s->pb_pair, V ? np : 0, &d.pb_pair);
   d.pbrec_floats = (6 + 3 * d.nB + 3) / 4 * 4;
-  d.npairs_pad = (d.npairs + 31) / 32 * 32;
   ap.add(s->pbrec, (V && s->pbrec) ? (size_t)std::max(d.npairs_pad, 1) * d.pbrec_floats : 0, &d.pbrec);
   ap.add(s->vconst, (3 + 3 * nB) * (size_t)d.v_pad, &d.vconst);
   ap.add(s->ell_idx, K * (size_t)d.v_pad, &d.ell_idx);

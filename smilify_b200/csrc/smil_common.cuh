@@ -67,6 +67,12 @@ struct DevModel {
   const float *JT, *JS, *jreg_rowsum;
   const int *pj_ptr, *pj_bone, *pj_joint;
   const float *pj_c0, *pj_cm;
+  // joint-bone coupling records for the lane-per-pair passes, SoA by float4 so that a warp's loads are coalesced:
+  //   rec4[(s0/32 * pr_nq + q) * 32 + lane], q0 = (bone bits | joint bits | c0.w | 0), q1 = (c0.xyz, 0),
+  //   q(2+3t4 .. 4+3t4) = (cm_x | cm_y | cm_z)[4 t4 .. 4 t4 + 3];  padding records carry bone -1 and zeros.
+  const float4* pjrec4;  // sorted by joint (forward: segmented sum per joint)
+  const float4* pbrec4;  // sorted by bone  (backward: segmented sum per bone)
+  int nbp4, pr_nq;       // beta axis padded to a multiple of 4; float4s per record = 2 + 3 nbp4 / 4
   const int *pb_ptr, *pb_pair;
   const float* pbrec;
   int pbrec_floats, npairs_pad;
