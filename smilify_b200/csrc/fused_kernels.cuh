@@ -70,7 +70,7 @@ struct SkinFwdArgs {
 };
 
 __host__ __device__ inline int skin_fwd_stage_floats(int chunk) { return ((3 * chunk + 4) + 3) & ~3; }
-__host__ __device__ inline int pair_block_floats(int J, int nbt_model) { return 24 * J + 2 * ((nbt_model + 1) & ~1) + 8; }
+__host__ __device__ inline int pair_block_floats(int J, int nbt_model) { return PPB * J + 2 * ((nbt_model + 1) & ~1) + 8; }
 __host__ inline size_t skin_fwd_smem_bytes(int GP, int blk, int chunk, bool direct) {
   return 32 + 2ull * GP * blk * 4 + (direct ? 0 : (size_t)SKIN_FWD_STAGES * 4 * skin_fwd_stage_floats(chunk) * 4);
 }
@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
   for (int k = 0; k < K; ++k) {
     const float w = (k < m.K) ? m.ell_w[(long long)k * m.v_pad + v] : 0.f;
     w2[k] = make_float2(w, w);
-    bo[k] = (k < m.K) ? m.ell_idx[(long long)k * m.v_pad + v] * 24 : 0;
+    bo[k] = (k < m.K) ? m.ell_idx[(long long)k * m.v_pad + v] * PPB : 0;
   }
   const int nv = min(C, V - chunk * C);
   const int n = 3 * nv;
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
   const bool second = (warp & 1) != 0;
   float* const ship_dst = (warp < 2) ? a.verts : a.v_shaped;
   const long long off_step = 6LL * V;
-  const int NB2M = (a.blk - 24 * J - 8) >> 1;   // beta pairs per block (model-level padding)
+  const int NB2M = (a.blk - PPB * J - 8) >> 1;   // beta pairs per block (model-level padding)
 
   int sidx = 0, it = 0;
   for (int grp = blockIdx.y; grp < ngroups; grp += gridDim.y, ++it) {
@@ -169,8 +169,8 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
     for (int g = 0; g < GPn; ++g) {
       float* st = sStage + sidx * (4 * SF);
       const float* Ag = blkp;
-      const float4* bp4 = reinterpret_cast<const float4*>(blkp + 24 * J);
-      const float4* tp4 = reinterpret_cast<const float4*>(blkp + 24 * J + 2 * NB2M);
+      const float4* bp4 = reinterpret_cast<const float4*>(blkp + PPB * J);
+      const float4* tp4 = reinterpret_cast<const float4*>(blkp + PPB * J + 2 * NB2M);
       // shape blend for both samples
       float2 vs0 = T2[0], vs1 = T2[1], vs2 = T2[2];
 #pragma unroll
@@ -252,6 +252,183 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
 }
 
 // =====================================================================================================
+// forward, lane = sample
+// =====================================================================================================
+// The thread-per-vertex pass above is bounded by shared-memory wavefronts: every (vertex, sample pair) gathers
+// 24 K floats of bone transforms at per-thread addresses (ncu r01 v2: 72 % of the smem pipe, 2.8 TB/s of
+// DRAM writes).  Here the roles are swapped: a warp owns 32 SAMPLES and walks the vertices of a tile; the
+// bone transforms of the current run live in REGISTERS (loaded coalesced from the sample-minor copy AT the
+// pose pass writes), the per-vertex constants arrive as warp-uniform float4 shared-memory loads (one wavefront
+// each), and the results are transposed through a per-warp staging tile so that every row leaves as
+// contiguous 8-byte-per-lane stores.  Shared-memory wavefronts per (vertex, 32 samples): ~6 constant loads +
+// 12 staging stores + 6 staging reads, against ~46 for the pass above.
+constexpr int F3_WARPS = 4;                      // warps per CTA: same vertex tile, different sample groups
+constexpr int F3_RS = 3 * F3_TILE + 2;           // staging row stride (floats): 8-byte aligned rows, == 2 (mod 16)
+
+struct SkinFwd3Args {
+  int B, nb;
+  const float* beta;  long long beta_stride;
+  const float* trans; long long trans_stride;
+  const float* AT;            // [ceil(B/32)][J][12][32]
+  float* verts;               // [B][V][3]
+  float* v_shaped;            // [B][V][3]
+};
+
+__host__ inline size_t skin_fwd3_smem_bytes(int recf, int max_runs) {
+  return (size_t)F3_TILE * recf * 4 + (size_t)((max_runs + 3) & ~3) * 16 + (size_t)F3_WARPS * 2 * 32 * F3_RS * 4;
+}
+
+template <int NBT>
+__global__ void __launch_bounds__(32 * F3_WARPS, 4) skin_fwd3_kernel(DevModel m, SkinFwd3Args a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int RECF = ((3 + 3 * NBT + 3) + 3) & ~3;
+  constexpr int NQ = RECF / 4;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tile = blockIdx.x;
+  const int V = m.V, J = m.J;
+  float4* sRec = reinterpret_cast<float4*>(smem_raw);                       // [F3_TILE][NQ]
+  const int run0 = m.f3_tile_run_ptr[tile], nrun = m.f3_tile_run_ptr[tile + 1] - run0;
+  int4* sRun = reinterpret_cast<int4*>(sRec + F3_TILE * NQ);                // [max_runs]
+  float* sStage = reinterpret_cast<float*>(sRun + ((m.f3_max_runs + 3) & ~3)) + (size_t)warp * 2 * 32 * F3_RS;
+  float* stV = sStage;                 // [32 samples][F3_RS] posed vertices of the tile
+  float* stS = sStage + 32 * F3_RS;    // [32 samples][F3_RS] shaped vertices
+  const int v0 = tile * F3_TILE;
+  const int nv = min(F3_TILE, V - v0);
+  {
+    const float4* src = reinterpret_cast<const float4*>(m.f3_rec) + (size_t)tile * F3_TILE * NQ;
+    for (int i = tid; i < nv * NQ; i += 32 * F3_WARPS) sRec[i] = src[i];
+    for (int i = tid; i < nrun; i += 32 * F3_WARPS) sRun[i] = m.f3_runs[run0 + i];
+  }
+  __syncthreads();
+
+  const int ngroups = (a.B + 31) >> 5;
+  // copy-out geometry, fixed for the tile: a step ships `rps` whole rows as float2, lane i (+32, +64) of the
+  // step -> (row inside the step, column)
+  const int rowf2 = (3 * nv) >> 1;               // float2 per row (3 nv is even for every tile but possibly the last)
+  const bool even_rows = ((3 * nv) & 1) == 0 && ((3LL * V) & 1) == 0;
+  const int rps = even_rows ? max(1, min(32, 96 / max(rowf2, 1))) : 1;
+  int so[3], go[3], rr[3];
+#pragma unroll
+  for (int q = 0; q < 3; ++q) {
+    const int i = lane + 32 * q;
+    const int r_ = i / max(rowf2, 1), c2 = i - r_ * rowf2;
+    rr[q] = (r_ < rps) ? r_ : 1 << 20;   // lanes beyond the step's rows never pass the row test
+    so[q] = r_ * F3_RS + 2 * c2;
+    go[q] = r_ * 3 * V + 2 * c2;
+  }
+  const int gstep = gridDim.y * F3_WARPS;
+  int grp = blockIdx.y * F3_WARPS + warp;
+  // per-sample operands of a group are fetched one group ahead (they come from HBM)
+  float beta_n[NBT], tn0 = 0.f, tn1 = 0.f, tn2 = 0.f;
+  auto fetch = [&](int g_) {
+    const int bb = min((g_ << 5) + lane, a.B - 1);
+#pragma unroll
+    for (int k = 0; k < NBT; ++k) beta_n[k] = (k < a.nb) ? a.beta[(long long)bb * a.beta_stride + k] : 0.f;
+    if (a.trans) { const float* tp = a.trans + (long long)bb * a.trans_stride; tn0 = tp[0]; tn1 = tp[1]; tn2 = tp[2]; }
+  };
+  if (grp < ngroups) fetch(grp);
+  for (; grp < ngroups; grp += gstep) {
+    float beta[NBT];
+#pragma unroll
+    for (int k = 0; k < NBT; ++k) beta[k] = beta_n[k];
+    const float t0 = tn0, t1 = tn1, t2 = tn2;
+    if (grp + gstep < ngroups) fetch(grp + gstep);
+    const float* ATg = a.AT + (size_t)grp * 12 * J * 32 + lane;
+    float A0[12], A1[12], An[12];   // An: second bone of the NEXT run (it changes with almost every run)
+    int cur0 = -1;
+    if (nrun > 0 && sRun[0].y >= 0) {
+#pragma unroll
+      for (int e = 0; e < 12; ++e) An[e] = ATg[(size_t)(sRun[0].y + e) * 32];
+    }
+    for (int r = 0; r < nrun; ++r) {
+      const int4 rd = sRun[r];
+      if (rd.x != cur0) {   // runs are sorted by (bone0, bone1): bone0 changes rarely
+#pragma unroll
+        for (int e = 0; e < 12; ++e) A0[e] = ATg[(size_t)(rd.x + e) * 32];
+        cur0 = rd.x;
+      }
+      const bool two = rd.y >= 0;
+      if (two) {
+#pragma unroll
+        for (int e = 0; e < 12; ++e) A1[e] = An[e];
+      }
+      if (r + 1 < nrun) {
+        const int ny = sRun[r + 1].y;
+        if (ny >= 0) {
+#pragma unroll
+          for (int e = 0; e < 12; ++e) An[e] = ATg[(size_t)(ny + e) * 32];
+        }
+      }
+      float4 nx[NQ];   // record of the next slot, loaded one slot ahead (warp-uniform shared loads)
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) nx[q] = sRec[rd.z * NQ + q];
+      for (int s = rd.z; s < rd.z + rd.w; ++s) {
+        float c[RECF];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+          c[4 * q] = nx[q].x; c[4 * q + 1] = nx[q].y; c[4 * q + 2] = nx[q].z; c[4 * q + 3] = nx[q].w;
+        }
+        if (s + 1 < rd.z + rd.w) {
+#pragma unroll
+          for (int q = 0; q < NQ; ++q) nx[q] = sRec[(s + 1) * NQ + q];
+        }
+        float x = c[0], y = c[1], z = c[2];
+#pragma unroll
+        for (int k = 0; k < NBT; ++k) {
+          x = fmaf(beta[k], c[3 + 3 * k], x); y = fmaf(beta[k], c[4 + 3 * k], y); z = fmaf(beta[k], c[5 + 3 * k], z);
+        }
+        const float w0 = c[3 + 3 * NBT], w1 = c[4 + 3 * NBT];
+        const int lv3 = __float_as_int(c[5 + 3 * NBT]);
+        float p0 = fmaf(A0[0], x, fmaf(A0[1], y, fmaf(A0[2], z, A0[3])));
+        float p1 = fmaf(A0[4], x, fmaf(A0[5], y, fmaf(A0[6], z, A0[7])));
+        float p2 = fmaf(A0[8], x, fmaf(A0[9], y, fmaf(A0[10], z, A0[11])));
+        float o0 = fmaf(w0, p0, t0), o1 = fmaf(w0, p1, t1), o2 = fmaf(w0, p2, t2);
+        if (two) {
+          p0 = fmaf(A1[0], x, fmaf(A1[1], y, fmaf(A1[2], z, A1[3])));
+          p1 = fmaf(A1[4], x, fmaf(A1[5], y, fmaf(A1[6], z, A1[7])));
+          p2 = fmaf(A1[8], x, fmaf(A1[9], y, fmaf(A1[10], z, A1[11])));
+          o0 = fmaf(w1, p0, o0); o1 = fmaf(w1, p1, o1); o2 = fmaf(w1, p2, o2);
+        }
+        float* dv = stV + lane * F3_RS + lv3;
+        float* ds = stS + lane * F3_RS + lv3;
+        dv[0] = o0; dv[1] = o1; dv[2] = o2;
+        ds[0] = x;  ds[1] = y;  ds[2] = z;
+      }
+    }
+    __syncwarp();
+    // ---- copy-out: row r of the staging tile -> verts / v_shaped [grp*32 + r][v0 .. v0+nv) ----------------
+    const int rows = min(32, a.B - (grp << 5));
+    const long long gbase = ((long long)(grp << 5) * V + v0) * 3;
+    if (even_rows) {
+      const float* sv = stV;
+      const float* ss = stS;
+      float* gv = a.verts + gbase;
+      float* gs = a.v_shaped + gbase;
+      for (int rp = 0; rp < rows; rp += rps) {
+        float2 bv[3], bs[3];
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+          if (rp + rr[q] < rows) { bv[q] = *reinterpret_cast<const float2*>(sv + so[q]); bs[q] = *reinterpret_cast<const float2*>(ss + so[q]); }
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+          if (rp + rr[q] < rows) { *reinterpret_cast<float2*>(gv + go[q]) = bv[q]; *reinterpret_cast<float2*>(gs + go[q]) = bs[q]; }
+        sv += rps * F3_RS; ss += rps * F3_RS;
+        gv += (long long)rps * 3 * V; gs += (long long)rps * 3 * V;
+      }
+    } else {
+      const int n = 3 * nv;
+      for (int r_ = 0; r_ < rows; ++r_)
+        for (int i = lane; i < n; i += 32) {
+          const long long g_ = gbase + (long long)r_ * 3 * V + i;
+          a.verts[g_] = stV[r_ * F3_RS + i];
+          a.v_shaped[g_] = stS[r_ * F3_RS + i];
+        }
+    }
+    __syncwarp();
+  }
+}
+
+// =====================================================================================================
 // backward
 // =====================================================================================================
 // Item-major, lane = sample (8 samples x 4 item streams per warp), two items per step packed into f32x2
@@ -304,7 +481,7 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
   float* sRec = reinterpret_cast<float*>(smem_raw + 32);   // [max_pairs][REC]
   float* sRows = sRec + (size_t)a.max_tile_pairs * REC;    // [2][G][RF]
   float* sRed = sRows + (size_t)STAGES * SKIN_BWD_G * RF;  // [4 warps][G][NBT+4]
-  int4* sUnit = reinterpret_cast<int4*>(sRed + 4ull * SKIN_BWD_G * (NBT + 4));   // [MAXU] (bone*24, first pair, end pair, slot)
+  int4* sUnit = reinterpret_cast<int4*>(sRed + 4ull * SKIN_BWD_G * (NBT + 4));   // [MAXU] (bone*PPB, first pair, end pair, slot)
 
   const int u_beg = m.tile_unit_ptr[ti], u_end = m.tile_unit_ptr[ti + 1];
   const int pr_base = m.unit_ptr[u_beg], pr_cnt = m.unit_ptr[u_end] - pr_base;
@@ -328,7 +505,7 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
     for (int i = tid; i < pr_cnt * (REC >> 2); i += 128) dst[i] = src[i];
     for (int i = tid; i < u_end - u_beg; i += 128) {   // unit descriptors in the order the warps walk them
       const int u = m.warp_unit[wu_base + i];
-      sUnit[i] = make_int4(m.unit_bone[u] * 24, m.unit_ptr[u] - pr_base, m.unit_ptr[u + 1] - pr_base, m.unit_slot[u]);
+      sUnit[i] = make_int4(m.unit_bone[u] * PPB, m.unit_ptr[u] - pr_base, m.unit_ptr[u + 1] - pr_base, m.unit_slot[u]);
     }
   }
   __syncthreads();

@@ -92,7 +92,7 @@ __global__ void deinterleave_A_kernel(int B, int J, int blk, const float* __rest
   const long long per = 12LL * J;
   if (i >= (long long)B * per) return;
   const long long b = i / per, e = i - b * per;
-  A[i] = pp[(b >> 1) * blk + 2 * e + (b & 1)];
+  A[i] = pp[(b >> 1) * blk + 2 * e + (e / 12) * (PPB - 24) + (b & 1)];
 }
 
 // ---- backward -------------------------------------------------------------------------------------

@@ -43,6 +43,7 @@ struct PoseArgs {
   float* pp;      // [ceil(B/2)][pp_blk] per-pair parameter blocks for the fused skinning passes, or null:
                   //   A2 [J][12][2] | beta2 [NB2][2] | trans2 [4][2], every entry interleaved (sample 2p, sample 2p+1)
   int pp_blk;     // floats per block (fused_kernels.cuh::pair_block_floats)
+  float* AT;      // [ceil(B/32)][J][12][32] the same transforms sample-minor (lane-per-sample forward skin pass), or null
   float* newJ;    // [B][J][3] or null
   float* joints;  // [B][J][3] or null
   // backward inputs
@@ -255,16 +256,25 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_fwd_kernel(DevModel m, Pose
     const float* X1 = smem_pose + wstride + L.x();
     float* blk = a.pp + (long long)blockIdx.x * a.pp_blk;
     float4* out = reinterpret_cast<float4*>(blk);
-    for (int i = threadIdx.x; i < 6 * J; i += POSE_THREADS) out[i] = make_float4(X0[2 * i], X1[2 * i], X0[2 * i + 1], X1[2 * i + 1]);
-    const int nb2 = (a.pp_blk - 24 * J - 8) >> 1;
+    for (int i = threadIdx.x; i < 6 * J; i += POSE_THREADS) {
+      const int j = i / 6;
+      out[i + j * (PPB / 4 - 6)] = make_float4(X0[2 * i], X1[2 * i], X0[2 * i + 1], X1[2 * i + 1]);
+    }
+    if (a.AT) {   // the CTA's two samples are neighbours on the sample-minor axis: one 8-byte store per entry
+      const int b0 = blockIdx.x * 2;
+      float* at = a.AT + (size_t)(b0 >> 5) * 12 * J * 32 + (b0 & 31);
+      for (int i = threadIdx.x; i < 12 * J; i += POSE_THREADS)
+        *reinterpret_cast<float2*>(at + (size_t)i * 32) = make_float2(X0[i], X1[i]);
+    }
+    const int nb2 = (a.pp_blk - PPB * J - 8) >> 1;
     for (int i = threadIdx.x; i < 2 * nb2; i += POSE_THREADS) {
       const int k = i >> 1, h = i & 1;
-      blk[24 * J + i] = (k < a.nb) ? smem_pose[h * wstride + L.beta() + k] : 0.f;
+      blk[PPB * J + i] = (k < a.nb) ? smem_pose[h * wstride + L.beta() + k] : 0.f;
     }
     for (int i = threadIdx.x; i < 8; i += POSE_THREADS) {
       const int c = i >> 1, h = i & 1;
       const int bs = min(blockIdx.x * 2 + h, a.B - 1);
-      blk[24 * J + 2 * nb2 + i] = (a.trans && c < 3) ? a.trans[(long long)bs * a.trans_stride + c] : 0.f;
+      blk[PPB * J + 2 * nb2 + i] = (a.trans && c < 3) ? a.trans[(long long)bs * a.trans_stride + c] : 0.f;
     }
   }
   if (!live) return;
@@ -355,7 +365,7 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
     __syncwarp();
   } else if (a.pp_saved) {
     const float* src = a.pp_saved + (long long)(b >> 1) * a.pp_blk + (b & 1);
-    for (int e = l; e < 12 * J; e += 32) G[e] = src[2 * e];
+    for (int e = l; e < 12 * J; e += 32) G[e] = src[2 * e + (e / 12) * (PPB - 24)];
     __syncwarp();
   } else {
     pose_walk(m, X, G, l);

@@ -30,6 +30,9 @@ int g_fwd_gp = 0;   // tuning override (SMIL_FWD_GP): sample pairs per TMA group
 int g_fwd_direct = 0;  // tuning override (SMIL_FWD_DIRECT): register -> global stores instead of the TMA staging ring
 int g_bwd_stages = 1;  // SMIL_BWD_STAGES: 1 = single-buffered g_verts rows (more CTAs per SM), 2 = double-buffered
 int g_bwd_cps = 0;     // SMIL_BWD_CPS
+int g_fwd_v3 = 0;      // SMIL_FWD_V3=1: lane-per-sample forward skin pass (K <= 2 rigs) instead of the thread-per-vertex pass.
+                       // Measured on B200 (STICK, B=4096): 98 us vs 85 us, plus 9 us in the pose pass for the sample-minor
+                       // copy of the transforms, so it is off by default; kept as the evaluated alternative.
 int g_fwd_cps = 0;  // tuning override (SMIL_FWD_CPS): resident CTAs per SM the forward grid is sized for
 std::mutex g_prof_mu;
 std::vector<ProfSlot> g_prof_slots;   // event pairs, created by smil_profile_enable
@@ -185,6 +188,44 @@ int launch_skin_bwd_inst2(const DevModel& m, const SkinBwdArgs& a, cudaStream_t 
   return SMIL_OK;
 }
 template <int NBT>
+int launch_skin_fwd3_inst(const DevModel& m, const SkinFwd3Args& a, cudaStream_t st) {
+  const size_t smem = skin_fwd3_smem_bytes(m.f3_recf, m.f3_max_runs);
+  int rc = set_smem(skin_fwd3_kernel<NBT>, smem);
+  if (rc != SMIL_OK) return rc;
+  static thread_local size_t occ_smem = 0;
+  static thread_local int occ = 0;
+  if (occ_smem != smem) {
+    SMIL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, skin_fwd3_kernel<NBT>, 32 * F3_WARPS, smem));
+    occ_smem = smem;
+  }
+  // persistent CTAs, one wave: a CTA keeps its tile's constants and walks its share of the 32-sample groups
+  const int ngroups = (a.B + 31) / 32;
+  const int ymax = (ngroups + F3_WARPS - 1) / F3_WARPS;
+  const int cps = g_fwd_cps > 0 ? std::min(g_fwd_cps, std::max(occ, 1)) : std::max(occ, 1);
+  const int Y = std::max(1, std::min(ymax, (m.sm_count * cps) / std::max(m.f3_ntile, 1)));
+  dim3 grid(m.f3_ntile, Y);
+  prof_begin("skin_fwd_kernel", st);
+  skin_fwd3_kernel<NBT><<<grid, 32 * F3_WARPS, smem, st>>>(m, a);
+  SMIL_LAUNCH_CHECK("skin_fwd3_kernel");
+  return SMIL_OK;
+}
+int launch_skin_fwd3(const DevModel& m, const SkinFwd3Args& a, cudaStream_t st) {
+  switch (nbt_of(a.nb > 0 ? std::max(a.nb, m.nB) : m.nB)) {
+    case 1: return launch_skin_fwd3_inst<1>(m, a, st);
+    case 2: return launch_skin_fwd3_inst<2>(m, a, st);
+    case 3: return launch_skin_fwd3_inst<3>(m, a, st);
+    case 4: return launch_skin_fwd3_inst<4>(m, a, st);
+    case 5: return launch_skin_fwd3_inst<5>(m, a, st);
+    case 6: return launch_skin_fwd3_inst<6>(m, a, st);
+    case 8: return launch_skin_fwd3_inst<8>(m, a, st);
+    case 10: return launch_skin_fwd3_inst<10>(m, a, st);
+    case 13: return launch_skin_fwd3_inst<13>(m, a, st);
+    case 16: return launch_skin_fwd3_inst<16>(m, a, st);
+  }
+  return fail(SMIL_EUNSUPPORTED, "lane-per-sample forward: %d betas not covered", m.nB);
+}
+
+template <int NBT>
 int launch_skin_bwd_inst(const DevModel& m, const SkinBwdArgs& a, cudaStream_t st) {
   if (g_bwd_stages == 1) return launch_skin_bwd_inst2<NBT, 1>(m, a, st);
   return launch_skin_bwd_inst2<NBT, 2>(m, a, st);
@@ -235,9 +276,12 @@ int make_plan(const DevModel& m, const SmilFwdArgs& f, Plan* p) {
 // saved = bone transforms (fused path: pair-interleaved, ceil(B/2) pairs; generic path: [B][J][12]) + rest joints
 int pair_blk(const DevModel& m) { return pair_block_floats(m.J, std::max(nbt_of(m.nB), 1)); }
 size_t saved_A_bytes(const DevModel& m, int B) {
-  return align_up((size_t)((B + 1) / 2) * std::max(pair_blk(m), 24 * m.J) * 4, 256);
+  return align_up((size_t)((B + 1) / 2) * std::max(pair_blk(m), PPB * m.J) * 4, 256);
 }
-size_t saved_bytes_for(const DevModel& m, int B) { return saved_A_bytes(m, B) + (size_t)B * m.J * 3 * 4; }
+size_t saved_jrest_bytes(const DevModel& m, int B) { return align_up((size_t)B * m.J * 3 * 4, 256); }
+// sample-minor copy of the bone transforms for the lane-per-sample forward skin pass: [ceil(B/32)][J][12][32]
+size_t saved_AT_bytes(const DevModel& m, int B) { return m.f3_ok ? (size_t)((B + 31) / 32) * m.J * 12 * 32 * 4 : 0; }
+size_t saved_bytes_for(const DevModel& m, int B) { return saved_A_bytes(m, B) + saved_jrest_bytes(m, B) + saved_AT_bytes(m, B); }
 
 PoseArgs base_pose_args(const DevModel& m, const SmilFwdArgs& f, const Plan& p) {
   PoseArgs a;
@@ -347,6 +391,7 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   if (const char* e = getenv("SMIL_FWD_CPS")) g_fwd_cps = atoi(e);
   if (const char* e = getenv("SMIL_BWD_STAGES")) g_bwd_stages = atoi(e);
   if (const char* e = getenv("SMIL_BWD_CPS")) g_bwd_cps = atoi(e);
+  if (const char* e = getenv("SMIL_FWD_V3")) g_fwd_v3 = atoi(e);
   if (const char* e = getenv("SMIL_FWD_DIRECT")) g_fwd_direct = atoi(e);
   SMIL_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, s->device));
 
@@ -409,6 +454,54 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
     fill(by_bone, pbrec4);
     ap.add(reinterpret_cast<const float4*>(pjrec4.data()), pjrec4.size() / 4, &d.pjrec4);
     ap.add(reinterpret_cast<const float4*>(pbrec4.data()), pbrec4.size() / 4, &d.pbrec4);
+  }
+  // ---- tables of the lane-per-sample forward skin pass (K <= 2 rigs) ---------------------------------
+  std::vector<float> f3rec;
+  std::vector<int> f3runs, f3ptr;
+  d.f3_ok = 0;
+  if (V && K <= 2 && nbt_of(d.nB) > 0 && s->v_template && s->skin_idx && s->skin_w && (nB == 0 || s->shapedirs)) {
+    const int NBTm = std::max(nbt_of(d.nB), 1);
+    d.f3_recf = ((3 + 3 * NBTm + 3) + 3) & ~3;
+    d.f3_ntile = (int)((V + F3_TILE - 1) / F3_TILE);
+    f3rec.assign((size_t)d.f3_ntile * F3_TILE * d.f3_recf, 0.f);
+    f3ptr.push_back(0);
+    d.f3_max_runs = 0;
+    for (int t = 0; t < d.f3_ntile; ++t) {
+      const int v0 = t * F3_TILE, v1 = std::min<int>((int)V, v0 + F3_TILE);
+      struct Key { int b0, b1, v; };
+      std::vector<Key> ks;
+      for (int v = v0; v < v1; ++v) {
+        int b0 = s->skin_idx[v * K], b1 = -1;
+        if (K > 1 && s->skin_w[v * K + 1] != 0.f) b1 = s->skin_idx[v * K + 1];
+        ks.push_back({b0, b1, v});
+      }
+      std::sort(ks.begin(), ks.end(), [](const Key& x, const Key& y) {
+        return x.b0 != y.b0 ? x.b0 < y.b0 : (x.b1 != y.b1 ? x.b1 < y.b1 : x.v < y.v);
+      });
+      int nruns = 0;
+      for (size_t i = 0; i < ks.size(); ++i) {
+        const int v = ks[i].v;
+        float* r = f3rec.data() + ((size_t)t * F3_TILE + i) * d.f3_recf;
+        for (int c = 0; c < 3; ++c) r[c] = s->v_template[v * 3 + c];
+        for (size_t k = 0; k < nB; ++k)
+          for (int c = 0; c < 3; ++c) r[3 + 3 * k + c] = s->shapedirs[k * 3 * V + (size_t)v * 3 + c];
+        r[3 + 3 * NBTm] = s->skin_w[v * K];
+        r[4 + 3 * NBTm] = ks[i].b1 >= 0 ? s->skin_w[v * K + 1] : 0.f;
+        const int lv3 = 3 * (v - v0);
+        memcpy(&r[5 + 3 * NBTm], &lv3, 4);
+        if (i == 0 || ks[i].b0 != ks[i - 1].b0 || ks[i].b1 != ks[i - 1].b1) {
+          f3runs.insert(f3runs.end(), {ks[i].b0 * 12, ks[i].b1 >= 0 ? ks[i].b1 * 12 : -1, (int)i, 0});
+          ++nruns;
+        }
+        ++f3runs[f3runs.size() - 1];
+      }
+      d.f3_max_runs = std::max(d.f3_max_runs, nruns);
+      f3ptr.push_back((int)(f3runs.size() / 4));
+    }
+    ap.add(f3rec.data(), f3rec.size(), &d.f3_rec);
+    ap.add(reinterpret_cast<const int4*>(f3runs.data()), f3runs.size() / 4, &d.f3_runs);
+    ap.add(f3ptr.data(), f3ptr.size(), &d.f3_tile_run_ptr);
+    d.f3_ok = 1;
   }
   ap.add(s->pb_ptr, V ? J + 1 : 0, &d.pb_ptr);
   ap.add(s->pb_pair, V ? np : 0, &d.pb_pair);
@@ -524,7 +617,18 @@ int smil_forward(const SmilModel* model, const SmilFwdArgs* f, void* stream) {
   if (p.fused) {
     pa.joints_mode = p.is_static ? 2 : 1;
     if (!p.is_static) pa.jrest_out = jrest;   // the backward reads the rest joints back instead of re-deriving them
+    const bool v3 = m.f3_ok && g_fwd_v3 && !p.joints_only;
+    float* AT = reinterpret_cast<float*>(static_cast<char*>(f->saved) + saved_A_bytes(m, B) + saved_jrest_bytes(m, B));
+    if (v3) pa.AT = AT;
     if ((rc = launch_pose(m, pa, false, st)) != SMIL_OK) return rc;
+    if (v3) {
+      SkinFwd3Args sa;
+      sa.B = B; sa.nb = f->num_betas_used;
+      sa.beta = f->beta; sa.beta_stride = f->beta_stride;
+      sa.trans = f->trans; sa.trans_stride = f->trans_stride;
+      sa.AT = AT; sa.verts = f->verts; sa.v_shaped = f->v_shaped;
+      return launch_skin_fwd3(m, sa, st);
+    }
     if (!p.joints_only) {
       SkinFwdArgs sa;
       sa.B = B; sa.nb = f->num_betas_used;

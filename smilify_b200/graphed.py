@@ -63,3 +63,66 @@ class GraphedStep:
 
     def replay(self):
         self.graph.replay()
+
+
+class HostPipeline:
+    """Streams HOST-resident parameter batches through graphed steps.
+
+    ``depth`` device buffer sets, each a :class:`GraphedStep` on its own CUDA stream: the host->device
+    copy of batch i+1 and the device->host copy of batch i-1 overlap the kernels of batch i, so a
+    stream of batches runs at ``max(copy, compute)`` per batch instead of their sum.  Upstream gradients
+    (``slot.g_verts`` / ``slot.g_joints``) stay on the device -- in a fit they come from a loss computed there.
+
+        pipe = HostPipeline(model, B)
+        for batch in batches:                       # pinned CPU tensors
+            done = pipe.submit(batch.beta, batch.theta, batch.trans)
+            if done is not None: consume(done)      # dict of pinned CPU tensors of an EARLIER batch
+        for done in pipe.drain(): consume(done)
+    """
+
+    OUT = ("grad_beta", "grad_theta", "grad_trans", "joints")
+
+    def __init__(self, model, batch, depth=2, **step_kwargs):
+        dev = model._device
+        self.slots = []
+        for _ in range(depth):
+            st = torch.cuda.Stream(device=dev)
+            with torch.cuda.stream(st):
+                gs = GraphedStep(model, batch, **step_kwargs)
+            st.synchronize()
+            host = {k: torch.empty(getattr(gs, k).shape, dtype=torch.float32).pin_memory() for k in self.OUT}
+            self.slots.append(dict(step=gs, stream=st, event=torch.cuda.Event(), host=host, busy=False))
+        self._n = 0
+        self.h2d_bytes = 0
+        self.d2h_bytes = sum(t.numel() * 4 for t in self.slots[0]["host"].values())
+
+    def submit(self, beta, theta, trans):
+        s = self.slots[self._n % len(self.slots)]
+        self._n += 1
+        done = None
+        if s["busy"]:
+            s["event"].synchronize()      # the batch that used this slot is complete: its outputs are in s["host"]
+            done = s["host"]
+        gs = s["step"]
+        with torch.cuda.stream(s["stream"]), torch.no_grad():
+            gs.beta.copy_(beta, non_blocking=True)
+            gs.theta.copy_(theta, non_blocking=True)
+            gs.trans.copy_(trans, non_blocking=True)
+            gs.replay()
+            for k in self.OUT:
+                s["host"][k].copy_(getattr(gs, k), non_blocking=True)
+            s["event"].record(s["stream"])
+        s["busy"] = True
+        self.h2d_bytes = (beta.numel() + theta.numel() + trans.numel()) * 4
+        return done
+
+    def drain(self):
+        out = []
+        n = len(self.slots)
+        for i in range(n):   # oldest first
+            s = self.slots[(self._n + i) % n]
+            if s["busy"]:
+                s["event"].synchronize()
+                s["busy"] = False
+                out.append(s["host"])
+        return out

@@ -30,3 +30,17 @@ def test_parent_indices_bit_exact():
         assert model.parents.dtype == np.int32 and np.array_equal(model.parents, ref)
         assert np.array_equal(model._tables["parents"][1:], ref[1:])
         assert model.faces.dtype == torch.int64
+
+
+@pytest.mark.parametrize("name", ["stick_base", "stick_full", "stick_beta3", "mouse_full", "stick_b1_nobeta"])
+def test_lane_per_sample_forward_variant(name, monkeypatch):
+    """The alternative forward skin pass (SMIL_FWD_V3=1, read at model creation) meets the same bar."""
+    monkeypatch.setenv("SMIL_FWD_V3", "1")
+    try:
+        rows = compare_case(rigs.CASE_BY_NAME[name])
+    finally:
+        monkeypatch.setenv("SMIL_FWD_V3", "0")
+        from tests.common import make_cuda_model
+        make_cuda_model(rigs.CASE_BY_NAME["stick_base"])   # the switch is process-wide: put it back
+    bad = [(n, e, g) for n, e, g in rows if not (e <= TOL) or (g is not None and not (g <= 2 * TOL))]
+    assert not bad, "tolerance %g exceeded: %s" % (TOL, bad)
