@@ -66,6 +66,20 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def traffic_for(kernel, args):
+    """DRAM bytes per launch of ``kernel`` from the committed ncu capture (profiles/r01_traffic.json), valid for the
+    rig / batch it was captured on; ``--traffic`` overrides; None when there is no matching capture."""
+    if args.traffic is not None:
+        return args.traffic
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        if t.get("rig") == args.rig and t.get("batch") == args.batch:
+            return t["kernels"].get(kernel)
+    except Exception:
+        pass
+    return None
+
+
 def synth_inputs(B, V, J, nB, seed):
     """SURVEY.md section 8(d) config 2 distributions."""
     rs = np.random.RandomState(seed)
@@ -357,7 +371,7 @@ def run_ours(args, rank, world, local_rank):
             ab = per_kernel.get(top, 0) * B
             ach = ab / (prof[top][1] / prof[top][0] * 1e-3) / 1e9
             roofline = {"kernel": top, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
-                        "frac": round(ach / peak, 4), "traffic": args.traffic, "peak_source": peak_src,
+                        "frac": round(ach / peak, 4), "traffic": traffic_for(top, args), "peak_source": peak_src,
                         "alg_bytes_per_launch": ab, "avg_us": kernels[top]["avg_us"]}
     if rank != 0:
         return

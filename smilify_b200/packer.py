@@ -26,7 +26,8 @@ from __future__ import annotations
 import numpy as np
 
 FWD_CHUNK = 256  # vertices per CTA of the fused forward skinning pass (one per thread)
-BWD_CHUNK = 256  # vertices per CTA tile of the fused backward pass
+import os as _os
+BWD_CHUNK = int(_os.environ.get("SMIL_BWD_CHUNK", "192"))  # vertices per CTA tile of the fused backward pass (multiple of 32)
 BWD_WARPS = 4    # warps per CTA of the fused backward pass
 MAX_FUSED_K = 4
 MAX_FUSED_NB = 16
@@ -338,14 +339,22 @@ def pack_backward_items(vt, S3, idx, val, nnz_row, J, nB, chunk=BWD_CHUNK, nwarp
             for s in range(int(nnz_row[v])):
                 per_bone.setdefault(int(idx[v, s]), []).append((v - v0, float(val[v, s]), 1.0 if s == 0 else 0.0))
         first_unit = len(unit_bone)
+        # a bone that owns more than one warp's share of the tile's items cannot be balanced as a single unit:
+        # it is cut into equal parts, each a unit with its own slot (the slots of a bone stay contiguous)
+        share = max(2, -(-sum(len(v) for v in per_bone.values()) // nwarps))
         for b in sorted(per_bone):
-            unit_bone.append(b)
-            unit_tile.append(ti)
-            for (lv, w, f) in per_bone[b]:
-                it_v.append(lv)
-                it_w.append(w)
-                it_first.append(f)
-            unit_ptr.append(len(it_v))
+            items = per_bone[b]
+            parts = max(1, -(-len(items) // share))
+            size = -(-len(items) // parts)
+            size += size & 1          # whole item pairs per part (only the last part may be odd)
+            for p0 in range(0, len(items), size):
+                unit_bone.append(b)
+                unit_tile.append(ti)
+                for (lv, w, f) in items[p0:p0 + size]:
+                    it_v.append(lv)
+                    it_w.append(w)
+                    it_first.append(f)
+                unit_ptr.append(len(it_v))
         tile_unit_ptr.append(len(unit_bone))
         # longest-processing-time assignment of the tile's units to warps
         units = list(range(first_unit, len(unit_bone)))
