@@ -217,10 +217,13 @@ class SmalFunction(torch.autograd.Function):
             g.g_Rs = gR.data_ptr() if gR is not None else None
             g.g_v_shaped = gvs.data_ptr() if gvs is not None else None
             opts = dict(device=dev, dtype=torch.float32)
-            o_beta = torch.empty((B, nb), **opts) if (need[3] and nb > 0) else None
+            # static-joint rigs: joints / Rs depend on neither the shape nor trans (smal_torch.py:257-260, 343-346),
+            # so with no upstream gradient on the vertices those inputs get None, like the reference graph gives
+            shape_path = not (bool(flags & _lib.F_STATIC_JOINTS) and gv is None and gvs is None)
+            o_beta = torch.empty((B, nb), **opts) if (need[3] and nb > 0 and shape_path) else None
             o_theta = torch.empty(tuple(theta.shape), **opts) if need[4] else None
-            o_trans = torch.empty((B, 3), **opts) if (need[5] and trans is not None) else None
-            o_delv = torch.empty((B, V, 3), **opts) if (need[6] and del_v is not None) else None
+            o_trans = torch.empty((B, 3), **opts) if (need[5] and trans is not None and shape_path) else None
+            o_delv = torch.empty((B, V, 3), **opts) if (need[6] and del_v is not None and shape_path) else None
             o_ls = torch.empty((B, J, 3), **opts) if (need[7] and ls is not None) else None
             o_bt = torch.empty((B, J, 3), **opts) if (need[8] and bt is not None) else None
             g.g_beta = o_beta.data_ptr() if o_beta is not None else None
