@@ -227,6 +227,79 @@ def pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J
 
 
 def forward_thread_assignment(idx, val, nnz_row, V, chunk):
+    if _os.environ.get("SMIL_FWD_ASSIGN", "uniform") == "uniform":
+        return forward_thread_assignment_uniform(idx, val, nnz_row, V, chunk)
+    return forward_thread_assignment_spread(idx, val, nnz_row, V, chunk)
+
+
+def forward_thread_assignment_uniform(idx, val, nnz_row, V, chunk):
+    """Thread -> vertex map of the fused forward pass that makes as many warps as possible BONE-UNIFORM.
+
+    The pass reads a vertex' bone transforms from shared memory with 16-byte loads at per-thread addresses.
+    Such a load costs four wavefronts whenever the lanes of a warp name more than one address and ONE when
+    they all name the same (measured, ncu r01: the warp-uniform beta / trans loads), so the vertices of a
+    chunk are grouped by their bone pair: every group first fills whole warps, the remainders are packed
+    together in group order.  Inside a warp the lanes are then permuted so that their staging positions are
+    as distinct as possible modulo 32 (the staging stores ``stage[3*pos + c]`` are conflict-free iff they are).
+    Same return values as :func:`forward_thread_assignment_spread`."""
+    nchunk = (V + chunk - 1) // chunk
+    nwarp = chunk // 32
+    K = idx.shape[1]
+    pos = np.full(nchunk * chunk, -1, dtype=np.int64)
+
+    def combo(v):
+        b0 = int(idx[v, 0])
+        b1 = int(idx[v, 1]) if K > 1 and nnz_row[v] > 1 else b0
+        rest = tuple(int(idx[v, k]) for k in range(2, K) if nnz_row[v] > k)
+        return (b0, b1) + rest
+
+    for c in range(nchunk):
+        v0, v1 = c * chunk, min(V, (c + 1) * chunk)
+        groups = {}
+        for v in range(v0, v1):
+            groups.setdefault(combo(v), []).append(v)
+        warps, rest = [], []
+        for key in sorted(groups, key=lambda k_: (-len(groups[k_]), k_)):
+            vs = groups[key]
+            # whole warps of one bone pair: pick 32 vertices with distinct positions mod 32 where the group allows
+            while len(vs) >= 32:
+                by_res = {}
+                for v in vs:
+                    by_res.setdefault((v - v0) % 32, []).append(v)
+                pick = [b.pop() for b in by_res.values()]
+                pool = sorted((v for b in by_res.values() for v in b), key=lambda v: -len(by_res[(v - v0) % 32]))
+                pick += pool[:32 - len(pick)]
+                pick = pick[:32]
+                warps.append(pick)
+                chosen = set(pick)
+                vs = [v for v in vs if v not in chosen]
+            rest.append((key, vs))
+        # remainders: consecutive in bone-pair order, so that a mixed warp holds as few pairs as possible
+        tail = [v for key, vs in sorted(rest) for v in vs]
+        for i in range(0, len(tail), 32):
+            warps.append(tail[i:i + 32])
+        assert len(warps) <= nwarp, (len(warps), nwarp)
+        for w, vs in enumerate(warps):
+            # lane order: vertices with a unique residue take the lane of that residue, the others the free lanes
+            lanes = [-1] * 32
+            left = []
+            for v in vs:
+                r = (v - v0) % 32
+                if lanes[r] < 0:
+                    lanes[r] = v
+                else:
+                    left.append(v)
+            free = [i for i in range(32) if lanes[i] < 0]
+            for v, i in zip(left, free):
+                lanes[i] = v
+            for lane, v in enumerate(lanes):
+                if v >= 0:
+                    pos[c * chunk + w * 32 + lane] = v - v0
+    owner = np.where(pos >= 0, pos + (np.arange(nchunk * chunk) // chunk) * chunk, -1)
+    return pos, owner
+
+
+def forward_thread_assignment_spread(idx, val, nnz_row, V, chunk):
     """Which vertex each thread of the fused forward pass owns.
 
     A CTA covers ``chunk`` consecutive vertices; inside it the mapping thread -> vertex is free
