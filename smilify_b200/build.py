@@ -39,6 +39,8 @@ def build(force=False, verbose=False):
     if not force and up_to_date():
         return OUT
     flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
+    if os.environ.get("SMIL_SKIN_BWD_G"):   # tuning: samples per warp pass of the fused backward (8 | 16 | 32)
+        flags.append("-DSMIL_SKIN_BWD_G=%d" % int(os.environ["SMIL_SKIN_BWD_G"]))
     cmd = [_nvcc()] + flags + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, SRC]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:

@@ -438,8 +438,17 @@ __global__ void __launch_bounds__(32 * F3_WARPS, 4) skin_fwd3_kernel(DevModel m,
 // folded once per unit.  Before the items are walked, the tile's share of Jreg g_joints is added to the
 // staged g_verts rows (joints = Jreg^T verts, smal_torch.py:348-351), so the posed-joint regression needs
 // no backward of its own.
-constexpr int SKIN_BWD_G = 8;       // samples per warp pass (lane & 7)
-constexpr int SKIN_BWD_STREAMS = 4; // item-pair streams per warp (lane >> 3)
+#ifndef SMIL_SKIN_BWD_G
+#define SMIL_SKIN_BWD_G 16
+#endif
+constexpr int SKIN_BWD_G = SMIL_SKIN_BWD_G;        // samples per warp pass (lane % G): 8, 16 or 32
+constexpr int SKIN_BWD_STREAMS = 32 / SKIN_BWD_G;  // item-pair streams per warp (lane / G)
+// fold the SKIN_BWD_STREAMS stream partials of a value onto every lane of its sample
+__device__ __forceinline__ float stream_sum(float v) {
+  if (SKIN_BWD_STREAMS >= 4) v += __shfl_xor_sync(0xffffffffu, v, 8);
+  if (SKIN_BWD_STREAMS >= 2) v += __shfl_xor_sync(0xffffffffu, v, 16);
+  return v;
+}
 
 struct SkinBwdArgs {
   int B, nb;
@@ -473,7 +482,7 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
   const int REC = m.bwd_rec;                  // record stride and tail offset follow the MODEL's beta count
   const int TAIL = m.bwd_tail;                // float offset of (w | first | 3*lv) inside a record
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int g = lane & (SKIN_BWD_G - 1), st = lane >> 3;
+  const int g = lane & (SKIN_BWD_G - 1), st = lane / SKIN_BWD_G;
   const int ti = blockIdx.x;
   const int C = m.bwd_chunk, V = m.V, J = m.J;
   const int RF = skin_bwd_row_floats(C);
@@ -636,8 +645,7 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
 #pragma unroll
       for (int q = 0; q < 12; ++q) {
         s[q] = acc[q].x + acc[q].y;
-        s[q] += __shfl_xor_sync(0xffffffffu, s[q], 8);
-        s[q] += __shfl_xor_sync(0xffffffffu, s[q], 16);
+        s[q] = stream_sum(s[q]);
       }
       if (st == 0 && valid) {
         float4* d = reinterpret_cast<float4*>(a.gA_slots + ((long long)b * m.num_units + ud.w) * 12);
@@ -651,13 +659,10 @@ __global__ void __launch_bounds__(128) skin_bwd_kernel(DevModel m, SkinBwdArgs a
 #pragma unroll
     for (int k = 0; k < NBT; ++k) {
       gb[k] = gb2[k].x + gb2[k].y;
-      gb[k] += __shfl_xor_sync(0xffffffffu, gb[k], 8);
-      gb[k] += __shfl_xor_sync(0xffffffffu, gb[k], 16);
+      gb[k] = stream_sum(gb[k]);
     }
     float gtx = gt0.x + gt0.y, gty = gt1.x + gt1.y, gtz = gt2.x + gt2.y;
-    gtx += __shfl_xor_sync(0xffffffffu, gtx, 8);  gtx += __shfl_xor_sync(0xffffffffu, gtx, 16);
-    gty += __shfl_xor_sync(0xffffffffu, gty, 8);  gty += __shfl_xor_sync(0xffffffffu, gty, 16);
-    gtz += __shfl_xor_sync(0xffffffffu, gtz, 8);  gtz += __shfl_xor_sync(0xffffffffu, gtz, 16);
+    gtx = stream_sum(gtx); gty = stream_sum(gty); gtz = stream_sum(gtz);
     if (st == 0) {
       float* r = sRed + ((size_t)warp * SKIN_BWD_G + g) * (NBT + 4);
 #pragma unroll
