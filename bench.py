@@ -53,6 +53,7 @@ def algorithmic_bytes(V, J, nB):
         "pose_bwd_kernel": 4 * (3 * J + 2 * n_in),              # g_joints + params in; param grads out
     }
     assert sum(per_kernel.values()) == fwd + bwd
+    per_kernel["pose_bwd_lean_kernel"] = per_kernel["pose_bwd_kernel"]   # the no-log-scale variant moves the same tensors
     return fwd, bwd, per_kernel
 
 

@@ -638,6 +638,268 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
   }
 }
 
+// Backward without per-joint log-scales (the headline configuration): the local rotation of joint i is then
+// M_i = R_i = GR_p^T GR_i and tl_i = J_i - J_p (+ betas_trans), both recomputable from the saved global
+// transforms and rest joints, so the local state (Rodrigues, X) is never rebuilt.  Per sample:
+//   G   [J][12]  (GR_j | Jrest_j) in the w column; once j is processed: (gM_j | dL/dJrest_j) for the epilogue
+//   rec [J][16]  (gGR | gGt)(12) + (dL/dJrest acc / contribution to the parent)(4)
+// = 28 J + nbp floats (6.2 KB for J = 55), half of the general kernel's, so a whole 4096-sample batch is
+// resident at once (one wave) instead of 1.4 waves.
+struct PoseSmemLean {
+  int J, nbp;
+  __host__ __device__ int g() const { return 0; }
+  __host__ __device__ int rec() const { return 12 * J; }
+  __host__ __device__ int beta() const { return 28 * J; }
+  __host__ __device__ int floats() const { return (28 * J + nbp + 3) & ~3; }
+};
+
+__global__ void __launch_bounds__(POSE_THREADS, 14) pose_bwd_lean_kernel(DevModel m, PoseArgs a, PoseSmemLean L, int pairs_mode) {
+  extern __shared__ __align__(16) float smem_pose[];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int b = blockIdx.x * POSE_WPB + w;
+  if (b >= a.B) return;
+  const int J = m.J, nb = a.nb;
+  float* sm = smem_pose + (size_t)w * L.floats();
+  float* G = sm + L.g();
+  float* rec = sm + L.rec();
+  float* sbeta = sm + L.beta();
+  float gbeta[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) gbeta[k] = 0.f;
+  const bool rotmat = (a.flags & SMIL_F_THETA_IS_ROTMAT) != 0;
+
+  for (int k = l; k < L.nbp; k += 32) sbeta[k] = (k < nb) ? a.beta[(long long)b * a.beta_stride + k] : 0.f;
+  {
+    const float* src = a.pp_saved + (long long)(b >> 1) * a.pp_blk + (b & 1);
+    const float* jsrc = (a.jrest_mode == 1) ? m.J_static : a.jrest_in + (long long)b * 3 * J;
+    for (int e = l; e < 12 * J; e += 32) {
+      const int j = e / 12, q = e - 12 * j;
+      G[e] = ((q & 3) == 3) ? jsrc[j * 3 + (q >> 2)] : src[2 * e + j * (PPB - 24)];
+    }
+  }
+  __syncwarp();
+
+  // ---- dL/dA per bone: slot partials of the skin pass (+ closed-form posed joints) ---------------------------
+  f3 gtr = mk3(0.f, 0.f, 0.f);
+  for (int e = l; e < 3 * J; e += 32) {
+    const int j = e / 3, r = e - 3 * j;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.gA_slots) {
+      const float4* sl = reinterpret_cast<const float4*>(a.gA_slots) + (long long)b * a.nslots * 3 + r;
+      int si = m.sb_ptr[j];
+      const int se = m.sb_ptr[j + 1];
+      for (; si + 3 < se; si += 4) {
+        const float4 t0 = sl[si * 3], t1 = sl[si * 3 + 3], t2 = sl[si * 3 + 6], t3 = sl[si * 3 + 9];
+        acc.x += (t0.x + t1.x) + (t2.x + t3.x); acc.y += (t0.y + t1.y) + (t2.y + t3.y);
+        acc.z += (t0.z + t1.z) + (t2.z + t3.z); acc.w += (t0.w + t1.w) + (t2.w + t3.w);
+      }
+      if (si + 1 < se) {
+        const float4 t0 = sl[si * 3], t1 = sl[si * 3 + 3];
+        acc.x += t0.x + t1.x; acc.y += t0.y + t1.y; acc.z += t0.z + t1.z; acc.w += t0.w + t1.w;
+        si += 2;
+      }
+      if (si < se) {
+        const float4 t = sl[si * 3];
+        acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+      }
+    }
+    if (pairs_mode) {  // joints_j = ... + rowsum_j * trans
+      const float rs = m.jreg_rowsum[j];
+      const float gjj = a.g_joints[(long long)b * 3 * J + e];
+      if (r == 0) gtr.x = fmaf(rs, gjj, gtr.x);
+      if (r == 1) gtr.y = fmaf(rs, gjj, gtr.y);
+      if (r == 2) gtr.z = fmaf(rs, gjj, gtr.z);
+    }
+    reinterpret_cast<float4*>(rec)[j * 4 + r] = acc;
+  }
+  __syncwarp();
+  if (pairs_mode) {   // same (joint, bone) pair pass as pose_bwd_kernel
+    const int NQ = m.pr_nq;
+    for (int s0 = 0; s0 < m.npairs_pad; s0 += 32) {
+      const float4* R4 = m.pbrec4 + (size_t)(s0 >> 5) * NQ * 32 + l;
+      const float4 h = R4[0], c0 = R4[32];
+      const int bone = __float_as_int(h.x);
+      const bool real = bone >= 0;
+      const int kb = real ? bone : 0;
+      f3 gj = mk3(0.f, 0.f, 0.f);
+      if (real) gj = ld3(a.g_joints + ((long long)b * J + __float_as_int(h.y)) * 3);
+      const float* Gk = G + kb * 12;
+      const f3 tg = mk3(fmaf(Gk[0], gj.x, fmaf(Gk[4], gj.y, Gk[8] * gj.z)), fmaf(Gk[1], gj.x, fmaf(Gk[5], gj.y, Gk[9] * gj.z)),
+                        fmaf(Gk[2], gj.x, fmaf(Gk[6], gj.y, Gk[10] * gj.z)));   // GR_k^T g_joints_j
+      f3 q = mk3(c0.x, c0.y, c0.z);
+      const float c0w = h.z;
+#pragma unroll
+      for (int t4 = 0; t4 < 4; ++t4) {
+        if (4 * t4 < nb) {
+          const float4 cx = R4[(2 + 3 * t4) * 32], cy = R4[(3 + 3 * t4) * 32], cz = R4[(4 + 3 * t4) * 32];
+          const float4 bb = reinterpret_cast<const float4*>(sbeta)[t4];
+          q.x = fmaf(bb.x, cx.x, fmaf(bb.y, cx.y, fmaf(bb.z, cx.z, fmaf(bb.w, cx.w, q.x))));
+          q.y = fmaf(bb.x, cy.x, fmaf(bb.y, cy.y, fmaf(bb.z, cy.z, fmaf(bb.w, cy.w, q.y))));
+          q.z = fmaf(bb.x, cz.x, fmaf(bb.y, cz.y, fmaf(bb.z, cz.z, fmaf(bb.w, cz.w, q.z))));
+          gbeta[4 * t4 + 0] += fmaf(tg.x, cx.x, fmaf(tg.y, cy.x, tg.z * cz.x));
+          gbeta[4 * t4 + 1] += fmaf(tg.x, cx.y, fmaf(tg.y, cy.y, tg.z * cz.y));
+          gbeta[4 * t4 + 2] += fmaf(tg.x, cx.z, fmaf(tg.y, cy.z, tg.z * cz.z));
+          gbeta[4 * t4 + 3] += fmaf(tg.x, cx.w, fmaf(tg.y, cy.w, tg.z * cz.w));
+        }
+      }
+      float v[12];
+      v[0] = gj.x * q.x; v[1] = gj.x * q.y; v[2] = gj.x * q.z; v[3] = gj.x * c0w;
+      v[4] = gj.y * q.x; v[5] = gj.y * q.y; v[6] = gj.y * q.z; v[7] = gj.y * c0w;
+      v[8] = gj.z * q.x; v[9] = gj.z * q.y; v[10] = gj.z * q.z; v[11] = gj.z * c0w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int ob = __shfl_down_sync(0xffffffffu, bone, d);
+        const bool same = (l + d < 32) && ob == bone;
+#pragma unroll
+        for (int i = 0; i < 12; ++i) {
+          const float o = __shfl_down_sync(0xffffffffu, v[i], d);
+          if (same) v[i] += o;
+        }
+      }
+      const int pb_ = __shfl_up_sync(0xffffffffu, bone, 1);
+      if (real && (l == 0 || pb_ != bone)) {
+        float4* d4 = reinterpret_cast<float4*>(rec + bone * 16);
+        float4 t0 = d4[0], t1 = d4[1], t2 = d4[2];
+        t0.x += v[0]; t0.y += v[1]; t0.z += v[2]; t0.w += v[3];
+        t1.x += v[4]; t1.y += v[5]; t1.z += v[6]; t1.w += v[7];
+        t2.x += v[8]; t2.y += v[9]; t2.z += v[10]; t2.w += v[11];
+        d4[0] = t0; d4[1] = t1; d4[2] = t2;
+      }
+      __syncwarp();
+    }
+  }
+  // ---- A = [GR | Gt - GR Jrest], new_J = Gt  ->  initial (gGR | gGt) and dL/dJrest ---------------------------
+  for (int j = l; j < J; j += 32) {
+    m3 gAR, GR; f3 gAt, Jr;
+    ld_rec(rec + j * 16, gAR, gAt);
+    ld_rec(G + j * 12, GR, Jr);
+    m3 gGR;
+    gGR.a[0] = gAR.a[0] - gAt.x * Jr.x; gGR.a[1] = gAR.a[1] - gAt.x * Jr.y; gGR.a[2] = gAR.a[2] - gAt.x * Jr.z;
+    gGR.a[3] = gAR.a[3] - gAt.y * Jr.x; gGR.a[4] = gAR.a[4] - gAt.y * Jr.y; gGR.a[5] = gAR.a[5] - gAt.y * Jr.z;
+    gGR.a[6] = gAR.a[6] - gAt.z * Jr.x; gGR.a[7] = gAR.a[7] - gAt.z * Jr.y; gGR.a[8] = gAR.a[8] - gAt.z * Jr.z;
+    f3 gGt = gAt;
+    if (a.joints_mode == 2 && a.g_joints) {
+      const f3 g = ld3(a.g_joints + ((long long)b * J + j) * 3);
+      gGt.x += g.x; gGt.y += g.y; gGt.z += g.z;
+    }
+    st_rec(rec + j * 16, gGR, gGt);
+    const f3 r = mulT(GR, gAt);
+    reinterpret_cast<float4*>(rec + j * 16)[3] = make_float4(-r.x, -r.y, -r.z, 0.f);
+  }
+  __syncwarp();
+  // ---- leaves -> root -----------------------------------------------------------------------------------
+  for (int lev = m.num_levels - 1; lev >= 1; --lev) {
+    const int beg = m.level_ptr[lev], end = m.level_ptr[lev + 1];
+    for (int q = beg + l; q < end; q += 32) {
+      const int i = m.order[q], p = m.parents[i];
+      m3 GRi, GRp, gGR; f3 Ji, Jp, gGt;
+      ld_rec(G + i * 12, GRi, Ji);
+      ld_rec(G + p * 12, GRp, Jp);
+      ld_rec(rec + i * 16, gGR, gGt);
+      const float4 jacc = reinterpret_cast<const float4*>(rec + i * 16)[3];
+      const m3 M = matmul_AtB(GRp, GRi);   // R_i
+      f3 tl = mk3(Ji.x - Jp.x, Ji.y - Jp.y, Ji.z - Jp.z);
+      if (a.bt) {
+        const float* bp = a.bt + (long long)b * a.bt_stride + i * 3;
+        tl.x += bp[0]; tl.y -= bp[1]; tl.z += bp[2];
+      }
+      const m3 gM = matmul_AtB(GRp, gGR);
+      const f3 gtl = mulT(GRp, gGt);
+      m3 dGR = matmul_ABt(gGR, M);
+      dGR.a[0] = fmaf(gGt.x, tl.x, dGR.a[0]); dGR.a[1] = fmaf(gGt.x, tl.y, dGR.a[1]); dGR.a[2] = fmaf(gGt.x, tl.z, dGR.a[2]);
+      dGR.a[3] = fmaf(gGt.y, tl.x, dGR.a[3]); dGR.a[4] = fmaf(gGt.y, tl.y, dGR.a[4]); dGR.a[5] = fmaf(gGt.y, tl.z, dGR.a[5]);
+      dGR.a[6] = fmaf(gGt.z, tl.x, dGR.a[6]); dGR.a[7] = fmaf(gGt.z, tl.y, dGR.a[7]); dGR.a[8] = fmaf(gGt.z, tl.z, dGR.a[8]);
+      st_rec(G + i * 12, gM, mk3(jacc.x + gtl.x, jacc.y + gtl.y, jacc.z + gtl.z));   // children of i are done: G[i] is free
+      st_rec(rec + i * 16, dGR, gGt);
+      reinterpret_cast<float4*>(rec + i * 16)[3] = make_float4(-gtl.x, -gtl.y, -gtl.z, 0.f);
+      if (a.g_bt) st3(a.g_bt + ((long long)b * J + i) * 3, mk3(gtl.x, -gtl.y, gtl.z));
+    }
+    __syncwarp();
+    const int pbeg = m.level_ptr[lev - 1], pend = m.level_ptr[lev];
+    const int ntask = (pend - pbeg) * 4;
+    for (int t = l; t < ntask; t += 32) {
+      const int pi = t >> 2, q4 = t & 3;
+      const int p = m.order[pbeg + pi];
+      const int c0 = m.child_ptr[p], c1 = m.child_ptr[p + 1];
+      if (c0 == c1) continue;
+      float4* dst = reinterpret_cast<float4*>(rec + p * 16) + q4;
+      float4 acc = *dst;
+      for (int ci = c0; ci < c1; ++ci) {
+        const float4 t4 = reinterpret_cast<const float4*>(rec + m.child_idx[ci] * 16)[q4];
+        acc.x += t4.x; acc.y += t4.y; acc.z += t4.z; acc.w += t4.w;
+      }
+      *dst = acc;
+    }
+    __syncwarp();
+  }
+  if (l == 0) {   // root: G_0 = (R_0 | J_0)
+    m3 gGR; f3 gGt;
+    ld_rec(rec, gGR, gGt);
+    const float4 jacc = reinterpret_cast<const float4*>(rec)[3];
+    st_rec(G, gGR, mk3(jacc.x + gGt.x, jacc.y + gGt.y, jacc.z + gGt.z));
+    if (a.g_bt) st3(a.g_bt + (long long)b * J * 3, mk3(0.f, 0.f, 0.f));
+  }
+  __syncwarp();
+  // ---- lane-per-joint epilogue: g_theta -------------------------------------------------------------------
+  if (a.g_theta) {
+    for (int j = l; j < J; j += 32) {
+      m3 gR; f3 dJ;
+      ld_rec(G + j * 12, gR, dJ);
+      if (a.g_Rs) {
+        const float* gp = a.g_Rs + ((long long)b * J + j) * 9;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) gR.a[t] += gp[t];
+      }
+      if (rotmat) {
+        float* o = a.g_theta + ((long long)b * J + j) * 9;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) o[t] = gR.a[t];
+      } else {
+        st3(a.g_theta + ((long long)b * J + j) * 3, rodrigues_vjp(ld3(a.theta + (long long)b * a.theta_stride + j * 3), gR));
+      }
+    }
+  }
+  // ---- g_beta, g_trans ---------------------------------------------------------------------------------------
+  const int ne = nb + 3;
+  float part = 0.f;
+  if (a.gbt_part && l < ne)
+    for (int t = 0; t < a.ntile; ++t) part += a.gbt_part[((long long)b * a.ntile + t) * ne + l];
+  float mine = 0.f;
+  if (a.g_beta) {
+    if (a.jrest_closed) {
+      for (int e = l; e < 3 * J; e += 32) {
+        const int j = e / 3;
+        const float gje = G[j * 12 + 3 + 4 * (e - 3 * j)];
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          if (k < nb) gbeta[k] = fmaf(m.JS[(long long)k * 3 * J + e], gje, gbeta[k]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      if (k < nb) {
+        float s = gbeta[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (l == k) mine = s;
+      }
+    }
+    if (l < nb) a.g_beta[(long long)b * nb + l] = mine + part;
+  }
+  if (a.g_trans) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      gtr.x += __shfl_xor_sync(0xffffffffu, gtr.x, o);
+      gtr.y += __shfl_xor_sync(0xffffffffu, gtr.y, o);
+      gtr.z += __shfl_xor_sync(0xffffffffu, gtr.z, o);
+    }
+    if (l >= nb && l < ne) {
+      const int c = l - nb;
+      a.g_trans[(long long)b * 3 + c] = part + (c == 0 ? gtr.x : (c == 1 ? gtr.y : gtr.z));
+    }
+  }
+}
+
 // ---- stand-alone Rodrigues (drop-in for batch_rodrigues) --------------------------------------------
 __global__ void rodrigues_fwd_kernel(const float* __restrict__ theta, float* __restrict__ R, long long n) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;

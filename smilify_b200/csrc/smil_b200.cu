@@ -30,6 +30,7 @@ int g_fwd_gp = 0;   // tuning override (SMIL_FWD_GP): sample pairs per TMA group
 int g_fwd_direct = 0;  // tuning override (SMIL_FWD_DIRECT): register -> global stores instead of the TMA staging ring
 int g_bwd_stages = 1;  // SMIL_BWD_STAGES: 1 = single-buffered g_verts rows (more CTAs per SM), 2 = double-buffered
 int g_bwd_cps = 0;     // SMIL_BWD_CPS
+int g_pose_lean = 1;  // SMIL_POSE_LEAN=0: always use the general backward pose kernel.
 int g_fwd_v3 = 0;      // SMIL_FWD_V3=1: lane-per-sample forward skin pass (K <= 2 rigs) instead of the thread-per-vertex pass.
                        // Measured on B200 (STICK, B=4096): 98 us vs 85 us, plus 9 us in the pose pass for the sample-minor
                        // copy of the transforms, so it is off by default; kept as the evaluated alternative.
@@ -102,7 +103,17 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
   const size_t smem = (size_t)((fl + 3) & ~3) * sizeof(float) * POSE_WPB;
   const int grid = (a.B + POSE_WPB - 1) / POSE_WPB;
   int rc = SMIL_OK;
-  if (backward) {
+  const bool lean = backward && g_pose_lean && a.beta_final && a.pp_saved && !a.ls && !a.g_newJ && !a.gA_dense &&
+                    !a.g_jrest && !a.g_Rs2 && (a.jrest_mode == 1 || (a.jrest_mode == 2 && a.jrest_in));
+  if (lean) {   // no per-joint scales: half the shared memory, the whole batch resident in one wave
+    PoseSmemLean LL;
+    LL.J = m.J;
+    LL.nbp = L.nbp;
+    const size_t smem_l = (size_t)LL.floats() * sizeof(float) * POSE_WPB;
+    if ((rc = set_smem(pose_bwd_lean_kernel, smem_l)) != SMIL_OK) return rc;
+    prof_begin("pose_bwd_lean_kernel", st);
+    pose_bwd_lean_kernel<<<grid, POSE_THREADS, smem_l, st>>>(m, a, LL, pairs_mode);
+  } else if (backward) {
     if ((rc = set_smem(pose_bwd_kernel, smem)) != SMIL_OK) return rc;
     prof_begin("pose_bwd_kernel", st);
     pose_bwd_kernel<<<grid, POSE_THREADS, smem, st>>>(m, a, L, pairs_mode);
@@ -111,7 +122,7 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
     prof_begin("pose_fwd_kernel", st);
     pose_fwd_kernel<<<grid, POSE_THREADS, smem, st>>>(m, a, L);
   }
-  SMIL_LAUNCH_CHECK(backward ? "pose_bwd_kernel" : "pose_fwd_kernel");
+  SMIL_LAUNCH_CHECK(lean ? "pose_bwd_lean_kernel" : (backward ? "pose_bwd_kernel" : "pose_fwd_kernel"));
   return SMIL_OK;
 }
 
@@ -392,6 +403,7 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   if (const char* e = getenv("SMIL_BWD_STAGES")) g_bwd_stages = atoi(e);
   if (const char* e = getenv("SMIL_BWD_CPS")) g_bwd_cps = atoi(e);
   if (const char* e = getenv("SMIL_FWD_V3")) g_fwd_v3 = atoi(e);
+  if (const char* e = getenv("SMIL_POSE_LEAN")) g_pose_lean = atoi(e);
   if (const char* e = getenv("SMIL_FWD_DIRECT")) g_fwd_direct = atoi(e);
   SMIL_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, s->device));
 
