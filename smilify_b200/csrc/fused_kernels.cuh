@@ -8,7 +8,7 @@
 //
 // Backward (skin_bwd_kernel):  item-major.  An item is one non-zero (vertex, bone, weight) of
 //   the skinning matrix; items are grouped per vertex tile and bone ("unit").  A lane owns one
-//   SAMPLE (8 samples x 4 item streams per warp), so every reduction over vertices -- g_A per
+//   SAMPLE (16 samples x 2 item streams per warp), so every reduction over vertices -- g_A per
 //   bone, g_beta, g_trans -- is a private register accumulation: no atomics, no cross-lane
 //   reduction per item, deterministic.  g_verts tiles arrive through double-buffered TMA bulk
 //   copies.  Autograd of smal_torch.py:223-253, 318-340.
@@ -431,13 +431,14 @@ __global__ void __launch_bounds__(32 * F3_WARPS, 4) skin_fwd3_kernel(DevModel m,
 // =====================================================================================================
 // backward
 // =====================================================================================================
-// Item-major, lane = sample (8 samples x 4 item streams per warp), two items per step packed into f32x2
-// lanes: the item-pair records hold every constant as an (item i, item i+1) pair, the per-sample operands
-// (bone rotation, betas) are duplicated into (x,x) register pairs once per unit / group.  All reductions
-// over vertices are private register accumulations; the two halves of a pair and the four streams are
-// folded once per unit.  Before the items are walked, the tile's share of Jreg g_joints is added to the
-// staged g_verts rows (joints = Jreg^T verts, smal_torch.py:348-351), so the posed-joint regression needs
-// no backward of its own.
+// Item-major, lane = sample (SKIN_BWD_G samples x 32/SKIN_BWD_G item streams per warp), two items per step
+// packed into f32x2 lanes: the item-pair records hold every constant as an (item i, item i+1) pair, the
+// per-sample operands (bone rotation, betas) enter the packed FMAs as broadcast scalars.  All reductions
+// over vertices are private register accumulations; the two halves of a pair and the streams are folded
+// once per unit.  Persistent: a CTA keeps its tile's records in shared memory and walks its share of the
+// sample groups, whose g_verts rows arrive through TMA bulk copies.  The posed-joint regression
+// (joints = Jreg^T verts, smal_torch.py:348-351) is NOT folded in here: its backward is the closed-form
+// (joint, bone) pair pass of the pose kernel (folding it cost more than it saved).
 #ifndef SMIL_SKIN_BWD_G
 #define SMIL_SKIN_BWD_G 16
 #endif

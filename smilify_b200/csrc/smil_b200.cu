@@ -395,7 +395,7 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
       d.h_max_tile_units = std::max(d.h_max_tile_units, s->tile_unit_ptr[t + 1] - s->tile_unit_ptr[t]);
     }
   d.fused_ok = s->fused_ok && d.V > 0 && s->fwd_chunk == SKIN_FWD_THREADS && s->bwd_warps == 4 && d.K <= 4 &&
-               nbt_of(d.nB) > 0 && d.P == 0 && (s->bwd_chunk % 32) == 0 &&
+               nbt_of(d.nB) > 0 && d.P == 0 && s->bwd_chunk > 0 &&
                s->bwd_rec == skin_bwd_rec_floats(nbt_of(d.nB)) && d.J <= 64 && d.h_max_tile_units <= SKIN_BWD_MAXU;
   d.device = s->device;
   if (const char* e = getenv("SMIL_FWD_GP")) g_fwd_gp = atoi(e);

@@ -27,7 +27,15 @@ import numpy as np
 
 FWD_CHUNK = 256  # vertices per CTA of the fused forward skinning pass (one per thread)
 import os as _os
-BWD_CHUNK = int(_os.environ.get("SMIL_BWD_CHUNK", "192"))  # vertices per CTA tile of the fused backward pass (multiple of 32)
+BWD_CHUNK = int(_os.environ.get("SMIL_BWD_CHUNK", "192"))  # upper bound of the vertices per CTA tile of the fused backward pass
+
+
+def backward_chunk(V: int, limit: int = None) -> int:
+    """Tile size of the fused backward pass: the fewest tiles of at most ``limit`` vertices, made equal
+    (STICK: 16 tiles of 189 instead of 15 x 192 + 140) so that every CTA column carries the same work."""
+    limit = BWD_CHUNK if limit is None else limit
+    ntile = max(1, -(-V // limit))
+    return max(1, -(-V // ntile))
 BWD_WARPS = 4    # warps per CTA of the fused backward pass
 MAX_FUSED_K = 4
 MAX_FUSED_NB = 16
@@ -210,14 +218,15 @@ def pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J
              ell_w=_f32(ell_w), fwd_pos=_i32(fwd_pos))
 
     # ---- fused backward pass: item-major tables ------------------------------------------------
-    t.update(pack_backward_items(vt, S3, idx, val, nnz_row, J, nB))
+    bchunk = backward_chunk(V)
+    t.update(pack_backward_items(vt, S3, idx, val, nnz_row, J, nB, chunk=bchunk))
     # vertices of every backward tile that carry joint-regressor entries (the backward folds
     # Jreg g_joints into the staged g_verts tile: joints = Jreg^T verts, smal_torch.py:348-351)
     nt = t["bwd_ntile"]
     has_j = np.diff(t["jr_ptr"]) > 0
     tjv_ptr, tjv_v = [0], []
     for ti in range(nt):
-        v0, v1 = ti * BWD_CHUNK, min(V, (ti + 1) * BWD_CHUNK)
+        v0, v1 = ti * bchunk, min(V, (ti + 1) * bchunk)
         tjv_v.extend((np.nonzero(has_j[v0:v1])[0]).tolist())
         tjv_ptr.append(len(tjv_v))
     t["tjv_ptr"] = _i32(tjv_ptr)
