@@ -1,0 +1,136 @@
+#!/usr/bin/env python
+"""BASELINE configs[3] on real GPUs: SMALFitter-style joint fit, frames sharded over the ranks, ONE packed NCCL
+all-reduce of the shared-parameter gradients (betas, fov) per step.
+
+Launch (N = 2, 4, 8):
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 \
+      tools_gpu/fitter_multigpu.py --frames 65536 --steps 10 --warmup 3
+or, for the single-GPU line, ``python tools_gpu/fitter_multigpu.py``.
+
+Every frame's parameters and targets are generated from the GLOBAL frame index, so every world size solves the same
+problem.  After the timed region rank 0 re-evaluates ALL frames alone (8192-frame chunks, gradients accumulated) and
+reports how far the all-reduced shared gradients and the loss of the sharded run are from that single-process result.
+OmniAnt's pickle is not in the repository: the STICK rig stands in (J = 55, nB = 5).
+Prints one JSON line on rank 0."""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import smilify_b200  # noqa: E402
+from smilify_b200 import _lib  # noqa: E402
+from smilify_b200 import fitter_step as FS  # noqa: E402
+from smilify_b200.smal_torch import SMAL  # noqa: E402
+from tests import rigs  # noqa: E402
+
+
+def frame_block(lo, hi, J, block=4096):
+    """Per-frame parameters / targets of global frames [lo, hi): seeded per 4096-frame block of the GLOBAL index."""
+    out = {k: [] for k in ("global_rotation", "joint_rotations", "trans", "target", "vis")}
+    b0 = (lo // block) * block
+    while b0 < hi:
+        rs = np.random.RandomState(1000 + b0 // block)
+        gr = rs.normal(0, 0.3, (block, 3)).astype(np.float32)
+        jr = rs.normal(0, 0.3, (block, J - 1, 3)).astype(np.float32)
+        tr = rs.normal(0, 0.1, (block, 3)).astype(np.float32)
+        tg = rs.uniform(0, 512, (block, J, 2)).astype(np.float32)
+        vi = (rs.uniform(size=(block, J)) < 0.8).astype(np.float32)
+        s, e = max(lo, b0) - b0, min(hi, b0 + block) - b0
+        for k, a in zip(out, (gr, jr, tr, tg, vi)):
+            out[k].append(a[s:e])
+        b0 += block
+    return {k: np.concatenate(v) for k, v in out.items()}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--frames", type=int, default=65536)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--get-skin", type=int, default=1, help="1: pose the mesh too, as fitter.py:262 does")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    smilify_b200.configure(rigs.REAL_RIGS["stick"])
+    model = SMAL(dev)
+    J, nB = model._tables["J"], model.num_betas
+    # the fitter's default camera, look_at_view_transform(2.7, 0, 0) (p3d_renderer.py:34-37)
+    R = torch.diag(torch.tensor([-1.0, 1.0, -1.0]))[None].to(dev)
+    T = torch.tensor([[0.0, 0.0, 2.7]], device=dev)
+
+    def build(lo, hi):
+        d = frame_block(lo, hi, J)
+        fp = {k: torch.from_numpy(d[k]).to(dev).requires_grad_(True) for k in ("global_rotation", "joint_rotations", "trans")}
+        rs = np.random.RandomState(7)
+        sp = dict(betas=torch.from_numpy(rs.normal(0, 0.5, (nB,)).astype(np.float32)).to(dev).requires_grad_(True),
+                  fov=torch.tensor([60.0], device=dev, requires_grad=True))
+        fn = FS.smal_joint_loss_fn(model, R, T, torch.from_numpy(d["target"]).to(dev), torch.from_numpy(d["vis"]).to(dev),
+                                   get_skin=bool(args.get_skin))
+        return fp, sp, fn
+
+    lo, hi = FS.shard_range(args.frames, rank, world)
+    fp, sp, fn = build(lo, hi)
+    step = FS.ShardedFitterStep(fp, sp, fn, args.frames)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        loss = step()
+    barrier()
+    before = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = _lib.launch_count() - before
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    g_sharded = {k: v.grad.detach().clone() for k, v in sp.items()}
+    loss_sharded = float(loss)
+
+    # single-process run over ALL frames on rank 0 (chunked accumulation): what the sharded gradients must equal
+    check = None
+    if rank == 0 and world > 1:
+        acc = {k: torch.zeros_like(v) for k, v in sp.items()}
+        tot = 0.0
+        for c0 in range(0, args.frames, 8192):
+            fpc, spc, fnc = build(c0, min(args.frames, c0 + 8192))
+            part = fnc(fpc, spc) / args.frames
+            part.backward()
+            tot += float(part)
+            for k in acc:
+                acc[k] += spc[k].grad
+        check = {k: float((g_sharded[k] - acc[k]).abs().max() / acc[k].abs().max().clamp_min(1e-30)) for k in acc}
+        check["loss"] = abs(loss_sharded - tot) / abs(tot)
+    if rank == 0:
+        print(json.dumps({
+            "metric": "SMALFitter-style frames/s (SMAL fwd+bwd + joint reprojection loss, shared betas/fov)",
+            "value": args.frames / ms * 1e3, "unit": "frames/s", "n_gpus": world, "ms_per_step": ms, "steps": args.steps,
+            "warmup": args.warmup, "frames_total": args.frames, "frames_per_gpu": hi - lo, "scaling": "strong",
+            "collective": "1 all_reduce(SUM) per step, %d bytes (g_betas, g_fov, loss)" % step.collective_bytes,
+            "backend": "nccl" if world > 1 else "none", "rig": "stick (OmniAnt stand-in)", "get_skin": bool(args.get_skin),
+            "gpu_launches": launches, "loss": loss_sharded,
+            "sharded_vs_single_process_rel_err": check}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
