@@ -162,3 +162,35 @@ def test_cuda_step_matches_oracle():
     for k in sp:
         r = ref_sg[k].float()
         assert float((sp[k].grad.cpu() - r).abs().max()) <= tol * float(r.abs().max()), k
+
+
+@pytest.mark.gpu
+def test_graphed_step_equals_eager_step():
+    """The CUDA-graph replay of the local part leaves the same loss and gradients as the eager step, and follows
+    in-place updates of the leaves."""
+    import smilify_b200
+    from smilify_b200.smal_torch import SMAL
+
+    dd = rigs.get_rig("stick")
+    smilify_b200.configure(rigs.REAL_RIGS["stick"])
+    dev = torch.device("cuda:0")
+    model = SMAL(dev)
+    n = 37
+    frame, shared, R, T, target, vis = _problem(dd, n, dtype=torch.float32)
+    fp = {k: v.to(dev).requires_grad_(True) for k, v in frame.items()}
+    sp = {k: v.to(dev).requires_grad_(True) for k, v in shared.items()}
+    fn = FS.smal_joint_loss_fn(model, R.to(dev), T.to(dev), target.to(dev), vis.to(dev), get_skin=True)
+    graphed = FS.GraphedShardedFitterStep(fp, sp, fn, n)
+    for trial in range(2):
+        loss_g = float(graphed())
+        got = {k: v.grad.clone() for k, v in list(fp.items()) + list(sp.items())}
+        loss_e = float(FS.ShardedFitterStep(fp, sp, fn, n)())
+        assert abs(loss_g - loss_e) <= 1e-6 * abs(loss_e)
+        for k, v in list(fp.items()) + list(sp.items()):
+            assert float((got[k] - v.grad).abs().max()) <= 1e-6 * float(v.grad.abs().max()), (trial, k)
+        with torch.no_grad():   # an optimiser step in place: the next replay must see it
+            for v in list(fp.values()) + list(sp.values()):
+                v.add_(0.01 * torch.randn_like(v))
+    with pytest.raises(RuntimeError):
+        FS.GraphedShardedFitterStep({k: v.detach().cpu().requires_grad_(True) for k, v in fp.items()},
+                                    {k: v.detach().cpu().requires_grad_(True) for k, v in sp.items()}, fn, n)

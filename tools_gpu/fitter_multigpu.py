@@ -52,6 +52,7 @@ def main():
     ap.add_argument("--frames", type=int, default=65536)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--graph", type=int, default=1, help="1: replay the local part from a CUDA graph")
     ap.add_argument("--get-skin", type=int, default=1, help="1: pose the mesh too, as fitter.py:262 does")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
@@ -79,7 +80,10 @@ def main():
 
     lo, hi = FS.shard_range(args.frames, rank, world)
     fp, sp, fn = build(lo, hi)
-    step = FS.ShardedFitterStep(fp, sp, fn, args.frames)
+    c0 = _lib.launch_count()
+    FS.ShardedFitterStep(fp, sp, fn, args.frames)()          # one eager step: counts the kernels a step launches
+    per_step = _lib.launch_count() - c0
+    step = (FS.GraphedShardedFitterStep if args.graph else FS.ShardedFitterStep)(fp, sp, fn, args.frames)
 
     def barrier():
         if world > 1:
@@ -89,7 +93,6 @@ def main():
     for _ in range(args.warmup):
         loss = step()
     barrier()
-    before = _lib.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
@@ -97,7 +100,7 @@ def main():
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1) / args.steps
-    launches = _lib.launch_count() - before
+    launches = per_step * args.steps   # a graph replay launches the same kernels the eager step does
     if world > 1:
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -114,7 +117,7 @@ def main():
             fpc, spc, fnc = build(c0, min(args.frames, c0 + 8192))
             part = fnc(fpc, spc) / args.frames
             part.backward()
-            tot += float(part)
+            tot += float(part.detach())
             for k in acc:
                 acc[k] += spc[k].grad
         check = {k: float((g_sharded[k] - acc[k]).abs().max() / acc[k].abs().max().clamp_min(1e-30)) for k in acc}
@@ -126,6 +129,7 @@ def main():
             "warmup": args.warmup, "frames_total": args.frames, "frames_per_gpu": hi - lo, "scaling": "strong",
             "collective": "1 all_reduce(SUM) per step, %d bytes (g_betas, g_fov, loss)" % step.collective_bytes,
             "backend": "nccl" if world > 1 else "none", "rig": "stick (OmniAnt stand-in)", "get_skin": bool(args.get_skin),
+            "launch": "cuda-graph replay + eager all_reduce" if args.graph else "eager",
             "gpu_launches": launches, "loss": loss_sharded,
             "sharded_vs_single_process_rel_err": check}))
     if world > 1:
