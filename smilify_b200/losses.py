@@ -265,8 +265,10 @@ def pca_joint_values(scale_weights, trans_weights, scaledirs, transdirs, transla
         betas_trans = torch.einsum("jck,bk->bjc", transdirs, trans_weights) * translation_factor
     else:
         betas_trans = torch.zeros(B, scaledirs.shape[0], 3, device=scale_weights.device)
-    if not torch.isfinite(log_beta_scales).all():
-        log_beta_scales = torch.nan_to_num(log_beta_scales, nan=0.0, posinf=0.0, neginf=-10.0)
-    if trans_weights is not None and not torch.isfinite(betas_trans).all():
+    # The reference tests ``isfinite(...).all()`` on the host and only then sanitises; nan_to_num is the identity (and
+    # passes gradients through unchanged) on finite values, so it is applied unconditionally here: no device->host
+    # sync per call, and the function can be captured in a CUDA graph.
+    log_beta_scales = torch.nan_to_num(log_beta_scales, nan=0.0, posinf=0.0, neginf=-10.0)
+    if trans_weights is not None:
         betas_trans = torch.nan_to_num(betas_trans, nan=0.0, posinf=0.0, neginf=0.0)
     return log_beta_scales, betas_trans

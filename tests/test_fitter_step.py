@@ -137,6 +137,21 @@ def test_pca_joint_values_matches_oracle():
     assert (sd * 0 + 1).sum() > 0 and torch.isfinite(a[0]).all()   # the clamp kept log() finite
     z = L.pca_joint_values(sw, None, sd, td)
     assert torch.count_nonzero(z[1]) == 0
+    # non-finite weights are sanitised as the reference does (smil_image_regressor.py:1166-1232: nan -> 0, +inf -> 0,
+    # -inf -> -10 / 0), without a host-side isfinite() branch; finite entries and their gradients are untouched
+    bad = sw.clone()
+    bad[0, 0] = float("nan")
+    bad[1, 1] = float("inf")
+    tb = tw.clone()
+    tb[2, 0] = float("-inf")
+    ls, bt = L.pca_joint_values(bad, tb, sd, td)
+    assert torch.isfinite(ls).all() and torch.isfinite(bt).all()
+    assert torch.allclose(ls[2:], a[0][2:]) and torch.allclose(bt[3:], a[1][3:])
+    g_in = sw.clone().requires_grad_(True)
+    L.pca_joint_values(g_in, tw, sd, td)[0].sum().backward()
+    g_ref = sw.clone().requires_grad_(True)
+    SO.pca_weights_to_joint_values(sd, td, g_ref, tw)[0].sum().backward()
+    assert torch.allclose(g_in.grad, g_ref.grad)
 
 
 @pytest.mark.gpu
