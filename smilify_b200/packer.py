@@ -249,14 +249,104 @@ def forward_thread_assignment(idx, val, nnz_row, V, chunk):
     return forward_thread_assignment_spread(idx, val, nnz_row, V, chunk)
 
 
+def _lds128_cost(d):
+    """Shared-memory wavefronts of one 16-byte warp load whose lanes name ``d`` distinct addresses (measured on B200,
+    tools_micro/lds_gather.cu / profiles/r01_lds_gather_micro.csv)."""
+    return 2 if d <= 2 else 4 if d <= 4 else 6 if d <= 8 else 8
+
+
+def _refine_anchor_warps(a0, a1, members, sweeps=4, w_load=0.77, w_store=0.61):
+    """Local search over the warps of one chunk: vertices that sit in a staging-store bank conflict (a second vertex of
+    their warp has the same position mod 32) are swapped with a vertex of the SAME anchor in another warp when that
+    lowers the modelled cost  ``w_load * 6 * (c(d0) + c(d1)) + w_store * 12 * max multiplicity``  of the two warps
+    (c = :func:`_lds128_cost`; the weights are the measured us per wavefront and warp pass of loads / stores in
+    ``skin_fwd``).  Same-anchor swaps leave slot 0 untouched, so the search stays small
+    (about a second for STICK); deterministic."""
+    nw = len(members)
+    wof = {}
+    for w, ms in enumerate(members):
+        for i in ms:
+            wof[i] = w
+    c0 = [dict() for _ in range(nw)]
+    c1 = [dict() for _ in range(nw)]
+    cr = [dict() for _ in range(nw)]
+
+    def mv(w, i, sgn):
+        for d, key in ((c0[w], a0[i]), (cr[w], i & 31)) + (((c1[w], a1[i]),) if a1[i] >= 0 else ()):
+            n = d.get(key, 0) + sgn
+            if n:
+                d[key] = n
+            else:
+                del d[key]
+
+    for i, w in wof.items():
+        mv(w, i, 1)
+
+    def cost(w):
+        if not cr[w]:
+            return 0.0
+        return (w_load * 6 * (_lds128_cost(len(c0[w])) + _lds128_cost(len(c1[w]))) + w_store * 12 * max(cr[w].values())
+                + 1e-3 * sum(x * x for x in cr[w].values()) - 1e-4 * sum(x * x for x in c1[w].values()))
+
+    by_anchor = {}
+    for i in sorted(wof):
+        by_anchor.setdefault(a0[i], []).append(i)
+    costs = [cost(w) for w in range(nw)]
+    for _ in range(sweeps):
+        improved = False
+        for i in sorted(wof):
+            wa = wof[i]
+            if cr[wa].get(i & 31, 0) < 2:
+                continue
+            best = None
+            for j in by_anchor[a0[i]]:
+                wb = wof[j]
+                if wb == wa:
+                    continue
+                mv(wa, i, -1); mv(wb, j, -1); mv(wa, j, 1); mv(wb, i, 1)
+                d = cost(wa) + cost(wb) - costs[wa] - costs[wb]
+                mv(wa, j, -1); mv(wb, i, -1); mv(wa, i, 1); mv(wb, j, 1)
+                if d < -1e-9 and (best is None or d < best[0]):
+                    best = (d, j, wb)
+            if best:
+                _, j, wb = best
+                mv(wa, i, -1); mv(wb, j, -1); mv(wa, j, 1); mv(wb, i, 1)
+                wof[i], wof[j] = wb, wa
+                costs[wa], costs[wb] = cost(wa), cost(wb)
+                improved = True
+        if not improved:
+            break
+    out = [[] for _ in range(nw)]
+    for i in sorted(wof):
+        out[wof[i]].append(i)
+    return out
+
+
+_ANCHOR_MEMO = {}
+
+
 def forward_thread_assignment_anchor(idx, val, nnz_row, V, chunk):
+    """Memoised per process on the skinning tables (the search below takes about a second per rig)."""
+    import hashlib
+
+    key = hashlib.sha1(np.ascontiguousarray(idx).tobytes() + np.ascontiguousarray(val).tobytes() +
+                       np.ascontiguousarray(nnz_row).tobytes() + repr((V, chunk, _os.environ.get("SMIL_FWD_REFINE", "1"))).encode()
+                       ).hexdigest()
+    if key not in _ANCHOR_MEMO:
+        _ANCHOR_MEMO[key] = _forward_thread_assignment_anchor(idx, val, nnz_row, V, chunk)
+    return tuple(a.copy() for a in _ANCHOR_MEMO[key])
+
+
+def _forward_thread_assignment_anchor(idx, val, nnz_row, V, chunk):
     """Thread -> vertex map for rigs with at most two weights per vertex, built on the measured cost of the bone
     transform gathers (tools_micro/lds_gather.cu: a 16-byte shared load costs 2 wavefronts while the lanes of a warp
     name <= 2 distinct addresses, 4 for 3-4, 6-8 beyond): what matters per skinning slot and warp is the NUMBER of
     distinct bones, and which of a vertex' two bones sits in slot 0 is free.  Per chunk the bones are ranked by how
     many vertices carry them; every vertex puts its higher-ranked bone (its anchor) into slot 0 and the vertices are
     dealt to the warps in (anchor, partner) order, so that slot 0 of a warp sees one or two anchors and slot 1 a short
-    run of partners; the unused slot 1 of a single-bone vertex names the most common partner of its warp.
+    run of partners; the unused slot 1 of a single-bone vertex names the most common partner of its warp.  A local
+    search (:func:`_refine_anchor_warps`) then trades vertices of the same anchor between warps to remove bank conflicts
+    of the staging stores.
     Returns ``(fwd_pos, owner, ell_idx (2, Vpad), ell_w (2, Vpad))``."""
     nchunk = (V + chunk - 1) // chunk
     Vpad = nchunk * chunk
@@ -282,8 +372,10 @@ def forward_thread_assignment_anchor(idx, val, nnz_row, V, chunk):
             else:
                 a1.append(-1); w1.append(0.0)
         order = sorted(range(n), key=lambda i: (prio[a0[i]], a1[i] < 0, a1[i], i))
-        for w in range((n + 31) // 32):
-            ms = order[w * 32:(w + 1) * 32]
+        members = [order[w * 32:(w + 1) * 32] for w in range((n + 31) // 32)]
+        if _os.environ.get("SMIL_FWD_REFINE", "1") != "0":
+            members = _refine_anchor_warps(a0, a1, members)
+        for w, ms in enumerate(members):
             partners = [a1[i] for i in ms if a1[i] >= 0]
             fill = max(set(partners), key=partners.count) if partners else -1
             lanes = [-1] * 32
