@@ -554,6 +554,44 @@ def forward_thread_assignment_spread(idx, val, nnz_row, V, chunk):
     return pos, owner
 
 
+def _interleave_for_streams(items):
+    """Order of a unit's items ``(local vertex, weight, first)`` for the two item-pair streams of the fused backward.
+
+    Items 4t, 4t+1 form the pair stream 0 handles in step t, items 4t+2, 4t+3 the pair of stream 1, and the two streams
+    read their ``g_verts`` entries with the same instruction: lane (sample g, stream s) reads ``row_g[3 v_s + c]`` with a
+    row stride of 4 (mod 32) floats, so the 16 samples of one stream already share banks two by two, and the two
+    streams fall onto the SAME banks (4-way conflict) exactly when ``v_0 = v_1 (mod 4)``.  Items are therefore dealt
+    so that the vertices at offsets 0 / 2 and 1 / 3 of a group of four differ mod 4 whenever the unit allows.
+    Any order is valid (the kernel only sums over a unit's items)."""
+    if _os.environ.get("SMIL_BWD_INTERLEAVE", "1") == "0" or len(items) < 4:
+        return items
+    buckets = [[], [], [], []]
+    for it in items:
+        buckets[it[0] & 3].append(it)
+    for b_ in buckets:
+        b_.reverse()   # pop() hands the items out in vertex order
+
+    def take(avoid):
+        cand = [r for r in range(4) if buckets[r] and r != avoid] or [r for r in range(4) if buckets[r]]
+        r = max(cand, key=lambda q: (len(buckets[q]), -q))
+        return buckets[r].pop()
+
+    out = []
+    left = len(items)
+    while left:
+        grp = [None] * 4
+        for slot, partner in ((0, None), (2, 0), (1, None), (3, 1)):
+            if not left:
+                break
+            avoid = grp[partner][0] & 3 if partner is not None and grp[partner] is not None else -1
+            grp[slot] = take(avoid)
+            left -= 1
+        # a short last group keeps the pair layout: offsets (0, 1) are stream 0's pair, (2, 3) stream 1's
+        got = [g for g in grp if g is not None]
+        out.extend(grp if len(got) == 4 else got)
+    return out
+
+
 def pack_backward_items(vt, S3, idx, val, nnz_row, J, nB, chunk=BWD_CHUNK, nwarps=BWD_WARPS):
     """Items ``(vertex, bone, weight)`` grouped per vertex tile and, inside a tile, per bone.
 
@@ -592,7 +630,7 @@ def pack_backward_items(vt, S3, idx, val, nnz_row, J, nB, chunk=BWD_CHUNK, nwarp
             for p0 in range(0, len(items), size):
                 unit_bone.append(b)
                 unit_tile.append(ti)
-                for (lv, w, f) in items[p0:p0 + size]:
+                for (lv, w, f) in _interleave_for_streams(items[p0:p0 + size]):
                     it_v.append(lv)
                     it_w.append(w)
                     it_first.append(f)
