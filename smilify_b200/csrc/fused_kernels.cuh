@@ -57,7 +57,11 @@ __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.
 // changes per pass -- beta, trans and the bone transforms of the sample pair -- sits in shared memory
 // pair-interleaved, so every LDS delivers (sample b, sample b+1) operands ready for FFMA2.
 constexpr int SKIN_FWD_THREADS = 256;  // == packer.FWD_CHUNK
-constexpr int SKIN_FWD_STAGES = 3;     // output staging ring (each stage: 4 rows = verts/v_shaped of 2 samples)
+#ifndef SMIL_FWD_PPS
+#define SMIL_FWD_PPS 2
+#endif
+constexpr int SKIN_FWD_PPS = SMIL_FWD_PPS;        // sample pairs computed per CTA barrier / shipping step (1 or 2)
+constexpr int SKIN_FWD_STAGES = SKIN_FWD_PPS == 1 ? 3 : 4;   // output staging ring (each stage: 4 rows = verts/v_shaped of 2 samples)
 constexpr int SKIN_FWD_GPMAX = 16;     // sample pairs per CTA
 
 struct SkinFwdArgs {
@@ -166,11 +170,15 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
     long long off = ((long long)(2 * p0 + (second ? 1 : 0)) * V + (long long)chunk * C) * 3;   // this warp's row
     long long offw = ((long long)(2 * p0) * V + (long long)chunk * C) * 3;                      // writer phases
     const float* blkp = sBlk + (size_t)buf * a.GP * a.blk;
-    for (int g = 0; g < GPn; ++g) {
-      float* st = sStage + sidx * (4 * SF);
-      const float* Ag = blkp;
-      const float4* bp4 = reinterpret_cast<const float4*>(blkp + PPB * J);
-      const float4* tp4 = reinterpret_cast<const float4*>(blkp + PPB * J + 2 * NB2M);
+    for (int g = 0; g < GPn; g += SKIN_FWD_PPS) {
+#pragma unroll
+     for (int u = 0; u < SKIN_FWD_PPS; ++u) {
+      if (g + u >= GPn) break;
+      float* st = sStage + (sidx + u) * (4 * SF);
+      const float* Ag = blkp + (size_t)u * a.blk;
+      const long long offw_u = offw + u * off_step;
+      const float4* bp4 = reinterpret_cast<const float4*>(Ag + PPB * J);
+      const float4* tp4 = reinterpret_cast<const float4*>(Ag + PPB * J + 2 * NB2M);
       // shape blend for both samples
       float2 vs0 = T2[0], vs1 = T2[1], vs2 = T2[2];
 #pragma unroll
@@ -206,46 +214,51 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
       if (DIRECT) {
         // straight from registers: 12-byte pieces at a 12-byte stride; a warp covers 384 contiguous bytes per tensor row
         if (writer) {
-          float* d = a.verts + offw + pos3;
+          float* d = a.verts + offw_u + pos3;
           d[0] = o0.x; d[1] = o1.x; d[2] = o2.x;
-          float* e = a.v_shaped + offw + pos3;
+          float* e = a.v_shaped + offw_u + pos3;
           e[0] = vs0.x; e[1] = vs1.x; e[2] = vs2.x;
-          if (2 * (p0 + g) + 1 < a.B) {
+          if (2 * (p0 + g + u) + 1 < a.B) {
             d += 3LL * V; e += 3LL * V;
             d[0] = o0.y; d[1] = o1.y; d[2] = o2.y;
             e[0] = vs0.y; e[1] = vs1.y; e[2] = vs2.y;
           }
         }
-      } else {
-      if (writer) {
+      } else if (writer) {
         float* r = st + pos3;
         int ph0 = 0, ph1 = 0;
-        if (!ALIGNED) { ph0 = (int)(offw & 3); ph1 = (int)((offw + 3LL * V) & 3); }
+        if (!ALIGNED) { ph0 = (int)(offw_u & 3); ph1 = (int)((offw_u + 3LL * V) & 3); }
         r[ph0 + 0] = o0.x;  r[ph0 + 1] = o1.x;  r[ph0 + 2] = o2.x;                         // verts, sample b
         r[SF + ph1 + 0] = o0.y;  r[SF + ph1 + 1] = o1.y;  r[SF + ph1 + 2] = o2.y;          // verts, sample b+1
         r[2 * SF + ph0 + 0] = vs0.x; r[2 * SF + ph0 + 1] = vs1.x; r[2 * SF + ph0 + 2] = vs2.x;  // v_shaped, b
         r[3 * SF + ph1 + 0] = vs0.y; r[3 * SF + ph1 + 1] = vs1.y; r[3 * SF + ph1 + 2] = vs2.y;  // v_shaped, b+1
       }
+     }
+      if (!DIRECT) {
       fence_proxy_async();
-      // the stage the NEXT pass writes was last read by the stores of pass (now)+1-STAGES
-      if (shipper && lane == 0) bulk_wait_read<SKIN_FWD_STAGES - 2>();
+      // the stages the NEXT step writes were last read by the stores of step (now)+1-STAGES/PPS
+      if (shipper && lane == 0) bulk_wait_read<SKIN_FWD_STAGES / SKIN_FWD_PPS - 2>();
       __syncthreads();
       if (shipper) {
-        if (!second || 2 * (p0 + g) + 1 < a.B) {
-          const float* src = st + warp * SF;
-          if (ALIGNED) {
-            if (lane == 0) bulk_s2g(ship_dst + off, src, (uint32_t)n * 4u);
-          } else {
-            store_row(ship_dst, off, src, (int)(off & 3), n, lane);
+#pragma unroll
+        for (int u = 0; u < SKIN_FWD_PPS; ++u) {
+          if (g + u < GPn && (!second || 2 * (p0 + g + u) + 1 < a.B)) {
+            const float* src = sStage + (sidx + u) * (4 * SF) + warp * SF;
+            const long long off_u = off + u * off_step;
+            if (ALIGNED) {
+              if (lane == 0) bulk_s2g(ship_dst + off_u, src, (uint32_t)n * 4u);
+            } else {
+              store_row(ship_dst, off_u, src, (int)(off_u & 3), n, lane);
+            }
           }
         }
         if (lane == 0) bulk_commit();
       }
       }
-      off += off_step;
-      offw += off_step;
-      blkp += a.blk;
-      sidx = (sidx + 1 == SKIN_FWD_STAGES) ? 0 : sidx + 1;
+      off += SKIN_FWD_PPS * off_step;
+      offw += SKIN_FWD_PPS * off_step;
+      blkp += (size_t)SKIN_FWD_PPS * a.blk;
+      sidx = (sidx + SKIN_FWD_PPS >= SKIN_FWD_STAGES) ? 0 : sidx + SKIN_FWD_PPS;
     }
   }
   if (!DIRECT && shipper && lane == 0) bulk_wait_read<0>();
