@@ -66,6 +66,7 @@ constexpr int SKIN_FWD_GPMAX = 16;     // sample pairs per CTA
 
 struct SkinFwdArgs {
   int B, nb, GP;              // GP sample pairs per group (one TMA load, GP passes)
+  int top_sync;               // 1: CTA barrier at the top of every group as well (tuning switch, see the kernel)
   int blk;                    // floats per pair block of `pp`
   const float* pp;            // [ceil(B/2)][blk] per-pair parameter blocks written by the pose pass:
                               //   A2 [J][12][2] | beta2 [NB2max][2] | trans2 [4][2]   (all pair-interleaved)
@@ -162,7 +163,9 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
   int sidx = 0, it = 0;
   for (int grp = blockIdx.y; grp < ngroups; grp += gridDim.y, ++it) {
     const int buf = it & 1;
-    __syncthreads();  // every thread is done with the other buffer (group it-1)
+    // every thread must be done with the other buffer (group it-1) before it is refilled: on the staged path the
+    // barrier of that group's last shipping step, which follows its last read of the buffer, already guarantees it
+    if (DIRECT || a.top_sync) __syncthreads();
     if (tid == 0 && grp + (int)gridDim.y < ngroups) issue(grp + gridDim.y, buf ^ 1);
     mbar_wait(&bars[buf], (uint32_t)((it >> 1) & 1));
     const int p0 = grp * a.GP;

@@ -26,6 +26,7 @@ namespace {
 struct ProfSlot { const char* name; cudaEvent_t beg, end; };
 std::atomic<long long> g_launches{0};
 std::atomic<int> g_prof_on{0};
+int g_fwd_topsync = -1;  // SMIL_FWD_TOPSYNC: extra CTA barrier at the top of every forward group (-1 = by group size)
 int g_fwd_gp = 0;   // tuning override (SMIL_FWD_GP): sample pairs per TMA group of the fused forward pass
 int g_fwd_direct = 0;  // tuning override (SMIL_FWD_DIRECT): register -> global stores instead of the TMA staging ring
 int g_bwd_stages = 1;  // SMIL_BWD_STAGES: 1 = single-buffered g_verts rows (more CTAs per SM), 2 = double-buffered
@@ -399,6 +400,7 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
                s->bwd_rec == skin_bwd_rec_floats(nbt_of(d.nB)) && d.J <= 64 && d.h_max_tile_units <= SKIN_BWD_MAXU;
   d.device = s->device;
   if (const char* e = getenv("SMIL_FWD_GP")) g_fwd_gp = atoi(e);
+  if (const char* e = getenv("SMIL_FWD_TOPSYNC")) g_fwd_topsync = atoi(e);
   if (const char* e = getenv("SMIL_FWD_CPS")) g_fwd_cps = atoi(e);
   if (const char* e = getenv("SMIL_BWD_STAGES")) g_bwd_stages = atoi(e);
   if (const char* e = getenv("SMIL_BWD_CPS")) g_bwd_cps = atoi(e);
@@ -646,6 +648,9 @@ int smil_forward(const SmilModel* model, const SmilFwdArgs* f, void* stream) {
       sa.B = B; sa.nb = f->num_betas_used;
       sa.GP = g_fwd_gp > 0 ? std::min(g_fwd_gp, SKIN_FWD_GPMAX) : 2;
       sa.blk = pair_blk(m);
+      // measured on B200 at B = 4096: with the barrier 74.6 vs 76.5 us on STICK (J = 55: 12.5 KB of transforms per TMA
+      // group), without it 224 vs 238 us on the mouse rig (J = 31: 7 KB per group) -> keep it for large groups only
+      sa.top_sync = g_fwd_topsync >= 0 ? g_fwd_topsync : ((size_t)sa.GP * sa.blk * sizeof(float) > 10 * 1024 ? 1 : 0);
       sa.pp = A; sa.verts = f->verts; sa.v_shaped = f->v_shaped;
       if ((rc = launch_skin_fwd(m, sa, st)) != SMIL_OK) return rc;
     }
