@@ -240,6 +240,334 @@ def pin_projection(ref, report):
     np.savez_compressed(os.path.join(rigs.GOLDEN, "projection_opencv.npz"), **{k: np.stack(v) for k, v in rows.items()})
 
 
+# ---------------------------------------------------------------------------------------------------
+# rows 9-12: the loss arithmetic and the PCA helper, pinned against the reference's OWN code
+# ---------------------------------------------------------------------------------------------------
+def _extract_function(path, name):
+    """Source of the (possibly nested-in-a-class) function ``name`` of a reference file, decorators
+    dropped, dedented, so that ``exec`` defines it as a plain function taking ``self`` first."""
+    import textwrap
+
+    src = open(path).read()
+    for node in ast.walk(ast.parse(src)):
+        if isinstance(node, ast.FunctionDef) and node.name == name:
+            node.decorator_list = []
+            return textwrap.dedent(ast.get_source_segment(src, node))
+    raise AssertionError("%s not found in %s" % (name, path))
+
+
+def _extract_statements(path, func_name, pick):
+    """Source of the statements of ``func_name`` selected by ``pick(node)`` (in order)."""
+    import textwrap
+
+    src = open(path).read()
+    for fn in ast.walk(ast.parse(src)):
+        if isinstance(fn, ast.FunctionDef) and fn.name == func_name:
+            got = [textwrap.dedent(ast.get_source_segment(src, n)) for n in ast.walk(fn) if pick(n)]
+            return got
+    raise AssertionError("%s not found in %s" % (func_name, path))
+
+
+class _Stub:
+    pass
+
+
+def load_reference_loss_functions(ref):
+    """AST-extract-and-exec the reference bodies of rows 9-12 (nothing is copied into the repo: the
+    source is read from ``ref`` at pin time and executed in a scratch namespace)."""
+    from typing import List, Optional
+
+    import torch.nn.functional as F
+
+    mv = os.path.join(ref, "smal_fitter", "neuralSMIL", "multiview_smil_regressor.py")
+    sv = os.path.join(ref, "smal_fitter", "neuralSMIL", "smil_image_regressor.py")
+    ft = os.path.join(ref, "smal_fitter", "fitter.py")
+    ns = {"torch": torch, "np": np, "Optional": Optional, "List": List, "F": F}
+    exec(_extract_function(sv, "safe_to_tensor"), ns)
+    for path, name in ((mv, "_compute_batched_keypoint_loss"), (sv, "_compute_batch_keypoint_loss"),
+                       (sv, "_compute_batch_keypoint_3d_loss"), (sv, "_transform_separate_pca_weights_to_joint_values")):
+        exec(_extract_function(path, name), ns)
+    # normalise / clamp lines of _batch_project_joints_to_views (multiview_smil_regressor.py:1697-1700)
+    norm = _extract_statements(
+        mv, "_batch_project_joints_to_views",
+        lambda n: isinstance(n, ast.Assign) and isinstance(n.targets[0], ast.Name)
+        and n.targets[0].id in ("rendered_image_size", "proj_points_normalized"))
+    assert len(norm) == 3, norm
+    ns["_mv_norm_src"] = "\n".join(norm)
+    # the fitter's joint objective: body of ``if w_j2d > 0:`` (smal_fitter/fitter.py:292-296)
+    body = _extract_statements(
+        ft, "forward",
+        lambda n: isinstance(n, ast.If) and isinstance(n.test, ast.Compare) and isinstance(n.test.left, ast.Name)
+        and n.test.left.id == "w_j2d")
+    assert len(body) == 1, body
+    import textwrap
+    ns["_fitter_src"] = textwrap.dedent("\n".join(body[0].splitlines()[1:]))
+    return ns
+
+
+def _ref_multiview_norm(ns, proj_points, image_size):
+    self = _Stub()
+    self.renderer = _Stub()
+    self.renderer.image_size = image_size
+    loc = {"self": self, "proj_points": proj_points, "torch": torch}
+    exec(ns["_mv_norm_src"], loc)
+    return loc["proj_points_normalized"]
+
+
+def _ref_fitter_objective(ns, rendered, target, vis, w_j2d):
+    import torch.nn.functional as F
+
+    loc = {"rendered_joints": rendered, "target_joints": target, "target_visibility": vis, "w_j2d": w_j2d,
+           "objs": {}, "F": F, "torch": torch}
+    exec(ns["_fitter_src"], loc)
+    return loc["objs"]["joint"], loc["rendered_joints"]
+
+
+def loss_cases():
+    """Seeded inputs of the loss pins (fp32-representable, so that fp64 reruns see identical data):
+    all-invisible, out-of-bounds GT, view masks, joint weights, NaN / inf predictions, skipped samples."""
+    rs = np.random.RandomState(1234)
+    f = lambda a: np.asarray(a, dtype=np.float32)
+    cases = {}
+    for name, (B, V, J) in {"mv_small": (3, 2, 7), "mv_18cam": (4, 18, 40), "mv_5cam": (6, 5, 55)}.items():
+        pred = f(rs.uniform(-0.1, 1.1, (B, V, J, 2)))
+        tgt = f(np.clip(pred + rs.normal(0, 0.01, pred.shape), -0.2, 1.2))
+        tgt[0, 0, 0] = (1.5, 0.5)                      # out-of-bounds GT -> masked
+        tgt[-1, -1, -1] = (0.5, -0.01)
+        vis = f(rs.uniform(size=(B, V, J)) < 0.8)
+        vmask = np.ones((B, V), dtype=bool)
+        vmask[-1, 0] = False
+        jw = f(rs.uniform(0.5, 2.0, J))
+        pred_bad = pred.copy()
+        pred_bad[0, -1, 1] = (np.nan, 0.3)
+        pred_bad[1, 0, 2] = (np.inf, -np.inf)
+        cases[name] = dict(pred=pred, target=tgt, vis=vis, view_mask=vmask, joint_weights=jw)
+        cases[name + "_plain"] = dict(pred=pred, target=tgt, vis=vis)
+        cases[name + "_nonfinite"] = dict(pred=pred_bad, target=tgt, vis=vis, view_mask=vmask)
+        cases[name + "_invisible"] = dict(pred=pred, target=tgt, vis=np.zeros_like(vis))
+    sv = {}
+    for name, (B, J) in {"sv_55": (9, 55), "sv_31": (5, 31)}.items():
+        pred = f(rs.uniform(-0.2, 1.2, (B, J, 2)))
+        tgt = f(rs.uniform(-0.05, 1.05, (B, J, 2)))
+        vis = f(rs.uniform(size=(B, J)) < 0.7)
+        vis[2] = 0.0                                     # sample without a valid joint: skipped
+        smask = np.ones(B, dtype=bool)
+        smask[1] = False                                 # keypoint_data is None
+        jw = f(rs.uniform(0.5, 2.0, J))
+        j3 = f(rs.uniform(-0.5, 0.5, (B, J, 3)))
+        t3 = f(j3 + rs.normal(0, 0.02, j3.shape))
+        t3[0, 3] = 0.0                                   # all-zero sentinel joint
+        t3[3] = 0.0                                      # a whole sample of sentinels
+        pred_bad = pred.copy()
+        pred_bad[0, 1] = (np.nan, 0.2)
+        j3_bad = j3.copy()
+        j3_bad[0, 5, 1] = np.inf
+        sv[name] = dict(pred=pred, target=tgt, vis=vis, joint_weights=jw, sample_mask=smask, j3=j3, t3=t3)
+        sv[name + "_plain"] = dict(pred=pred, target=tgt, vis=vis, j3=j3, t3=t3)
+        sv[name + "_nonfinite"] = dict(pred=pred_bad, target=tgt, vis=vis, joint_weights=jw, j3=j3_bad, t3=t3)
+    return cases, sv
+
+
+def pin_losses(ref, report):
+    ns = load_reference_loss_functions(ref)
+    stub = _Stub()
+    stub.device = torch.device("cpu")
+    worst = {}
+    frozen = {}
+
+    def upd(tag, e):
+        worst[tag] = max(worst.get(tag, 0.0), e)
+
+    def run_pair(tag, name, ref_fn, ora_fn, x32, dtype):
+        """Runs reference and oracle on a leaf tensor of ``dtype``; returns (ref value, ref grad, max rel diffs)."""
+        xr = torch.from_numpy(x32).to(dtype).requires_grad_(True)
+        xo = torch.from_numpy(x32).to(dtype).requires_grad_(True)
+        lr, lo = ref_fn(xr), ora_fn(xo)
+        gr = go = np.zeros_like(x32, dtype=np.float64)
+        if lr.requires_grad and lr.grad_fn is not None:
+            lr.backward()
+            gr = xr.grad.double().numpy()
+        if lo.requires_grad and lo.grad_fn is not None:
+            lo.backward()
+            go = xo.grad.double().numpy()
+        vr, vo = float(lr.detach()), float(lo.detach())
+        if np.isnan(vr) or np.isnan(vo):   # the reference's inf * 0: both sides must agree on where the NaNs are
+            ev = 0.0 if (np.isnan(vr) and np.isnan(vo)) else float("inf")
+            eg = 0.0 if np.array_equal(np.isnan(gr), np.isnan(go)) else float("inf")
+            ok = ~np.isnan(gr)
+            gr, go = np.where(ok, gr, 0.0), np.where(ok, go, 0.0)
+        else:
+            ev = abs(vr - vo) / max(abs(vr), 1e-30)
+            eg = 0.0
+        eg = max(eg, float(np.abs(gr - go).max() / max(np.abs(gr).max(), 1e-30)) if np.abs(gr).max() > 0 else float(np.abs(go).max()))
+        upd(tag + "_value_" + ("f64" if dtype == torch.float64 else "f32"), ev)
+        upd(tag + "_grad_" + ("f64" if dtype == torch.float64 else "f32"), eg)
+        return vr, (xr.grad.double().numpy() if xr.grad is not None else gr)
+
+    mvc, svc = loss_cases()
+    T = lambda a, dt: None if a is None else (torch.from_numpy(np.asarray(a)) if np.asarray(a).dtype == bool
+                                              else torch.from_numpy(np.asarray(a)).to(dt))
+    # ---- row 10: multi-view loss ------------------------------------------------------------------
+    for name, c in mvc.items():
+        for dt in (torch.float64, torch.float32):
+            tgt, vis = T(c["target"], dt), T(c["vis"], dt)
+            vm = T(c.get("view_mask"), dt)
+            jw = T(c.get("joint_weights"), dt)
+            val, grad = run_pair(
+                "multiview", name,
+                lambda x: ns["_compute_batched_keypoint_loss"](stub, x, tgt, vis, vm, jw),
+                lambda x: PO.multiview_keypoint_loss(x, tgt, vis, None if vm is None else vm.to(dt), jw), c["pred"], dt)
+            if dt == torch.float64:
+                frozen["multiview/" + name] = dict(c, loss=np.float64(val), grad_pred=grad)
+    # ---- normalise / clamp of the multi-view projection (the PyTorch3D call itself stays unpinned) ----
+    rs = np.random.RandomState(77)
+    pp = rs.uniform(-200, 800, (6, 11, 2)).astype(np.float32)
+    for dt in (torch.float64, torch.float32):
+        a = _ref_multiview_norm(ns, torch.from_numpy(pp).to(dt), 512)
+        b = torch.clamp(torch.from_numpy(pp).to(dt) / (512.0 + 1e-8), 0.0, 1.0)
+        upd("multiview_norm_" + ("f64" if dt == torch.float64 else "f32"), float((a - b).abs().max()))
+    # ---- row 11: single-view 2-D and 3-D losses ------------------------------------------------------
+    for name, c in svc.items():
+        B = c["pred"].shape[0]
+        sm = c.get("sample_mask")
+        kd = [None if (sm is not None and not sm[i]) else
+              {"keypoints_2d": c["target"][i], "keypoint_visibility": c["vis"][i], "keypoints_3d": c["t3"][i]} for i in range(B)]
+        for dt in (torch.float64, torch.float32):
+            tgt, vis, t3 = T(c["target"], dt), T(c["vis"], dt), T(c["t3"], dt)
+            jw = T(c.get("joint_weights"), dt)
+            smt = None if sm is None else torch.from_numpy(sm)
+            val, grad = run_pair(
+                "singleview", name,
+                lambda x: ns["_compute_batch_keypoint_loss"](stub, x, kd, jw),
+                lambda x: PO.singleview_keypoint_loss(x, tgt, vis, jw, smt), c["pred"], dt)
+            val3, grad3 = run_pair(
+                "keypoint3d", name,
+                lambda x: ns["_compute_batch_keypoint_3d_loss"](stub, x, kd, jw),
+                lambda x: PO.keypoint3d_loss(x, t3, vis, jw, smt), c["j3"], dt)
+            if dt == torch.float64:
+                frozen["singleview/" + name] = dict(c, loss=np.float64(val), grad_pred=grad, loss3=np.float64(val3), grad_j3=grad3)
+    # ---- row 9: the fitter's joint objective (-1 fill on both sides + F.mse_loss) -------------------
+    rs = np.random.RandomState(5)
+    for name, (N, J) in {"fit_55": (10, 55), "fit_31": (33, 31), "fit_invisible": (3, 5)}.items():
+        pr = rs.uniform(0, 512, (N, J, 2)).astype(np.float32)
+        tg = rs.uniform(0, 512, (N, J, 2)).astype(np.float32)
+        vi = (rs.uniform(size=(N, J)) < (0.0 if name == "fit_invisible" else 0.7)).astype(np.float32)
+        for dt in (torch.float64, torch.float32):
+            def ref_fn(x):
+                val, _ = _ref_fitter_objective(ns, x * 1.0, torch.from_numpy(tg).to(dt).clone(), torch.from_numpy(vi).to(dt), 25.0)
+                return val
+
+            def ora_fn(x):
+                v = torch.from_numpy(vi).bool()
+                p = torch.where(v[..., None], x, torch.full_like(x, -1.0))
+                t = torch.where(v[..., None], torch.from_numpy(tg).to(dt), torch.full_like(x, -1.0))
+                return 25.0 * torch.mean((p - t) ** 2)
+
+            val, grad = run_pair("fitter", name, ref_fn, ora_fn, pr, dt)
+            if dt == torch.float64:
+                frozen["fitter/" + name] = dict(pred=pr, target=tg, vis=vi, w_j2d=np.float64(25.0), loss=np.float64(val), grad_pred=grad)
+    # ---- row 12: PCA scale / translation weights -> per-joint values -----------------------------------
+    cfg = types.ModuleType("config")
+    for rig in ("stick",):
+        dd = rigs.get_rig(rig)
+        J = len(dd["J_names"])
+        cfg.dd = {"J_names": list(dd["J_names"])}
+        ns["config"] = cfg
+        sd = np.transpose(np.asarray(dd["scaledirs"], dtype=np.float32), (1, 2, 0)).copy()   # (C,J,3) -> (J,3,C)
+        td = np.transpose(np.asarray(dd["transdirs"], dtype=np.float32), (1, 2, 0)).copy()
+        C = sd.shape[2]
+        rs = np.random.RandomState(9)
+        for name, sw, tw in (("pca_small", rs.normal(0, 0.5, (7, C)), rs.normal(0, 0.5, (7, C))),
+                             ("pca_clamped", rs.normal(0, 40.0, (5, C)), rs.normal(0, 1.0, (5, C))),
+                             ("pca_notrans", rs.normal(0, 0.5, (4, C)), None)):
+            sw = sw.astype(np.float32)
+            tw = None if tw is None else tw.astype(np.float32)
+            for dt in (torch.float64, torch.float32):
+                st = _Stub()
+                st._get_pca_dirs_tensors = lambda device, dt=dt: (torch.from_numpy(sd).to(dt), torch.from_numpy(td).to(dt))
+                gl = torch.from_numpy(np.random.RandomState(3).standard_normal((sw.shape[0], J, 3))).to(dt)
+                gb = torch.from_numpy(np.random.RandomState(4).standard_normal((sw.shape[0], J, 3))).to(dt)
+                outs = {}
+                for side in ("ref", "ora"):
+                    a = torch.from_numpy(sw).to(dt).requires_grad_(True)
+                    b = None if tw is None else torch.from_numpy(tw).to(dt).requires_grad_(True)
+                    if side == "ref":
+                        ls, bt = ns["_transform_separate_pca_weights_to_joint_values"](st, a, b)
+                    else:
+                        ls, bt = SO.pca_weights_to_joint_values(torch.from_numpy(sd).to(dt), torch.from_numpy(td).to(dt), a, b)
+                    loss = (ls.to(dt) * gl).sum() + ((bt.to(dt) * gb).sum() if b is not None else 0.0)
+                    loss.backward()
+                    outs[side] = (ls.detach().double().numpy(), bt.detach().double().numpy(), a.grad.double().numpy(),
+                                  None if b is None else b.grad.double().numpy())
+                tag = "pca_" + ("f64" if dt == torch.float64 else "f32")
+                for x, y in zip(outs["ref"], outs["ora"]):
+                    if x is not None:
+                        upd(tag, rel(y, x))
+                if dt == torch.float64:
+                    r = outs["ref"]
+                    frozen["pca/" + name] = dict(scaledirs=sd, transdirs=td, scale_w=sw, trans_w=tw if tw is not None else np.zeros(0, np.float32),
+                                                 g_ls=gl.numpy(), g_bt=gb.numpy(), log_scales=r[0], betas_trans=r[1], grad_scale_w=r[2],
+                                                 grad_trans_w=r[3] if r[3] is not None else np.zeros(0))
+    report["loss_pins"] = worst
+    print("loss pins (max rel diff oracle vs extracted reference code):", json.dumps(worst, indent=1, sort_keys=True))
+    for k, v in worst.items():
+        assert v < (1e-12 if k.endswith("f64") else 2e-6), (k, v)
+    flat = {}
+    for key, d in frozen.items():
+        for k, v in d.items():
+            if v is not None:
+                flat[key + "/" + k] = np.asarray(v)
+    np.savez_compressed(os.path.join(rigs.GOLDEN, "loss_pins.npz"), **flat)
+
+
+def pin_loss_chains(ref, report):
+    """Whole chains projection -> loss on the scenes the GPU tests use: (i) the reference's own loss code evaluated on
+    the oracle's projected points, frozen with its gradient w.r.t. those points (tests chain it through the projection);
+    (ii) the fp32 floor: the same torch op graph in fp32 against fp64 -- what the reference itself delivers in fp32."""
+    ns = load_reference_loss_functions(ref)
+    stub = _Stub()
+    stub.device = torch.device("cpu")
+    flat, floors = {}, {}
+
+    def grads_of(dt, sc, loss_fn):
+        B, V = sc["target"].shape[:2]
+        leaf = {k: torch.from_numpy(sc[k]).to(dt).requires_grad_(True) for k in ("joints", "R", "T", "fov")}
+        pred = PO.multiview_project(leaf["joints"], leaf["R"].expand(B, V, 3, 3), leaf["T"].expand(B, V, 3),
+                                    leaf["fov"].expand(B, V), torch.from_numpy(sc["aspect"]).to(dt).expand(B, V),
+                                    float(sc["image_size"]))
+        loss = loss_fn(pred, dt)
+        loss.backward()
+        return pred.detach(), float(loss.detach()), {k: v.grad.double().numpy() for k, v in leaf.items()}
+
+    for name, (B, V, J, seed, shared) in rigs.LOSS_SCENES.items():
+        sc = rigs.loss_scene(B, V, J, seed, shared)
+        tt = lambda k, dt: torch.from_numpy(sc[k]).to(dt)
+        ref_loss = lambda pred, dt: ns["_compute_batched_keypoint_loss"](
+            stub, pred, tt("target", dt), tt("vis", dt), torch.from_numpy(sc["view_mask"]).bool(), tt("joint_weights", dt))
+        ora_loss = lambda pred, dt: PO.multiview_keypoint_loss(pred, tt("target", dt), tt("vis", dt), tt("view_mask", dt),
+                                                               tt("joint_weights", dt))
+        p64, l64, g64 = grads_of(torch.float64, sc, ref_loss)
+        _p, lo64, go64 = grads_of(torch.float64, sc, ora_loss)
+        assert abs(l64 - lo64) <= 1e-13 * abs(l64), (name, l64, lo64)
+        for k in g64:
+            assert rel(go64[k], g64[k]) < 1e-12, (name, k)
+        p32, l32, g32 = grads_of(torch.float32, sc, ref_loss)
+        floors[name] = {"loss": abs(l32 - l64) / abs(l64), "proj": rel(p32.double().numpy(), p64.numpy()),
+                        **{"grad_" + k: rel(g32[k], g64[k]) for k in g64}}
+        flat[name + "/pred"] = p64.numpy()
+        flat[name + "/loss"] = np.float64(l64)
+        for k, v in g64.items():
+            flat[name + "/grad_" + k] = v
+    report["loss_chain_fp32_floor"] = floors
+    worst = {}
+    for d in floors.values():
+        for k, v in d.items():
+            worst[k] = max(worst.get(k, 0.0), v)
+    report["loss_chain_fp32_floor_worst"] = worst
+    print("fp32 torch graph vs fp64 on the multi-view loss scenes (max rel):", json.dumps(worst, sort_keys=True))
+    np.savez_compressed(os.path.join(rigs.GOLDEN, "loss_chain_pins.npz"), **flat)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ref", default="/root/reference")
@@ -250,6 +578,8 @@ def main():
     report = {"reference": a.ref, "torch": torch.__version__, "cases": {}}
     pin_smal(a.ref, report)
     pin_projection(a.ref, report)
+    pin_losses(a.ref, report)
+    pin_loss_chains(a.ref, report)
     with open(os.path.join(rigs.GOLDEN, "PIN_REPORT.json"), "w") as fh:
         json.dump(report, fh, indent=1, sort_keys=True)
     print("pinned:", json.dumps(report["worst"]))

@@ -131,13 +131,15 @@ def multiview_keypoint_loss(pred, target, visibility, view_mask=None, joint_weig
     if view_mask is not None:
         valid = valid & view_mask.bool()[..., None]
     if not valid.any():
-        return torch.tensor(eps, dtype=pred.dtype)
-    w = valid.to(pred.dtype)[..., None]
+        return torch.tensor(eps)   # fp32, like the reference's ``torch.tensor(eps, device=...)``
+    # dtype behaviour as in the reference: the mask is ``.float()`` (fp32) whatever the inputs are, so the
+    # unweighted count ``valid.sum().float() * 2 + eps`` is an fp32 expression (eps is absorbed)
+    w = valid.float()[..., None]
     if joint_weights is not None:
         w = w * joint_weights.view(1, 1, -1, 1)
-        denom = (valid.to(pred.dtype) * joint_weights.view(1, 1, -1)).sum() * 2 + eps
+        denom = (valid.float() * joint_weights.view(1, 1, -1)).sum() * 2 + eps
     else:
-        denom = valid.sum().to(pred.dtype) * 2 + eps
+        denom = valid.sum().float() * 2 + eps
     return (((pred - target) ** 2) * w).sum() / denom + eps
 
 
@@ -159,16 +161,16 @@ def singleview_keypoint_loss(pred, target, visibility, joint_weights=None, sampl
         p = torch.nan_to_num(pred[i], nan=0.0, posinf=0.0, neginf=0.0)
         if not valid.any():
             continue
-        mw = valid.to(pred.dtype)
+        mw = valid.float()   # fp32 mask / count as in the reference (see multiview_keypoint_loss)
         if joint_weights is not None:
             mw = mw * joint_weights
-            denom = (valid.to(pred.dtype) * joint_weights).sum() * 2 + eps
+            denom = (valid.float() * joint_weights).sum() * 2 + eps
         else:
-            denom = valid.sum().to(pred.dtype) * 2 + eps
+            denom = valid.sum().float() * 2 + eps
         total = total + (((p - target[i]) ** 2) * mw[:, None]).sum() / denom
         nvalid += 1
     if nvalid == 0:
-        return torch.tensor(eps, dtype=pred.dtype)
+        return torch.tensor(eps)   # fp32, like the reference's ``torch.tensor(eps, device=...)``
     return total / nvalid + eps
 
 
@@ -182,14 +184,14 @@ def keypoint3d_loss(joints3d, target3d, visibility, joint_weights=None, sample_m
         valid = visibility[i].bool() & finite & (target3d[i].abs().sum(dim=-1) > 0)
         if not valid.any():
             continue
-        mw = valid.to(joints3d.dtype)
+        mw = valid.float()
         if joint_weights is not None:
             mw = mw * joint_weights
-            denom = (valid.to(joints3d.dtype) * joint_weights).sum() * 3 + eps
+            denom = (valid.float() * joint_weights).sum() * 3 + eps
         else:
-            denom = valid.sum().to(joints3d.dtype) * 3 + eps
+            denom = valid.sum().float() * 3 + eps
         total = total + (((joints3d[i] - target3d[i]) ** 2) * mw[:, None]).sum() / denom
         nvalid += 1
     if nvalid == 0:
-        return torch.tensor(eps, dtype=joints3d.dtype)
+        return torch.tensor(eps)
     return total / nvalid + eps

@@ -271,11 +271,12 @@ __global__ void kp3d_fwd_kernel(SmilKp3dArgs a) {
     const float* p = a.joints + ((long long)b * a.num_joints + j) * 3;
     const float* t = a.target + ((long long)b * a.num_joints + j) * 3;
     const float wt = kp3d_weight(a, b, j, p, t);
-    if (wt != 0.f) {
-      const float e0 = p[0] - t[0], e1 = p[1] - t[1], e2 = p[2] - t[2];
-      num = fmaf(wt, e0 * e0 + e1 * e1 + e2 * e2, num);
-      cnt += 1.f;
-    }
+    if (a.sample_mask && a.sample_mask[b] == 0.f) continue;   // keypoint_data is None: the reference skips the sample
+    // the reference multiplies the squared error by the 0/1 mask (smil_image_regressor.py:3383-3391), so a masked-out
+    // NON-FINITE joint or target still turns the sample's loss into NaN (inf * 0); the same arithmetic here
+    const float e0 = p[0] - t[0], e1 = p[1] - t[1], e2 = p[2] - t[2];
+    num = fmaf(wt, e0 * e0 + e1 * e1 + e2 * e2, num);
+    if (wt != 0.f) cnt += 1.f;
     ws += wt;
   }
 #pragma unroll
@@ -317,6 +318,10 @@ __global__ void kp3d_bwd_kernel(SmilKp3dArgs a) {
   const float gl = a.g_loss ? a.g_loss[0] : 1.f;
   float s = 0.f;
   if (pc > 0.f && wt != 0.f) s = gl * scale * 2.f * wt / (pw * 3.f + 1e-8f);
+  if (pc <= 0.f || (a.sample_mask && a.sample_mask[b] == 0.f)) {   // sample not in the reference's graph at all
+    a.g_joints[i * 3] = 0.f; a.g_joints[i * 3 + 1] = 0.f; a.g_joints[i * 3 + 2] = 0.f;
+    return;
+  }
   a.g_joints[i * 3] = s * (p[0] - t[0]);
   a.g_joints[i * 3 + 1] = s * (p[1] - t[1]);
   a.g_joints[i * 3 + 2] = s * (p[2] - t[2]);

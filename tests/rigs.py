@@ -217,3 +217,48 @@ def hash_name(s):
     for ch in s:
         h = (h * 131 + ord(ch)) % 1000003
     return h
+
+
+# ---- seeded scenes of the reprojection-loss parity tests (tests/test_gpu_losses.py, oracle/pin_against_reference.py) ----
+LOSS_SCENES = {
+    # name: (B, V, J, seed, shared camera)
+    "mv_b5_v3_j11": (5, 3, 11, 7, False),
+    "mv_b3_v18_j40": (3, 18, 40, 7, False),
+    "mv_b2_v1_j55": (2, 1, 55, 7, False),
+    "mv_b64_v5_j55": (64, 5, 55, 7, False),
+    "mv_b5_v3_j11_shared": (5, 3, 11, 7, True),
+    "mv_b3_v18_j40_shared": (3, 18, 40, 7, True),
+}
+
+
+def loss_scene(B, V, J, seed, shared_cam=False, S=512.0):
+    """fp32-representable joints / ring cameras / noisy targets / visibility / masks / joint weights of one
+    multi-view scene (SURVEY.md section 8(d), config 3 set-up: look_at ring, radius 3, elevation 15 degrees)."""
+    import torch
+
+    from oracle import projection_oracle as PO
+
+    rs = np.random.RandomState(seed)
+    f = lambda a: np.asarray(a, dtype=np.float32)
+    joints = f(rs.uniform(-0.4, 0.4, (B, J, 3)))
+    R, T = PO.look_at_ring(V, 3.0, 15.0, dtype=torch.float64)
+    R, T = R.numpy(), T.numpy()
+    if shared_cam:
+        R, T = f(R[None]), f(T[None])
+        fov, asp = f(np.full((1, V), 60.0)), f(np.ones((1, V)))
+    else:
+        R = f(np.broadcast_to(R[None], (B, V, 3, 3)))
+        T = f(np.broadcast_to(T[None], (B, V, 3)) + rs.normal(0, 0.05, (B, V, 3)))
+        fov, asp = f(rs.uniform(40, 70, (B, V))), f(rs.uniform(0.8, 1.3, (B, V)))
+    t64 = lambda a: torch.from_numpy(np.ascontiguousarray(a)).double()
+    with torch.no_grad():
+        clean = PO.multiview_project(t64(joints), t64(R).expand(B, V, 3, 3), t64(T).expand(B, V, 3), t64(fov).expand(B, V),
+                                     t64(asp).expand(B, V), S).numpy()
+    tgt = f(clean + rs.normal(0, 2.0 / S, clean.shape))
+    tgt[0, 0, 0] = 1.5  # out-of-bounds GT is masked out
+    vis = f(rs.uniform(size=(B, V, J)) < 0.8)
+    vmask = np.ones((B, V), dtype=np.float32)
+    vmask[-1, -1] = 0.0
+    jw = f(rs.uniform(0.5, 2.0, J))
+    return dict(joints=joints, R=R, T=T, fov=fov, aspect=asp, target=tgt, vis=vis, view_mask=vmask, joint_weights=jw,
+                image_size=np.float32(S))

@@ -1,8 +1,12 @@
 """GPU parity of the reprojection / keypoint losses and of the stand-alone batch_lbs drop-ins,
 called through the public Python surface (-> C ABI), against the fp64 oracles.
 
-Tolerance: 1e-5 relative on the loss and on projected points; 1e-4 relative (max-norm) on loss
-gradients, whose fp32 value is a difference of O(1e2)-pixel terms."""
+Tolerance: 1e-5 relative on the loss and on projected points.  Gradients of the projection + loss chain:
+GRAD_TOL = 3.5e-5 relative (max-norm).  north_star asks 1e-5, but the reference's OWN torch graph run in fp32
+differs from its fp64 evaluation by up to 1.6e-5 on these very scenes (measured by
+oracle/pin_against_reference.py::pin_loss_chains, tests/golden/PIN_REPORT.json key
+"loss_chain_fp32_floor_worst": grad_fov 1.6e-5, grad_R 1.1e-5, grad_T 6.9e-6, grad_joints 6.6e-6), so the bar is
+twice that measured fp32 floor; the loss arithmetic alone (3-D loss, given points) is held to 1e-5."""
 import numpy as np
 import pytest
 import torch
@@ -13,6 +17,7 @@ from tests.common import rel
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
+GRAD_TOL = 3.5e-5   # 2 x the fp32 floor of the reference's own graph (module docstring)
 
 
 def _scene(B, V, J, seed, shared_cam=False):
@@ -65,7 +70,7 @@ def test_multiview_loss(B, V, J, shared_cam):
     assert abs(loss.item() - ref.item()) <= 1e-5 * abs(ref.item())
     for name, a, b in zip(("joints", "R", "T", "fov"), c, o):
         assert a.grad.shape == a.shape, name
-        assert rel(a.grad.cpu().numpy(), b.grad.numpy()) < 1e-4, name
+        assert rel(a.grad.cpu().numpy(), b.grad.numpy()) < GRAD_TOL, name
 
 
 def test_multiview_loss_no_valid_joint():
@@ -101,9 +106,9 @@ def test_fitter_joint_loss(N, J):
     loss.backward()
     assert rel(proj.cpu().numpy(), rproj.detach().numpy()) < 1e-5
     assert abs(loss.item() - ref.item()) <= 1e-5 * abs(ref.item())
-    assert rel(cj.grad.cpu().numpy(), oj.grad.numpy()) < 1e-4
-    assert rel(ct.grad.cpu().numpy(), ot.grad.numpy()) < 1e-4
-    assert cf.grad.shape == (1,) and rel(cf.grad.cpu().numpy(), of.grad.numpy()) < 1e-4
+    assert rel(cj.grad.cpu().numpy(), oj.grad.numpy()) < GRAD_TOL
+    assert rel(ct.grad.cpu().numpy(), ot.grad.numpy()) < GRAD_TOL
+    assert cf.grad.shape == (1,) and rel(cf.grad.cpu().numpy(), of.grad.numpy()) < GRAD_TOL
 
 
 def test_singleview_and_3d_loss():
@@ -132,7 +137,7 @@ def test_singleview_and_3d_loss():
     loss.backward()
     assert rel(proj.cpu().numpy(), pred.detach().numpy()) < 1e-5
     assert abs(loss.item() - ref.item()) <= 1e-5 * abs(ref.item())
-    assert rel(cj.grad.cpu().numpy(), oj.grad.numpy()) < 1e-4
+    assert rel(cj.grad.cpu().numpy(), oj.grad.numpy()) < GRAD_TOL
     # 3D keypoint loss
     t3 = torch.from_numpy(rs.uniform(-0.5, 0.5, (B, J, 3)))
     t3[1, 3] = 0.0  # all-zero GT joint is invalid
@@ -183,3 +188,132 @@ def test_batch_lbs_dropins():
         assert rel(Ac.detach().cpu().numpy(), A.detach().numpy()) < 1e-5
         for name, a, b in zip(("Rs", "Js", "ls", "bt"), c, o):
             assert rel(a.grad.cpu().numpy(), b.grad.numpy()) < 1e-5, (prop, name)
+
+
+# ---- against values the REFERENCE'S OWN loss code produced (frozen by oracle/pin_against_reference.py) ----------
+def _t(a, grad=False):
+    t = torch.from_numpy(np.ascontiguousarray(a)).to(DEV, torch.float32)
+    return t.requires_grad_(True) if grad else t
+
+
+@pytest.mark.parametrize("name", list(__import__("tests.rigs", fromlist=["LOSS_SCENES"]).LOSS_SCENES))
+def test_multiview_loss_vs_frozen_reference_code(name):
+    """CUDA projection + loss against `_compute_batched_keypoint_loss` of the reference executed on the oracle's
+    projected points (tests/golden/loss_chain_pins.npz), gradients chained through the projection in fp64."""
+    import os
+
+    from smilify_b200 import losses
+    from tests import rigs
+
+    z = np.load(os.path.join(rigs.GOLDEN, "loss_chain_pins.npz"))
+    B, V, J, seed, shared = rigs.LOSS_SCENES[name]
+    sc = rigs.loss_scene(B, V, J, seed, shared)
+    c = {k: _t(sc[k], grad=True) for k in ("joints", "R", "T", "fov")}
+    loss, proj = losses.multiview_keypoint_loss(c["joints"], c["R"], c["T"], c["fov"], _t(sc["aspect"]), _t(sc["target"]),
+                                                _t(sc["vis"]), _t(sc["view_mask"]), _t(sc["joint_weights"]),
+                                                float(sc["image_size"]))
+    loss.backward()
+    assert rel(proj.detach().cpu().numpy(), z[name + "/pred"]) < 1e-5
+    assert abs(loss.item() - float(z[name + "/loss"])) <= 1e-5 * abs(float(z[name + "/loss"]))
+    for k, v in c.items():
+        assert v.grad.shape == v.shape, k
+        assert rel(v.grad.cpu().numpy(), z[name + "/grad_" + k]) < GRAD_TOL, (k, rel(v.grad.cpu().numpy(), z[name + "/grad_" + k]))
+
+
+def _pins(prefix):
+    import os
+
+    from tests import rigs
+
+    z = np.load(os.path.join(rigs.GOLDEN, "loss_pins.npz"))
+    return z, sorted({k.split("/")[1] for k in z.files if k.startswith(prefix + "/")})
+
+
+def _joints_for_points(pred_yx, S):
+    """World joints that the camera R = I, T = 0, fov = 90 degrees, aspect 1 projects onto the given (y,x) pixels:
+    screen = S/2 (1 - X/Z) at Z = 1."""
+    p = np.asarray(pred_yx, dtype=np.float64)
+    return np.stack([1.0 - 2.0 * p[..., 1] / S, 1.0 - 2.0 * p[..., 0] / S, np.ones(p.shape[:-1])], axis=-1)
+
+
+def test_keypoint3d_loss_vs_frozen_reference_code():
+    from smilify_b200 import losses
+
+    z, names = _pins("singleview")
+    for n in names:
+        p = "singleview/%s/" % n
+        j3 = _t(z[p + "j3"], grad=True)
+        jw = _t(z[p + "joint_weights"]) if p + "joint_weights" in z.files else None
+        sm = _t(z[p + "sample_mask"].astype(np.float32)) if p + "sample_mask" in z.files else None
+        loss = losses.keypoint3d_loss(j3, _t(z[p + "t3"]), _t(z[p + "vis"]), jw, sm)
+        loss.backward()
+        ref, gref = float(z[p + "loss3"]), z[p + "grad_j3"]
+        if np.isnan(ref):   # the reference's inf * 0 -> NaN for a non-finite predicted joint
+            assert np.isnan(loss.item()), n
+            g = j3.grad.cpu().numpy()
+            assert np.array_equal(np.isnan(g), np.isnan(gref)), n
+            continue
+        assert abs(loss.item() - ref) <= 1e-5 * abs(ref), n
+        assert rel(j3.grad.cpu().numpy(), gref) < 1e-5, n
+
+
+def test_singleview_loss_vs_frozen_reference_code():
+    """`_compute_batch_keypoint_loss` of the reference on given 2-D points; the CUDA path gets joints that a
+    trivial camera maps onto exactly those points (so only the loss arithmetic is compared)."""
+    from smilify_b200 import losses
+
+    z, names = _pins("singleview")
+    S = 512.0
+    for n in names:
+        if n.endswith("nonfinite"):
+            continue   # non-finite 2-D points cannot be produced through a finite camera; covered on the CPU side
+        p = "singleview/%s/" % n
+        pred = z[p + "pred"].astype(np.float64)
+        B = pred.shape[0]
+        joints = _t(_joints_for_points(pred * (S + 1e-8), S), grad=True)
+        R = torch.eye(3, device=DEV).expand(B, 3, 3)
+        T = torch.zeros(B, 3, device=DEV)
+        fov = torch.full((B,), 90.0, device=DEV)
+        jw = _t(z[p + "joint_weights"]) if p + "joint_weights" in z.files else None
+        sm = _t(z[p + "sample_mask"].astype(np.float32)) if p + "sample_mask" in z.files else None
+        loss, proj = losses.singleview_keypoint_loss(joints, R, T, fov, _t(z[p + "target"]), _t(z[p + "vis"]), jw, sm, S)
+        assert np.abs(proj.detach().cpu().numpy() - pred).max() < 2e-6, n
+        ref = float(z[p + "loss"])
+        assert abs(loss.item() - ref) <= 2e-5 * abs(ref), (n, loss.item(), ref)   # points reproduced to ~1e-6 only
+
+
+def test_fitter_objective_vs_frozen_reference_code():
+    """fitter.py:292-296 (-1 fill on both sides + F.mse_loss) executed by the reference on given pixels."""
+    from smilify_b200 import losses
+
+    z, names = _pins("fitter")
+    S = 512.0
+    for n in names:
+        p = "fitter/%s/" % n
+        pred = z[p + "pred"].astype(np.float64)
+        N = pred.shape[0]
+        joints = _t(_joints_for_points(pred, S), grad=True)
+        loss, proj = losses.fitter_joint_loss(joints, torch.eye(3, device=DEV)[None], torch.zeros(1, 3, device=DEV),
+                                              torch.tensor([90.0], device=DEV), _t(z[p + "target"]), _t(z[p + "vis"]),
+                                              float(z[p + "w_j2d"]), S)
+        ref = float(z[p + "loss"])
+        vis = z[p + "vis"] > 0
+        assert np.abs(proj.detach().cpu().numpy()[vis] - pred[vis]).max() < 5e-4, n   # pixels, fp32 camera round trip
+        assert abs(loss.item() - ref) <= 2e-5 * max(abs(ref), 1e-30), (n, loss.item(), ref)
+
+
+def test_pca_joint_values_vs_frozen_reference_code():
+    from smilify_b200 import losses
+
+    z, names = _pins("pca")
+    for n in names:
+        p = "pca/%s/" % n
+        sw = _t(z[p + "scale_w"], grad=True)
+        tw = _t(z[p + "trans_w"], grad=True) if z[p + "trans_w"].size else None
+        ls, bt = losses.pca_joint_values(sw, tw, _t(z[p + "scaledirs"]), _t(z[p + "transdirs"]))
+        ((ls * _t(z[p + "g_ls"])).sum() + ((bt * _t(z[p + "g_bt"])).sum() if tw is not None else 0.0)).backward()
+        assert rel(ls.detach().cpu().numpy(), z[p + "log_scales"]) < 1e-5, n
+        assert rel(bt.detach().cpu().numpy(), z[p + "betas_trans"]) < 1e-5, n
+        assert rel(sw.grad.cpu().numpy(), z[p + "grad_scale_w"]) < 1e-5, n
+        if tw is not None:
+            assert rel(tw.grad.cpu().numpy(), z[p + "grad_trans_w"]) < 1e-5, n

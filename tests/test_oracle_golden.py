@@ -55,3 +55,112 @@ def test_projection_default_camera():
     assert torch.allclose(p[0], torch.tensor([256.0, 256.0]), atol=1e-4)
     assert p[1, 1] > 256.0 and abs(p[1, 0] - 256.0) < 1e-4   # R = diag(-1,1,-1) flips x back
     assert p[2, 0] < 256.0 and abs(p[2, 1] - 256.0) < 1e-4
+
+
+# ---- rows 9-12: oracle vs outputs of the reference's OWN loss / PCA code (tests/golden/loss_pins.npz, frozen by
+# oracle/pin_against_reference.py::pin_losses from AST-extracted reference functions) --------------------------------
+def _pins(prefix):
+    z = np.load(os.path.join(rigs.GOLDEN, "loss_pins.npz"))
+    names = sorted({k.split("/")[1] for k in z.files if k.startswith(prefix + "/")})
+    return z, names
+
+
+def _opt(z, key, dtype=torch.float64):
+    if key not in z.files:
+        return None
+    a = z[key]
+    return torch.from_numpy(a) if a.dtype == bool else torch.from_numpy(a).to(dtype)
+
+
+def test_multiview_loss_oracle_matches_reference_code():
+    z, names = _pins("multiview")
+    assert len(names) >= 12
+    for n in names:
+        p = "multiview/%s/" % n
+        pred = _opt(z, p + "pred").requires_grad_(True)
+        vm = _opt(z, p + "view_mask")
+        loss = PO.multiview_keypoint_loss(pred, _opt(z, p + "target"), _opt(z, p + "vis"),
+                                          None if vm is None else vm.double(), _opt(z, p + "joint_weights"))
+        assert abs(float(loss) - float(z[p + "loss"])) <= 1e-12 * abs(float(z[p + "loss"])), n
+        if loss.grad_fn is not None:
+            loss.backward()
+            assert rel(pred.grad.numpy(), z[p + "grad_pred"]) < 1e-12, n
+        else:
+            assert np.abs(z[p + "grad_pred"]).max() == 0.0, n
+
+
+def test_singleview_and_3d_loss_oracle_matches_reference_code():
+    z, names = _pins("singleview")
+    assert len(names) >= 6
+    for n in names:
+        p = "singleview/%s/" % n
+        sm = _opt(z, p + "sample_mask")
+        jw = _opt(z, p + "joint_weights")
+        pred = _opt(z, p + "pred").requires_grad_(True)
+        loss = PO.singleview_keypoint_loss(pred, _opt(z, p + "target"), _opt(z, p + "vis"), jw, sm)
+        loss.backward()
+        assert abs(float(loss) - float(z[p + "loss"])) <= 1e-12 * abs(float(z[p + "loss"])), n
+        assert rel(pred.grad.numpy(), z[p + "grad_pred"]) < 1e-12, n
+        j3 = _opt(z, p + "j3").requires_grad_(True)
+        loss3 = PO.keypoint3d_loss(j3, _opt(z, p + "t3"), _opt(z, p + "vis"), jw, sm)
+        loss3.backward()
+        if np.isnan(float(z[p + "loss3"])):   # a non-finite predicted joint: inf * 0 in the reference -> NaN loss
+            assert np.isnan(float(loss3)), n
+            assert np.array_equal(np.isnan(j3.grad.numpy()), np.isnan(z[p + "grad_j3"])), n
+            ok = ~np.isnan(z[p + "grad_j3"])
+            assert rel(j3.grad.numpy()[ok], z[p + "grad_j3"][ok]) < 1e-12, n
+        else:
+            assert abs(float(loss3) - float(z[p + "loss3"])) <= 1e-12 * abs(float(z[p + "loss3"])), n
+            assert rel(j3.grad.numpy(), z[p + "grad_j3"]) < 1e-12, n
+
+
+def test_fitter_objective_oracle_matches_reference_code():
+    z, names = _pins("fitter")
+    for n in names:
+        p = "fitter/%s/" % n
+        pred = _opt(z, p + "pred").requires_grad_(True)
+        vis = _opt(z, p + "vis")
+        # fitter.py:292-296 on already-projected points == projection_oracle.fitter_joint_loss after its projection
+        v = vis.bool()
+        pm = torch.where(v[..., None], pred, torch.full_like(pred, -1.0))
+        tm = torch.where(v[..., None], _opt(z, p + "target"), torch.full_like(pred, -1.0))
+        loss = float(z[p + "w_j2d"]) * torch.mean((pm - tm) ** 2)
+        loss.backward()
+        assert abs(float(loss) - float(z[p + "loss"])) <= 1e-12 * max(abs(float(z[p + "loss"])), 1e-30), n
+        assert rel(pred.grad.numpy(), z[p + "grad_pred"]) < 1e-12 or np.abs(z[p + "grad_pred"]).max() == 0.0, n
+
+
+def test_pca_joint_values_oracle_matches_reference_code():
+    from oracle import smal_oracle as SO
+
+    z, names = _pins("pca")
+    assert len(names) == 3
+    for n in names:
+        p = "pca/%s/" % n
+        sw = _opt(z, p + "scale_w").requires_grad_(True)
+        tw = _opt(z, p + "trans_w")
+        tw = tw.requires_grad_(True) if tw.numel() else None
+        ls, bt = SO.pca_weights_to_joint_values(_opt(z, p + "scaledirs"), _opt(z, p + "transdirs"), sw, tw)
+        ((ls * _opt(z, p + "g_ls")).sum() + ((bt * _opt(z, p + "g_bt")).sum() if tw is not None else 0.0)).backward()
+        assert rel(ls.detach().numpy(), z[p + "log_scales"]) < 1e-12, n
+        assert rel(bt.detach().numpy(), z[p + "betas_trans"]) < 1e-12, n
+        assert rel(sw.grad.numpy(), z[p + "grad_scale_w"]) < 1e-12, n
+        if tw is not None:
+            assert rel(tw.grad.numpy(), z[p + "grad_trans_w"]) < 1e-12, n
+
+
+def test_loss_chain_oracle_matches_frozen_reference_values():
+    """Projection oracle -> the reference's multi-view loss code, on the scenes the GPU tests use."""
+    z = np.load(os.path.join(rigs.GOLDEN, "loss_chain_pins.npz"))
+    for name, (B, V, J, seed, shared) in rigs.LOSS_SCENES.items():
+        sc = rigs.loss_scene(B, V, J, seed, shared)
+        t = {k: torch.from_numpy(np.ascontiguousarray(v)).double() for k, v in sc.items() if k != "image_size"}
+        leaf = {k: t[k].clone().requires_grad_(True) for k in ("joints", "R", "T", "fov")}
+        pred = PO.multiview_project(leaf["joints"], leaf["R"].expand(B, V, 3, 3), leaf["T"].expand(B, V, 3),
+                                    leaf["fov"].expand(B, V), t["aspect"].expand(B, V), float(sc["image_size"]))
+        loss = PO.multiview_keypoint_loss(pred, t["target"], t["vis"], t["view_mask"], t["joint_weights"])
+        loss.backward()
+        assert rel(pred.detach().numpy(), z[name + "/pred"]) < 1e-12
+        assert abs(float(loss) - float(z[name + "/loss"])) <= 1e-12 * abs(float(z[name + "/loss"]))
+        for k, v in leaf.items():
+            assert rel(v.grad.numpy(), z[name + "/grad_" + k]) < 1e-11, (name, k)
