@@ -54,6 +54,7 @@ def algorithmic_bytes(V, J, nB):
     }
     assert sum(per_kernel.values()) == fwd + bwd
     per_kernel["pose_bwd_lean_kernel"] = per_kernel["pose_bwd_kernel"]   # the no-log-scale variant moves the same tensors
+    per_kernel["skin_bwd_vm_kernel"] = per_kernel["skin_bwd_kernel"]     # vertex-major variant: the same contract tensor
     return fwd, bwd, per_kernel
 
 
@@ -73,7 +74,7 @@ def traffic_for(kernel, args):
     if args.traffic is not None:
         return args.traffic
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        t = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))
         if t.get("rig") == args.rig and t.get("batch") == args.batch:
             return t["kernels"].get(kernel)
     except Exception:
@@ -137,6 +138,56 @@ class ClockSampler:
         except OSError:
             pass
         return out
+
+
+def pin_rank_to_cores(local_rank, world):
+    """Disjoint CPU cores per rank (the 8 ranks of a box otherwise share one affinity mask and their copy / launch
+    threads migrate over each other); pinned host buffers are first-touched AFTER this, so they land on the local node."""
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        per = max(1, len(cores) // max(world, 1))
+        mine = cores[local_rank * per:(local_rank + 1) * per] or cores
+        os.sched_setaffinity(0, mine)
+        return len(mine)
+    except (AttributeError, OSError):
+        return None
+
+
+def torch_gpu_baseline(rig_path, B, dev, seed=0, warmup=3, iters=10):
+    """The reference's op-by-op torch graph (oracle/smal_oracle.py, pinned against the unmodified reference) with every
+    tensor on the SAME B200 at the full batch: the comparator SURVEY.md section 8(d) config 2 / BASELINE configs[1] ask
+    for ("vs reference torch path").  Eager, CUDA events."""
+    import torch
+
+    from oracle import smal_oracle as SO
+
+    dd = SO.load_model_dict(rig_path)
+    m = SO.build_model(dd, dtype=torch.float32)
+    for k, v in list(vars(m).items()):
+        if isinstance(v, torch.Tensor):
+            setattr(m, k, v.to(dev))
+    V, J, nB = m.num_verts, m.num_joints, m.num_betas
+    x = synth_inputs(B, V, J, nB, seed)
+    beta, theta, trans = (torch.from_numpy(x[k]).to(dev).requires_grad_(True) for k in ("beta", "theta", "trans"))
+    gv, gj = torch.from_numpy(x["g_verts"]).to(dev), torch.from_numpy(x["g_joints"]).to(dev)
+
+    def step():
+        verts, joints, _Rs, _vs = SO.smal_forward(m, beta, theta, trans)
+        torch.autograd.backward([verts, joints], [gv, gj])
+        beta.grad = theta.grad = trans.grad = None
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    return {"value": B / ms * 1e3, "unit": UNIT, "ms_per_step": ms, "kind": "port-on-cuda", "batch": B,
+            "what": "oracle/smal_oracle.py (the reference's dense op-by-op torch graph) on cuda, eager, %d timed steps" % iters}
 
 
 # ---- CPU arm: the reference's algorithm on the host cores (oracle/ restatement) -----------------------
@@ -230,6 +281,7 @@ def run_ours(args, rank, world, local_rank):
         raise RuntimeError("bench.py --impl ours needs a CUDA device (there is no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    cores_pinned = pin_rank_to_cores(local_rank, world) if world > 1 else None
     smilify_b200.configure(rigs.REAL_RIGS[args.rig])
     model = SMAL(dev)
     V, J, nB = model._tables["V"], model._tables["J"], model.num_betas
@@ -275,6 +327,12 @@ def run_ours(args, rank, world, local_rank):
             return (gs.grad_beta, gs.grad_theta, gs.grad_trans, gs.joints)
         dst_in = (gs.beta, gs.theta, gs.trans)
 
+    c0 = _lib.launch_count()
+    with torch.enable_grad():
+        _b, _t, _tr = (torch.from_numpy(x[k][:8]).to(dev).requires_grad_(True) for k in ("beta", "theta", "trans"))
+        _v, _j, _r, _s = model(_b, _t, trans=_tr)
+        torch.autograd.grad([_v, _j], [_b, _t, _tr], [torch.zeros_like(_v), torch.zeros_like(_j)])
+    launches_per_step = int(_lib.launch_count() - c0)   # kernels of this library per fused step (a replay launches the same)
     sampler = ClockSampler(local_rank) if rank == 0 else None
     # pre-warm so that clock samples are taken under load even when K is small
     t_end = time.perf_counter() + 0.6
@@ -322,19 +380,23 @@ def run_ours(args, rank, world, local_rank):
         for sl in pipe.slots:
             with torch.no_grad():
                 sl["step"].g_verts.copy_(gs.g_verts); sl["step"].g_joints.copy_(gs.g_joints)
+        packed, (hb, ht, htr) = pipe.new_input()     # pinned, first-touched after the rank's cores were pinned
+        hb.copy_(h_in[0]); ht.copy_(h_in[1]); htr.copy_(h_in[2])
         torch.cuda.synchronize()
-        h2d = sum(t.numel() * 4 for t in h_in)
+        h2d = pipe.h2d_bytes
         d2h = pipe.d2h_bytes
         sink = [0.0]
 
         def e2e_run(n):
             for _ in range(n):
-                done = pipe.submit(*h_in)
+                done = pipe.submit_packed(packed)
                 if done is not None:
                     sink[0] += float(done["grad_trans"][0, 0])   # the caller reads the finished step's result
             for done in pipe.drain():
                 sink[0] += float(done["grad_trans"][0, 0])
-        e2e_mode = "HostPipeline depth 2 (copies overlap kernels of neighbouring steps)"
+        e2e_mode = ("HostPipeline depth 2: per step ONE pinned host->device copy (beta | theta | trans) and ONE "
+                    "device->host copy (parameter gradients | posed joints) overlap the kernels of neighbouring steps; "
+                    "posed vertices and upstream gradients stay device-resident (the loss lives on the device)")
 
     e2e_run(3)
     barrier()
@@ -368,14 +430,33 @@ def run_ours(args, rank, world, local_rank):
                              "alg_bytes_per_launch": ab * B if ab else None,
                              "GBps": round(ab * B / (us * 1e-6) / 1e9, 1) if ab else None}
         if prof:
-            top = max(prof, key=lambda k: prof[k][1])
+            top = max((k for k in prof if per_kernel.get(k)), key=lambda k: prof[k][1])
             ab = per_kernel.get(top, 0) * B
             ach = ab / (prof[top][1] / prof[top][0] * 1e-3) / 1e9
             roofline = {"kernel": top, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                         "frac": round(ach / peak, 4), "traffic": traffic_for(top, args), "peak_source": peak_src,
                         "alg_bytes_per_launch": ab, "avg_us": kernels[top]["avg_us"]}
+    fitter = None
+    if world > 1 and not args.no_fitter:
+        # the one collective of the path (north_star): BASELINE configs[3], frames strong-scaled over the ranks, shared
+        # betas / fov, ONE packed NCCL all-reduce per step captured inside the step's CUDA graph
+        import importlib.util
+
+        spec = importlib.util.spec_from_file_location("fitter_multigpu", os.path.join(ROOT, "tools_gpu", "fitter_multigpu.py"))
+        fm = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(fm)
+        del gs
+        torch.cuda.empty_cache()
+        fitter = fm.run_fitter(args.fitter_frames, max(5, min(K, 20)), 3, rank, world, dev, rig="stick13")
+        smilify_b200.configure(rigs.REAL_RIGS[args.rig])
     if rank != 0:
         return
+    torch_gpu = None
+    if world == 1 and not args.no_torch_gpu:
+        try:
+            torch_gpu = torch_gpu_baseline(rigs.REAL_RIGS[args.rig], B, dev)
+        except Exception as e:   # e.g. out of memory on a smaller part: the dense graph materialises (B, V, J) tensors
+            torch_gpu = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:120])}
     peak, peak_src = measured_peaks()
     ms_step = ms_total / K
     value = world * B * K / (ms_total * 1e-3)
@@ -393,17 +474,24 @@ def run_ours(args, rank, world, local_rank):
         "e2e": {"value": world * B * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / K, "mode": e2e_mode,
                 "timing": "host wall clock around K steps incl. the final drain (max over ranks)"},
-        "gpu_launches": int(eager_launches) if args.no_graph else 4 * K,
+        "gpu_launches": int(eager_launches) if args.no_graph else launches_per_step * K,
         "clocks": clocks,
         "roofline": roofline,
         "roofline_step": {"bound": "hbm", "alg_bytes_per_mesh": fwd_b + bwd_b, "achieved": round(step_gbs, 1),
                           "peak": peak, "unit": "GB/s", "frac": round(step_gbs / peak, 4), "peak_source": peak_src},
         "kernels": kernels,
     }
+    if torch_gpu is not None:
+        line["torch_gpu_baseline"] = torch_gpu
+    if fitter is not None:
+        line["fitter"] = fitter
+    if cores_pinned:
+        line["config"]["host_cores_per_rank"] = cores_pinned
     if cpu_val is not None:
         line["cpu_baseline"] = {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port",
-                                "sample": "%d-mesh batches of the same workload, %d timed fwd+bwd (median), torch-CPU "
-                                          "oracle, %d threads" % (args.cpu_batch, n_it, cores)}
+                                "sample": "%d-mesh batches (%s) of the same workload, %d timed fwd+bwd (median), torch-CPU "
+                                          "oracle, %d threads" % (args.cpu_batch, "the full step" if args.cpu_batch >= B
+                                                                  else "a bounded sample", n_it, cores)}
     print(json.dumps(line), flush=True)
 
 
@@ -416,7 +504,10 @@ def main():
     ap.add_argument("--rig", default="stick", choices=["stick", "mouse"])
     ap.add_argument("--batch", type=int, default=4096, help="meshes per GPU per step")
     ap.add_argument("--no-graph", action="store_true", help="time the eager Python call instead of the graph replay")
-    ap.add_argument("--cpu-batch", type=int, default=256, help="meshes per CPU step (bounded sample)")
+    ap.add_argument("--cpu-batch", type=int, default=4096, help="meshes per CPU step (4096 = the full batch of a step)")
+    ap.add_argument("--no-torch-gpu", action="store_true", help="skip the torch-on-the-same-GPU comparator")
+    ap.add_argument("--no-fitter", action="store_true", help="N > 1: skip the frame-sharded fitter step (the NCCL path)")
+    ap.add_argument("--fitter-frames", type=int, default=65536)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--traffic", type=float, default=None, help="dram bytes/launch of the dominant kernel from ncu")
     args = ap.parse_args()

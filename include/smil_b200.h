@@ -24,6 +24,9 @@
  *                                  _compute_batched_keypoint_loss    smal_fitter/neuralSMIL/multiview_smil_regressor.py:2319-2388
  *                                  _compute_batch_keypoint_loss      smal_fitter/neuralSMIL/smil_image_regressor.py:3032-3115
  *   smil_keypoint3d_loss_*      <- _compute_batch_keypoint_3d_loss   smal_fitter/neuralSMIL/smil_image_regressor.py:3334-3407
+ *   smil_triangulate_dlt_*      <- _triangulate_joints_dlt           smal_fitter/neuralSMIL/multiview_smil_regressor.py:1707-1838
+ *   smil_rot6d_to_rotmat_*      <- _rotation_6d_to_matrix            smal_fitter/neuralSMIL/multiview_smil_regressor.py:250-272
+ *                                  rotation_6d_to_axis_angle (1st half) smal_fitter/neuralSMIL/smil_image_regressor.py:87-96
  */
 #ifndef SMIL_B200_H
 #define SMIL_B200_H
@@ -35,7 +38,7 @@
 extern "C" {
 #endif
 
-#define SMIL_ABI_VERSION 4
+#define SMIL_ABI_VERSION 6
 
 enum {
   SMIL_OK = 0,
@@ -46,6 +49,24 @@ enum {
 };
 
 typedef struct SmilModel SmilModel; /* opaque; device-resident packed constants */
+
+/* Per-model tuning switches (all 0 = the library's defaults, so a zero-initialised desc needs no attention).  They
+ * select between measured kernel variants and never change results beyond fp32 rounding order. */
+typedef struct SmilTuning {
+  int32_t fwd_gp;       /* sample pairs per TMA group of the fused forward skin pass (0 = 2) */
+  int32_t fwd_topsync;  /* CTA barrier at the top of every forward group: 0 = by group size, 1 = always, 2 = never */
+  int32_t fwd_cps;      /* resident CTAs per SM the forward grid is sized for (0 = 3) */
+  int32_t bwd_stages;   /* g_verts row buffers of the backward skin pass: 0/1 = single, 2 = double */
+  int32_t bwd_cps;      /* resident CTAs per SM the backward grid is sized for (0 = occupancy limit) */
+  int32_t bwd_vm;       /* vertex-major backward skin pass for K <= 2 rigs: 0 = on, 2 = off (item-major) */
+  int32_t pose_v2;      /* several-samples-per-warp pose kernels (measured slower at B = 4096): 0 = off, 1 = on */
+  int32_t pose_lean;    /* log-scale-free backward pose kernel where it applies: 0 = on, 2 = off */
+  int32_t bwd_atomic;      /* vertex-major pass adds its partials to a dense dL/dA with vector reductions instead of
+                              writing per-(tile, bone) slots: 0 = on, 2 = off (deterministic slots + summing pass) */
+  int32_t bwd_slot_reduce; /* sum the partial slots in a streaming pass before the pose backward: 0 = on, 2 = off */
+  int32_t bwd_stagger_ns; /* start delay per resident-CTA slot of the backward skin pass (de-phases the CTAs of an SM so that
+                             one's TMA wait hides under the others' arithmetic): 0 = default, -1 = none */
+} SmilTuning;
 
 /* Host-side description of a rig: the packed tables `smilify_b200/packer.py` derives from
  * exactly the arrays SMAL.__init__ holds (smal_torch.py:120-196).  All pointers are HOST
@@ -116,6 +137,20 @@ typedef struct SmilModelDesc {
   const int32_t* tjv_v;      /* ... as indices local to the tile */
   const int32_t* sb_ptr;     /* [J+1] bone k owns the g_A partial slots sb_ptr[k] .. sb_ptr[k+1] */
   const int32_t* unit_slot;  /* [num_units] slot a unit's partial is written to (bone-major numbering) */
+  /* fused backward pass, vertex-major (rigs with <= 2 weights per vertex; packer.py::pack_backward_vm): a tile's
+   * vertices in the order a warp with two register-resident bones walks them, cut into bwd_warps shares */
+  int32_t vm_ok, vm_chunk, vm_ntile, vm_recf;   /* vm_recf = floats per vertex record */
+  int32_t vm_nslots, vm_nseg, vm_max_tile_recs, vm_max_tile_segs;
+  int32_t vm_warps;               /* warps per CTA of the vertex-major pass that share one tile (1, 2 or 4) */
+  int32_t vm_nphase;              /* sub-ranges of a tile with their own g_verts row buffer (1..4); vm_chunk % (4 vm_nphase) == 0 */
+  const float* vm_rec;            /* [sum of tile records][vm_recf]: wX wY 3*local-vertex(int bits) T[3] S[nB][3] pad */
+  const int32_t* vm_seg;          /* [vm_nseg][8]: load X bone|-1, load Y bone|-1, first record (tile-local), records,
+                                     flush X slot|-1, flush Y slot|-1, mode (0 both slots, 1 X only), the warp's next segment (tile-local)|-1 */
+  const int32_t* vm_tile_rec_ptr; /* [vm_ntile+1] */
+  const int32_t* vm_warp_seg_ptr; /* [vm_ntile*vm_nphase*vm_warps+1], index (tile * vm_nphase + phase) * vm_warps + warp */
+  const int32_t* vm_sb_ptr;       /* [J+1] bone k owns the vertex-major partial slots vm_sb_ptr[k] .. vm_sb_ptr[k+1] */
+  const int32_t* vm_slot_bone;    /* [vm_nslots] bone of every slot (atomic mode adds a flush to its bone's dense entry) */
+  SmilTuning tuning;              /* per-model kernel variant switches; zeros = defaults */
 } SmilModelDesc;
 
 typedef struct SmilModelInfo {
@@ -284,6 +319,37 @@ typedef struct SmilKp3dArgs {
 } SmilKp3dArgs;
 int smil_keypoint3d_loss_forward(const SmilKp3dArgs* args, void* stream);
 int smil_keypoint3d_loss_backward(const SmilKp3dArgs* args, void* stream);
+
+/* ---- DLT triangulation from multi-view 2-D keypoints (multiview_smil_regressor.py:1707-1838) ----------------------
+ * Cameras as in SmilProjArgs (PyTorch3D FoV, row vectors, per frame & view strides, 0 = shared).  Per (frame, joint):
+ * rows u c3 - c0, v c3 - c1 of every view that sees the joint, w = 1 normalisation, damped (1e-6) 3x3 normal equations;
+ * valid where >= 2 views contribute.  Backward: gradients to the cameras (the keypoints are data). */
+typedef struct SmilTriArgs {
+  int32_t batch, num_views, num_joints;
+  float image_size;
+  const float* keypoints;   /* [B][V][J][2] normalised (y,x) */
+  const float* visibility;  /* [B][V][J] non-zero = visible */
+  const float* view_mask;   /* [B][V] or NULL */
+  const float* cam_R;   int64_t R_bstride, R_vstride;
+  const float* cam_T;   int64_t T_bstride, T_vstride;
+  const float* fov_deg; int64_t fov_bstride, fov_vstride;
+  const float* aspect;  int64_t asp_bstride, asp_vstride;   /* or NULL (=1) */
+  float* tri;           /* [B][J][3] world-space joints */
+  float* valid;         /* [B][J] 1.0 where >= 2 views contributed, else 0.0; or NULL */
+  /* backward */
+  const float* g_tri;   /* [B][J][3] */
+  float* g_cam_R;       /* [B][V][9] or NULL */
+  float* g_cam_T;       /* [B][V][3] or NULL */
+  float* g_fov;         /* [B][V]    or NULL */
+} SmilTriArgs;
+int smil_triangulate_dlt_forward(const SmilTriArgs* args, void* stream);
+int smil_triangulate_dlt_backward(const SmilTriArgs* args, void* stream);
+
+/* 6-D rotation representation -> rotation matrix by Gram-Schmidt: d6 [N][6] -> R [N][9] row-major.
+ * columns = 0: b1, b2, b3 are the ROWS (pytorch3d.transforms.rotation_6d_to_matrix, smil_image_regressor.py:87-96);
+ * columns = 1: the COLUMNS (the reference's own _rotation_6d_to_matrix for cameras, multiview_smil_regressor.py:250-272). */
+int smil_rot6d_to_rotmat_forward(const float* d6, float* R, int64_t n, int32_t columns, void* stream);
+int smil_rot6d_to_rotmat_backward(const float* d6, const float* g_R, float* g_d6, int64_t n, int32_t columns, void* stream);
 
 #ifdef __cplusplus
 }

@@ -145,6 +145,12 @@ def pin_smal(ref, report):
         rig_files[name] = p
     for name in ("stick", "mouse"):
         export_fixture(SO.load_model_dict(rig_files[name]), rigs.REAL_RIGS[name])
+    for name in rigs.PADDED_SPECS:   # stand-ins derived from the fixtures just exported
+        p = os.path.join(tmp, name + ".pkl")
+        with open(p, "wb") as fh:
+            pickle.dump({k: (np.asarray(v) if isinstance(v, np.ndarray) else v) for k, v in rigs.get_rig(name).items()},
+                        fh, protocol=2)
+        rig_files[name] = p
 
     worst = {"o32_fwd": 0.0, "o32_grad": 0.0, "o64_fwd": 0.0, "o64_grad": 0.0}
     for case in rigs.CASES:
@@ -568,6 +574,90 @@ def pin_loss_chains(ref, report):
     np.savez_compressed(os.path.join(rigs.GOLDEN, "loss_chain_pins.npz"), **flat)
 
 
+def pin_triangulation(ref, report):
+    """(f)1: everything of ``_triangulate_joints_dlt`` after the PyTorch3D projection matrix, and the reference's own
+    ``_rotation_6d_to_matrix``, executed from the reference source against the oracle; frozen vectors for the tests."""
+    import textwrap
+    from typing import List, Optional, Tuple
+
+    import torch.nn.functional as F
+
+    mv = os.path.join(ref, "smal_fitter", "neuralSMIL", "multiview_smil_regressor.py")
+    src = open(mv).read()
+    fn = None
+    for node in ast.walk(ast.parse(src)):
+        if isinstance(node, ast.FunctionDef) and node.name == "_triangulate_joints_dlt":
+            fn = node
+    assert fn is not None
+    # top-level statements after ``P = P.view(B, V, 4, 4)`` up to (not including) the return
+    start = None
+    for i, st in enumerate(fn.body):
+        seg = ast.get_source_segment(src, st)
+        if isinstance(st, ast.Assign) and seg.replace(" ", "").startswith("P=P.view("):
+            start = i + 1
+    assert start is not None, "reference _triangulate_joints_dlt layout changed"
+    stmts = [textwrap.dedent(ast.get_source_segment(src, st)) for st in fn.body[start:] if not isinstance(st, ast.Return)]
+    body = "\n".join(stmts)
+    ns = {"torch": torch, "F": F}
+    exec(_extract_function(mv, "_rotation_6d_to_matrix"), ns)
+
+    rs = np.random.RandomState(21)
+    worst = {}
+    flat = {}
+    for name, (B, V, J, shared) in {"tri_b3_v4_j11": (3, 4, 11, False), "tri_b2_v18_j40": (2, 18, 40, False),
+                                     "tri_b4_v5_j55": (4, 5, 55, True)}.items():
+        sc = rigs.loss_scene(B, V, J, 31, shared)
+        kp = sc["target"].copy()
+        kp[0, 0, 0] = (0.4, 0.6)
+        vis = sc["vis"].copy()
+        vis[0, :, 1] = 0.0          # a joint nobody sees
+        vis[0, 1:, 2] = 0.0         # a joint only one view sees
+        vmask = sc["view_mask"].copy()
+        for dt in (torch.float64, torch.float32):
+            t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dt)
+            R, T = t(sc["R"]).expand(B, V, 3, 3).contiguous(), t(sc["T"]).expand(B, V, 3).contiguous()
+            fov, asp = t(sc["fov"]).expand(B, V).contiguous(), t(sc["aspect"]).expand(B, V).contiguous()
+            leaves = [x.clone().requires_grad_(True) for x in (R, T, fov)]
+            P = PO.full_projection_matrix(leaves[0].reshape(B * V, 3, 3), leaves[1].reshape(B * V, 3),
+                                          leaves[2].reshape(B * V), asp.reshape(B * V)).view(B, V, 4, 4)
+            loc = {"torch": torch, "P": P, "keypoints_2d": t(kp), "visibility": t(vis), "view_mask": torch.from_numpy(vmask).bool(),
+                   "img_size": 512.0, "device": torch.device("cpu"), "B": B, "V": V, "J": J}
+            exec(body, loc)
+            r_tri, r_valid = loc["triangulated"], loc["valid_mask"]
+            gup = torch.from_numpy(np.random.RandomState(5).standard_normal((B, J, 3))).to(dt) * r_valid[..., None]
+            (r_tri * gup).sum().backward()
+            r_g = [x.grad.double().numpy() for x in leaves]
+            leaves2 = [x.detach().clone().requires_grad_(True) for x in (R, T, fov)]
+            o_tri, o_valid = PO.triangulate_joints_dlt(t(kp), t(vis), leaves2[0], leaves2[1], leaves2[2], asp, 512.0, t(vmask))
+            (o_tri * gup).sum().backward()
+            tag = "f64" if dt == torch.float64 else "f32"
+            assert torch.equal(o_valid, r_valid)
+            m = r_valid.numpy()
+            worst["tri_" + tag] = max(worst.get("tri_" + tag, 0.0), rel(o_tri.detach().numpy()[m], r_tri.detach().numpy()[m]))
+            for nm, a, b in zip(("R", "T", "fov"), leaves2, r_g):
+                worst["tri_grad_%s_%s" % (nm, tag)] = max(worst.get("tri_grad_%s_%s" % (nm, tag), 0.0),
+                                                          rel(a.grad.double().numpy(), b))
+            if dt == torch.float64:
+                flat.update({name + "/kp": kp, name + "/vis": vis, name + "/view_mask": vmask, name + "/R": R.numpy(),
+                             name + "/T": T.numpy(), name + "/fov": fov.numpy(), name + "/aspect": asp.numpy(),
+                             name + "/tri": r_tri.detach().numpy(), name + "/valid": r_valid.numpy(), name + "/g_tri": gup.numpy(),
+                             name + "/grad_R": r_g[0], name + "/grad_T": r_g[1], name + "/grad_fov": r_g[2]})
+    d6 = rs.standard_normal((64, 6))
+    d6[0] = (1, 0, 0, 0, 1, 0)
+    for dt in (torch.float64, torch.float32):
+        x = torch.from_numpy(d6).to(dt)
+        a = ns["_rotation_6d_to_matrix"](None, x)
+        b = PO.rotation_6d_to_matrix(x, columns=True)
+        worst["rot6d_cols_" + ("f64" if dt == torch.float64 else "f32")] = float((a - b).abs().max())
+    flat["rot6d/d6"] = d6
+    flat["rot6d/R_cols"] = ns["_rotation_6d_to_matrix"](None, torch.from_numpy(d6)).numpy()
+    report["triangulation_pins"] = worst
+    print("triangulation / rot6d pins:", json.dumps(worst, sort_keys=True))
+    for k, v in worst.items():
+        assert v < (1e-9 if k.endswith("f64") else 5e-4), (k, v)   # fp32: LU of torch vs itself on reordered sums
+    np.savez_compressed(os.path.join(rigs.GOLDEN, "triangulation_pins.npz"), **flat)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ref", default="/root/reference")
@@ -580,6 +670,7 @@ def main():
     pin_projection(a.ref, report)
     pin_losses(a.ref, report)
     pin_loss_chains(a.ref, report)
+    pin_triangulation(a.ref, report)
     with open(os.path.join(rigs.GOLDEN, "PIN_REPORT.json"), "w") as fh:
         json.dump(report, fh, indent=1, sort_keys=True)
     print("pinned:", json.dumps(report["worst"]))

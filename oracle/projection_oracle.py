@@ -195,3 +195,70 @@ def keypoint3d_loss(joints3d, target3d, visibility, joint_weights=None, sample_m
     if nvalid == 0:
         return torch.tensor(eps)
     return total / nvalid + eps
+
+
+# ---- (f)1: DLT triangulation + 6-D rotations (multiview_smil_regressor.py:1707-1838, 250-272;
+#            smil_image_regressor.py:87-96) -----------------------------------------------------------
+def full_projection_matrix(R, T, fov_deg, aspect, znear=0.001, zfar=1000.0):
+    """PyTorch3D ``FoVPerspectiveCameras.get_full_projection_transform().get_matrix()`` (row-vector convention,
+    ``ndc_homo = world_homo @ P``): the same world->view and FoV matrices as :func:`fov_project_screen`.
+    R (N,3,3), T (N,3), fov_deg (N,), aspect (N,) -> (N,4,4).  Parity at the PyTorch3D boundary: see the module
+    docstring (the restatement is cross-checked against the reference's numpy OpenCV projection)."""
+    dt = R.dtype
+    N = R.shape[0]
+    W2V = torch.zeros(N, 4, 4, dtype=dt)
+    W2V[:, :3, :3] = R
+    W2V[:, 3, :3] = T
+    W2V[:, 3, 3] = 1.0
+    th = torch.tan(fov_deg * (math.pi / 180.0) / 2)
+    max_y = th * znear
+    max_x = max_y * aspect
+    K = torch.zeros(N, 4, 4, dtype=dt)
+    K[:, 0, 0] = 2.0 * znear / (2.0 * max_x)
+    K[:, 1, 1] = 2.0 * znear / (2.0 * max_y)
+    K[:, 3, 2] = 1.0
+    K[:, 2, 2] = zfar / (zfar - znear)
+    K[:, 2, 3] = -(zfar * znear) / (zfar - znear)
+    return W2V @ K.transpose(1, 2)
+
+
+def triangulate_joints_dlt(keypoints_2d, visibility, R, T, fov_deg, aspect, image_size, view_mask=None):
+    """``_triangulate_joints_dlt`` (multiview_smil_regressor.py:1707-1838): per (frame, joint) the 2V x 4 DLT system
+    from the full projection matrices, w = 1 normalisation, damped 3x3 normal equations, valid where >= 2 views see the
+    joint.  keypoints_2d (B,V,J,2) normalised (y,x); visibility (B,V,J); cameras (B,V,...) -> ((B,J,3), (B,J) bool).
+    Everything after the projection matrix is pinned against the reference's own statements (AST-extracted)."""
+    B, V, J, _ = keypoints_2d.shape
+    P = full_projection_matrix(R.reshape(B * V, 3, 3), T.reshape(B * V, 3), fov_deg.reshape(B * V),
+                               aspect.reshape(B * V)).view(B, V, 4, 4)
+    kp_screen = keypoints_2d * float(image_size)
+    kp_screen = kp_screen[..., [1, 0]]
+    ndc_xy = 1.0 - kp_screen / (float(image_size) / 2.0)
+    joint_vis = visibility.bool()
+    if view_mask is not None:
+        joint_vis = joint_vis & view_mask.bool().unsqueeze(-1)
+    c0, c1, c3 = P[:, :, :, 0], P[:, :, :, 1], P[:, :, :, 3]
+    u, v = ndc_xy[..., 0], ndc_xy[..., 1]
+    row1 = u.unsqueeze(-1) * c3.unsqueeze(2) - c0.unsqueeze(2)
+    row2 = v.unsqueeze(-1) * c3.unsqueeze(2) - c1.unsqueeze(2)
+    vis_mask = joint_vis.unsqueeze(-1).float()
+    row1, row2 = row1 * vis_mask, row2 * vis_mask
+    A = torch.stack([row1, row2], dim=3).permute(0, 2, 1, 3, 4).reshape(B, J, V * 2, 4)
+    A_xyz, a_w = A[..., :3], A[..., 3]
+    AtA = torch.einsum("bkni,bknj->bkij", A_xyz, A_xyz) + 1e-6 * torch.eye(3, dtype=A.dtype)
+    Atb = torch.einsum("bkni,bkn->bki", A_xyz, -a_w)
+    tri = torch.linalg.solve(AtA, Atb)
+    return tri, joint_vis.float().sum(dim=1) >= 2.0
+
+
+def rotation_6d_to_matrix(d6, columns=False):
+    """6-D rotation representation (Zhou et al. 2019) -> rotation matrix by Gram-Schmidt.  ``columns=False``: PyTorch3D
+    ``pytorch3d.transforms.rotation_6d_to_matrix`` (b1, b2, b3 are the ROWS; third-party, restated from its published
+    algorithm; used through ``rotation_6d_to_axis_angle``, smil_image_regressor.py:87-96).  ``columns=True``: the
+    reference's own ``_rotation_6d_to_matrix`` for camera rotations (b1, b2, b3 are the COLUMNS,
+    multiview_smil_regressor.py:250-272; pinned against that code)."""
+    a1, a2 = d6[..., :3], d6[..., 3:6]
+    b1 = torch.nn.functional.normalize(a1, dim=-1)
+    b2 = a2 - (b1 * a2).sum(dim=-1, keepdim=True) * b1
+    b2 = torch.nn.functional.normalize(b2, dim=-1)
+    b3 = torch.cross(b1, b2, dim=-1)
+    return torch.stack([b1, b2, b3], dim=-1 if columns else -2)

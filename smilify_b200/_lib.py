@@ -11,10 +11,15 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsmil_b200.so")
-ABI_VERSION = 4
+ABI_VERSION = 6
 
 c_f = C.POINTER(C.c_float)
 c_i = C.POINTER(C.c_int32)
+
+
+class SmilTuning(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("fwd_gp", "fwd_topsync", "fwd_cps", "bwd_stages", "bwd_cps", "bwd_vm", "pose_v2",
+                                          "pose_lean", "bwd_atomic", "bwd_slot_reduce", "bwd_stagger_ns")]
 
 
 class SmilModelDesc(C.Structure):
@@ -37,6 +42,12 @@ class SmilModelDesc(C.Structure):
         ("rec2", c_f), ("unit_bone", c_i), ("unit_ptr", c_i), ("unit_tile", c_i), ("tile_unit_ptr", c_i),
         ("warp_unit_ptr", c_i), ("warp_unit", c_i), ("tjv_ptr", c_i), ("tjv_v", c_i),
         ("sb_ptr", c_i), ("unit_slot", c_i),
+        ("vm_ok", C.c_int32), ("vm_chunk", C.c_int32), ("vm_ntile", C.c_int32), ("vm_recf", C.c_int32),
+        ("vm_nslots", C.c_int32), ("vm_nseg", C.c_int32), ("vm_max_tile_recs", C.c_int32), ("vm_max_tile_segs", C.c_int32),
+        ("vm_warps", C.c_int32), ("vm_nphase", C.c_int32),
+        ("vm_rec", c_f), ("vm_seg", c_i), ("vm_tile_rec_ptr", c_i), ("vm_warp_seg_ptr", c_i), ("vm_sb_ptr", c_i),
+        ("vm_slot_bone", c_i),
+        ("tuning", SmilTuning),
     ]
 
 
@@ -114,6 +125,19 @@ class SmilKp3dArgs(C.Structure):
     ]
 
 
+class SmilTriArgs(C.Structure):
+    _fields_ = [
+        ("batch", C.c_int32), ("num_views", C.c_int32), ("num_joints", C.c_int32), ("image_size", C.c_float),
+        ("keypoints", C.c_void_p), ("visibility", C.c_void_p), ("view_mask", C.c_void_p),
+        ("cam_R", C.c_void_p), ("R_bstride", C.c_int64), ("R_vstride", C.c_int64),
+        ("cam_T", C.c_void_p), ("T_bstride", C.c_int64), ("T_vstride", C.c_int64),
+        ("fov_deg", C.c_void_p), ("fov_bstride", C.c_int64), ("fov_vstride", C.c_int64),
+        ("aspect", C.c_void_p), ("asp_bstride", C.c_int64), ("asp_vstride", C.c_int64),
+        ("tri", C.c_void_p), ("valid", C.c_void_p),
+        ("g_tri", C.c_void_p), ("g_cam_R", C.c_void_p), ("g_cam_T", C.c_void_p), ("g_fov", C.c_void_p),
+    ]
+
+
 F_THETA_IS_ROTMAT = 1 << 0
 F_STATIC_JOINTS = 1 << 1
 F_PROPAGATE_SCALING = 1 << 2
@@ -128,7 +152,8 @@ EXPORTS = (
     "smil_saved_bytes", "smil_fwd_scratch_bytes", "smil_bwd_scratch_bytes", "smil_forward", "smil_backward",
     "smil_rodrigues_forward", "smil_rodrigues_backward", "smil_chain_forward", "smil_chain_backward",
     "smil_project_loss_forward", "smil_project_loss_backward", "smil_keypoint3d_loss_forward",
-    "smil_keypoint3d_loss_backward",
+    "smil_keypoint3d_loss_backward", "smil_triangulate_dlt_forward", "smil_triangulate_dlt_backward",
+    "smil_rot6d_to_rotmat_forward", "smil_rot6d_to_rotmat_backward",
 )
 
 _lib = None
@@ -169,6 +194,10 @@ def lib():
     L.smil_project_loss_backward.argtypes = [C.POINTER(SmilProjArgs), C.c_void_p]
     L.smil_keypoint3d_loss_forward.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
     L.smil_keypoint3d_loss_backward.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
+    L.smil_triangulate_dlt_forward.argtypes = [C.POINTER(SmilTriArgs), C.c_void_p]
+    L.smil_triangulate_dlt_backward.argtypes = [C.POINTER(SmilTriArgs), C.c_void_p]
+    L.smil_rot6d_to_rotmat_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]
+    L.smil_rot6d_to_rotmat_backward.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]
     for name in EXPORTS:
         getattr(L, name)  # AttributeError here = the .so is older than include/smil_b200.h
     if L.smil_abi_version() != ABI_VERSION:
@@ -206,15 +235,36 @@ def _np_ptr(a: np.ndarray, ctype):
 
 
 _DESC_F32 = ("v_template", "shapedirs", "posedirs", "J_static", "skin_w", "jc_val", "jr_val", "JT", "JS", "jreg_rowsum",
-             "pj_c0", "pj_cm", "pbrec", "vconst", "ell_w", "rec2")
+             "pj_c0", "pj_cm", "pbrec", "vconst", "ell_w", "rec2", "vm_rec")
 _DESC_I32 = ("skin_idx", "jc_ptr", "jc_vid", "jr_ptr", "jr_jid", "parents", "order", "level_ptr", "child_ptr",
              "child_idx", "pj_ptr", "pj_bone", "pj_joint", "pb_ptr", "pb_pair", "ell_idx", "fwd_pos", "unit_bone", "unit_ptr",
-             "unit_tile", "tile_unit_ptr", "warp_unit_ptr", "warp_unit", "tjv_ptr", "tjv_v", "sb_ptr", "unit_slot")
+             "unit_tile", "tile_unit_ptr", "warp_unit_ptr", "warp_unit", "tjv_ptr", "tjv_v", "sb_ptr", "unit_slot",
+             "vm_seg", "vm_tile_rec_ptr", "vm_warp_seg_ptr", "vm_sb_ptr", "vm_slot_bone")
+
+
+def tuning_from_env(overrides=None) -> dict:
+    """Per-model tuning switches (SmilTuning): ``SMIL_*`` environment variables read at MODEL CREATION (development
+    sweeps), overridden by ``overrides``.  Integers pass through; for the on/off switches "0" means off."""
+    out = {}
+    for name in ("fwd_gp", "fwd_cps", "bwd_stages", "bwd_cps", "bwd_stagger_ns"):
+        v = os.environ.get("SMIL_" + name.upper())
+        out[name] = int(v) if v else 0
+    v = os.environ.get("SMIL_FWD_TOPSYNC")
+    out["fwd_topsync"] = 0 if v in (None, "") else (1 if int(v) else 2)
+    for name in ("bwd_vm", "pose_lean", "bwd_slot_reduce", "bwd_atomic"):
+        v = os.environ.get("SMIL_" + name.upper())
+        out[name] = 0 if v in (None, "") else (0 if int(v) else 2)
+    v = os.environ.get("SMIL_POSE_V2")
+    out["pose_v2"] = 1 if v not in (None, "") and int(v) else 0
+    out.update(overrides or {})
+    return out
 
 
 def desc_from_tables(t: dict, device: int):
     """Fill a SmilModelDesc from packer tables.  Returns (desc, keepalive list)."""
     d = SmilModelDesc()
+    for k, v in tuning_from_env(t.get("tuning")).items():
+        setattr(d.tuning, k, int(v))
     keep = []
     d.device = device
     d.num_verts, d.num_joints, d.num_betas, d.num_pose_basis = t.get("V", 0), t["J"], t.get("nB", 0), t.get("P", 0)
@@ -228,6 +278,9 @@ def desc_from_tables(t: dict, device: int):
     d.num_units, d.num_item_pairs = t.get("nunits", 0), t.get("npair_items", 0)
     d.bwd_max_tile_pairs = t.get("bwd_max_tile_pairs", 0)
     d.fused_ok = int(t.get("fused_ok", False))
+    d.vm_ok = int(t.get("vm_ok", False))
+    for name in ("vm_chunk", "vm_ntile", "vm_recf", "vm_nslots", "vm_nseg", "vm_max_tile_recs", "vm_max_tile_segs", "vm_nphase", "vm_warps"):
+        setattr(d, name, int(t.get(name, 0)))
     for name in _DESC_F32:
         a = t.get(name)
         a = np.ascontiguousarray(a, dtype=np.float32) if a is not None else None

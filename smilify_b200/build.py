@@ -41,6 +41,8 @@ def build(force=False, verbose=False):
     flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
     if os.environ.get("SMIL_SKIN_BWD_G"):   # tuning: samples per warp pass of the fused backward (8 | 16 | 32)
         flags.append("-DSMIL_SKIN_BWD_G=%d" % int(os.environ["SMIL_SKIN_BWD_G"]))
+    if os.environ.get("SMIL_FAST_BUILD"):    # development: only the nB = 3 / 5 instances of the fused kernels
+        flags.append("-DSMIL_FAST_BUILD")
     cmd = [_nvcc()] + flags + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, SRC]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:

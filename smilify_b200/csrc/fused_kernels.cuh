@@ -76,8 +76,8 @@ struct SkinFwdArgs {
 
 __host__ __device__ inline int skin_fwd_stage_floats(int chunk) { return ((3 * chunk + 4) + 3) & ~3; }
 __host__ __device__ inline int pair_block_floats(int J, int nbt_model) { return PPB * J + 2 * ((nbt_model + 1) & ~1) + 8; }
-__host__ inline size_t skin_fwd_smem_bytes(int GP, int blk, int chunk, bool direct) {
-  return 32 + 2ull * GP * blk * 4 + (direct ? 0 : (size_t)SKIN_FWD_STAGES * 4 * skin_fwd_stage_floats(chunk) * 4);
+__host__ inline size_t skin_fwd_smem_bytes(int GP, int blk, int chunk) {
+  return 32 + 2ull * GP * blk * 4 + (size_t)SKIN_FWD_STAGES * 4 * skin_fwd_stage_floats(chunk) * 4;
 }
 
 template <int K_>
@@ -98,7 +98,7 @@ __device__ __forceinline__ void store_row(float* __restrict__ dst, long long off
   if (lane >= 4 && lane < 4 + tail) dst[off + head + body + (lane - 4)] = stage[phase + head + body + (lane - 4)];
 }
 
-template <int NBT, int K, bool ALIGNED, bool DIRECT>
+template <int NBT, int K, bool ALIGNED>
 __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, SkinFwdArgs a) {
   // ALIGNED: 3V % 4 == 0, i.e. every staged row starts and ends on a 16-byte boundary of the output tensors
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -149,6 +149,11 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
     w2[k] = make_float2(w, w);
     bo[k] = (k < m.K) ? m.ell_idx[(long long)k * m.v_pad + v] * PPB : 0;
   }
+  // warps whose vertices all have a single bone skip the higher skinning slots (the packer groups such vertices)
+  bool upper = false;
+#pragma unroll
+  for (int k = 1; k < K; ++k) upper = upper || (w2[k].x != 0.f);
+  const bool multi = __any_sync(0xffffffffu, upper);
   const int nv = min(C, V - chunk * C);
   const int n = 3 * nv;
   const int pos3 = 3 * m.fwd_pos[v];   // this thread's vertex, local to the chunk (packer: forward_thread_assignment)
@@ -165,7 +170,7 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
     const int buf = it & 1;
     // every thread must be done with the other buffer (group it-1) before it is refilled: on the staged path the
     // barrier of that group's last shipping step, which follows its last read of the buffer, already guarantees it
-    if (DIRECT || a.top_sync) __syncthreads();
+    if (a.top_sync) __syncthreads();
     if (tid == 0 && grp + (int)gridDim.y < ngroups) issue(grp + gridDim.y, buf ^ 1);
     mbar_wait(&bars[buf], (uint32_t)((it >> 1) & 1));
     const int p0 = grp * a.GP;
@@ -201,6 +206,7 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
       float2 o0 = make_float2(t01.x, t01.y), o1 = make_float2(t01.z, t01.w), o2 = t2_;
 #pragma unroll
       for (int k = 0; k < K; ++k) {
+        if (k > 0 && !multi) break;
         const float4* Ak = reinterpret_cast<const float4*>(Ag + bo[k]);
         float4 q;
         float2 t;
@@ -214,20 +220,7 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
         q = Ak[4]; t = __ffma2_rn(make_float2(q.z, q.w), vs1, t); t = __ffma2_rn(make_float2(q.x, q.y), vs0, t);
         o2 = __ffma2_rn(w2[k], t, o2);
       }
-      if (DIRECT) {
-        // straight from registers: 12-byte pieces at a 12-byte stride; a warp covers 384 contiguous bytes per tensor row
-        if (writer) {
-          float* d = a.verts + offw_u + pos3;
-          d[0] = o0.x; d[1] = o1.x; d[2] = o2.x;
-          float* e = a.v_shaped + offw_u + pos3;
-          e[0] = vs0.x; e[1] = vs1.x; e[2] = vs2.x;
-          if (2 * (p0 + g + u) + 1 < a.B) {
-            d += 3LL * V; e += 3LL * V;
-            d[0] = o0.y; d[1] = o1.y; d[2] = o2.y;
-            e[0] = vs0.y; e[1] = vs1.y; e[2] = vs2.y;
-          }
-        }
-      } else if (writer) {
+      if (writer) {
         float* r = st + pos3;
         int ph0 = 0, ph1 = 0;
         if (!ALIGNED) { ph0 = (int)(offw_u & 3); ph1 = (int)((offw_u + 3LL * V) & 3); }
@@ -237,7 +230,7 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
         r[3 * SF + ph1 + 0] = vs0.y; r[3 * SF + ph1 + 1] = vs1.y; r[3 * SF + ph1 + 2] = vs2.y;  // v_shaped, b+1
       }
      }
-      if (!DIRECT) {
+      {
       fence_proxy_async();
       // the stages the NEXT step writes were last read by the stores of step (now)+1-STAGES/PPS
       if (shipper && lane == 0) bulk_wait_read<SKIN_FWD_STAGES / SKIN_FWD_PPS - 2>();
@@ -264,184 +257,7 @@ __global__ void __launch_bounds__(SKIN_FWD_THREADS) skin_fwd_kernel(DevModel m, 
       sidx = (sidx + SKIN_FWD_PPS >= SKIN_FWD_STAGES) ? 0 : sidx + SKIN_FWD_PPS;
     }
   }
-  if (!DIRECT && shipper && lane == 0) bulk_wait_read<0>();
-}
-
-// =====================================================================================================
-// forward, lane = sample
-// =====================================================================================================
-// The thread-per-vertex pass above is bounded by shared-memory wavefronts: every (vertex, sample pair) gathers
-// 24 K floats of bone transforms at per-thread addresses (ncu r01 v2: 72 % of the smem pipe, 2.8 TB/s of
-// DRAM writes).  Here the roles are swapped: a warp owns 32 SAMPLES and walks the vertices of a tile; the
-// bone transforms of the current run live in REGISTERS (loaded coalesced from the sample-minor copy AT the
-// pose pass writes), the per-vertex constants arrive as warp-uniform float4 shared-memory loads (one wavefront
-// each), and the results are transposed through a per-warp staging tile so that every row leaves as
-// contiguous 8-byte-per-lane stores.  Shared-memory wavefronts per (vertex, 32 samples): ~6 constant loads +
-// 12 staging stores + 6 staging reads, against ~46 for the pass above.
-constexpr int F3_WARPS = 4;                      // warps per CTA: same vertex tile, different sample groups
-constexpr int F3_RS = 3 * F3_TILE + 2;           // staging row stride (floats): 8-byte aligned rows, == 2 (mod 16)
-
-struct SkinFwd3Args {
-  int B, nb;
-  const float* beta;  long long beta_stride;
-  const float* trans; long long trans_stride;
-  const float* AT;            // [ceil(B/32)][J][12][32]
-  float* verts;               // [B][V][3]
-  float* v_shaped;            // [B][V][3]
-};
-
-__host__ inline size_t skin_fwd3_smem_bytes(int recf, int max_runs) {
-  return (size_t)F3_TILE * recf * 4 + (size_t)((max_runs + 3) & ~3) * 16 + (size_t)F3_WARPS * 2 * 32 * F3_RS * 4;
-}
-
-template <int NBT>
-__global__ void __launch_bounds__(32 * F3_WARPS, 4) skin_fwd3_kernel(DevModel m, SkinFwd3Args a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  constexpr int RECF = ((3 + 3 * NBT + 3) + 3) & ~3;
-  constexpr int NQ = RECF / 4;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int tile = blockIdx.x;
-  const int V = m.V, J = m.J;
-  float4* sRec = reinterpret_cast<float4*>(smem_raw);                       // [F3_TILE][NQ]
-  const int run0 = m.f3_tile_run_ptr[tile], nrun = m.f3_tile_run_ptr[tile + 1] - run0;
-  int4* sRun = reinterpret_cast<int4*>(sRec + F3_TILE * NQ);                // [max_runs]
-  float* sStage = reinterpret_cast<float*>(sRun + ((m.f3_max_runs + 3) & ~3)) + (size_t)warp * 2 * 32 * F3_RS;
-  float* stV = sStage;                 // [32 samples][F3_RS] posed vertices of the tile
-  float* stS = sStage + 32 * F3_RS;    // [32 samples][F3_RS] shaped vertices
-  const int v0 = tile * F3_TILE;
-  const int nv = min(F3_TILE, V - v0);
-  {
-    const float4* src = reinterpret_cast<const float4*>(m.f3_rec) + (size_t)tile * F3_TILE * NQ;
-    for (int i = tid; i < nv * NQ; i += 32 * F3_WARPS) sRec[i] = src[i];
-    for (int i = tid; i < nrun; i += 32 * F3_WARPS) sRun[i] = m.f3_runs[run0 + i];
-  }
-  __syncthreads();
-
-  const int ngroups = (a.B + 31) >> 5;
-  // copy-out geometry, fixed for the tile: a step ships `rps` whole rows as float2, lane i (+32, +64) of the
-  // step -> (row inside the step, column)
-  const int rowf2 = (3 * nv) >> 1;               // float2 per row (3 nv is even for every tile but possibly the last)
-  const bool even_rows = ((3 * nv) & 1) == 0 && ((3LL * V) & 1) == 0;
-  const int rps = even_rows ? max(1, min(32, 96 / max(rowf2, 1))) : 1;
-  int so[3], go[3], rr[3];
-#pragma unroll
-  for (int q = 0; q < 3; ++q) {
-    const int i = lane + 32 * q;
-    const int r_ = i / max(rowf2, 1), c2 = i - r_ * rowf2;
-    rr[q] = (r_ < rps) ? r_ : 1 << 20;   // lanes beyond the step's rows never pass the row test
-    so[q] = r_ * F3_RS + 2 * c2;
-    go[q] = r_ * 3 * V + 2 * c2;
-  }
-  const int gstep = gridDim.y * F3_WARPS;
-  int grp = blockIdx.y * F3_WARPS + warp;
-  // per-sample operands of a group are fetched one group ahead (they come from HBM)
-  float beta_n[NBT], tn0 = 0.f, tn1 = 0.f, tn2 = 0.f;
-  auto fetch = [&](int g_) {
-    const int bb = min((g_ << 5) + lane, a.B - 1);
-#pragma unroll
-    for (int k = 0; k < NBT; ++k) beta_n[k] = (k < a.nb) ? a.beta[(long long)bb * a.beta_stride + k] : 0.f;
-    if (a.trans) { const float* tp = a.trans + (long long)bb * a.trans_stride; tn0 = tp[0]; tn1 = tp[1]; tn2 = tp[2]; }
-  };
-  if (grp < ngroups) fetch(grp);
-  for (; grp < ngroups; grp += gstep) {
-    float beta[NBT];
-#pragma unroll
-    for (int k = 0; k < NBT; ++k) beta[k] = beta_n[k];
-    const float t0 = tn0, t1 = tn1, t2 = tn2;
-    if (grp + gstep < ngroups) fetch(grp + gstep);
-    const float* ATg = a.AT + (size_t)grp * 12 * J * 32 + lane;
-    float A0[12], A1[12], An[12];   // An: second bone of the NEXT run (it changes with almost every run)
-    int cur0 = -1;
-    if (nrun > 0 && sRun[0].y >= 0) {
-#pragma unroll
-      for (int e = 0; e < 12; ++e) An[e] = ATg[(size_t)(sRun[0].y + e) * 32];
-    }
-    for (int r = 0; r < nrun; ++r) {
-      const int4 rd = sRun[r];
-      if (rd.x != cur0) {   // runs are sorted by (bone0, bone1): bone0 changes rarely
-#pragma unroll
-        for (int e = 0; e < 12; ++e) A0[e] = ATg[(size_t)(rd.x + e) * 32];
-        cur0 = rd.x;
-      }
-      const bool two = rd.y >= 0;
-      if (two) {
-#pragma unroll
-        for (int e = 0; e < 12; ++e) A1[e] = An[e];
-      }
-      if (r + 1 < nrun) {
-        const int ny = sRun[r + 1].y;
-        if (ny >= 0) {
-#pragma unroll
-          for (int e = 0; e < 12; ++e) An[e] = ATg[(size_t)(ny + e) * 32];
-        }
-      }
-      float4 nx[NQ];   // record of the next slot, loaded one slot ahead (warp-uniform shared loads)
-#pragma unroll
-      for (int q = 0; q < NQ; ++q) nx[q] = sRec[rd.z * NQ + q];
-      for (int s = rd.z; s < rd.z + rd.w; ++s) {
-        float c[RECF];
-#pragma unroll
-        for (int q = 0; q < NQ; ++q) {
-          c[4 * q] = nx[q].x; c[4 * q + 1] = nx[q].y; c[4 * q + 2] = nx[q].z; c[4 * q + 3] = nx[q].w;
-        }
-        if (s + 1 < rd.z + rd.w) {
-#pragma unroll
-          for (int q = 0; q < NQ; ++q) nx[q] = sRec[(s + 1) * NQ + q];
-        }
-        float x = c[0], y = c[1], z = c[2];
-#pragma unroll
-        for (int k = 0; k < NBT; ++k) {
-          x = fmaf(beta[k], c[3 + 3 * k], x); y = fmaf(beta[k], c[4 + 3 * k], y); z = fmaf(beta[k], c[5 + 3 * k], z);
-        }
-        const float w0 = c[3 + 3 * NBT], w1 = c[4 + 3 * NBT];
-        const int lv3 = __float_as_int(c[5 + 3 * NBT]);
-        float p0 = fmaf(A0[0], x, fmaf(A0[1], y, fmaf(A0[2], z, A0[3])));
-        float p1 = fmaf(A0[4], x, fmaf(A0[5], y, fmaf(A0[6], z, A0[7])));
-        float p2 = fmaf(A0[8], x, fmaf(A0[9], y, fmaf(A0[10], z, A0[11])));
-        float o0 = fmaf(w0, p0, t0), o1 = fmaf(w0, p1, t1), o2 = fmaf(w0, p2, t2);
-        if (two) {
-          p0 = fmaf(A1[0], x, fmaf(A1[1], y, fmaf(A1[2], z, A1[3])));
-          p1 = fmaf(A1[4], x, fmaf(A1[5], y, fmaf(A1[6], z, A1[7])));
-          p2 = fmaf(A1[8], x, fmaf(A1[9], y, fmaf(A1[10], z, A1[11])));
-          o0 = fmaf(w1, p0, o0); o1 = fmaf(w1, p1, o1); o2 = fmaf(w1, p2, o2);
-        }
-        float* dv = stV + lane * F3_RS + lv3;
-        float* ds = stS + lane * F3_RS + lv3;
-        dv[0] = o0; dv[1] = o1; dv[2] = o2;
-        ds[0] = x;  ds[1] = y;  ds[2] = z;
-      }
-    }
-    __syncwarp();
-    // ---- copy-out: row r of the staging tile -> verts / v_shaped [grp*32 + r][v0 .. v0+nv) ----------------
-    const int rows = min(32, a.B - (grp << 5));
-    const long long gbase = ((long long)(grp << 5) * V + v0) * 3;
-    if (even_rows) {
-      const float* sv = stV;
-      const float* ss = stS;
-      float* gv = a.verts + gbase;
-      float* gs = a.v_shaped + gbase;
-      for (int rp = 0; rp < rows; rp += rps) {
-        float2 bv[3], bs[3];
-#pragma unroll
-        for (int q = 0; q < 3; ++q)
-          if (rp + rr[q] < rows) { bv[q] = *reinterpret_cast<const float2*>(sv + so[q]); bs[q] = *reinterpret_cast<const float2*>(ss + so[q]); }
-#pragma unroll
-        for (int q = 0; q < 3; ++q)
-          if (rp + rr[q] < rows) { *reinterpret_cast<float2*>(gv + go[q]) = bv[q]; *reinterpret_cast<float2*>(gs + go[q]) = bs[q]; }
-        sv += rps * F3_RS; ss += rps * F3_RS;
-        gv += (long long)rps * 3 * V; gs += (long long)rps * 3 * V;
-      }
-    } else {
-      const int n = 3 * nv;
-      for (int r_ = 0; r_ < rows; ++r_)
-        for (int i = lane; i < n; i += 32) {
-          const long long g_ = gbase + (long long)r_ * 3 * V + i;
-          a.verts[g_] = stV[r_ * F3_RS + i];
-          a.v_shaped[g_] = stS[r_ * F3_RS + i];
-        }
-    }
-    __syncwarp();
-  }
+  if (shipper && lane == 0) bulk_wait_read<0>();
 }
 
 // =====================================================================================================

@@ -43,15 +43,17 @@ struct PoseArgs {
   float* pp;      // [ceil(B/2)][pp_blk] per-pair parameter blocks for the fused skinning passes, or null:
                   //   A2 [J][12][2] | beta2 [NB2][2] | trans2 [4][2], every entry interleaved (sample 2p, sample 2p+1)
   int pp_blk;     // floats per block (fused_kernels.cuh::pair_block_floats)
-  float* AT;      // [ceil(B/32)][J][12][32] the same transforms sample-minor (lane-per-sample forward skin pass), or null
   float* newJ;    // [B][J][3] or null
   float* joints;  // [B][J][3] or null
   // backward inputs
   const float* A_saved;   // [B][J][12] written by the forward (its 3x3 part is the global rotation) or null
   const float* pp_saved;  // the pair blocks the forward wrote (A2 part is read) or null
   const float* gA_dense;  // [B][J][12] or null
-  const float* gA_slots;  // [B][nslots][12] or null; the slots of bone k are sb_ptr[k] .. sb_ptr[k+1]
+  const float* gA_slots;  // per-(tile, bone) partials of the skin pass or null; the slots of bone k are sb_ptr[k] .. sb_ptr[k+1]
   int nslots;
+  const int* sb_ptr;             // [J+1] (device) slot ranges per bone for the table set the skin pass used
+  long long slot_bstride;        // float4 units between consecutive samples of one slot ...
+  long long slot_sstride;        // ... and between consecutive slots of one sample ([B][nslots][12]: 3 nslots, 3; [nslots][B][12]: 3, 3 B)
   const float* gbt_part;  // [B][ntile][nb+3] partial (g_beta, g_trans) from the fused skin pass, or null
   int ntile;
   int joints_in_skin;     // 1: the fused skin pass already folded Jreg g_joints into g_verts
@@ -260,12 +262,6 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_fwd_kernel(DevModel m, Pose
       const int j = i / 6;
       out[i + j * (PPB / 4 - 6)] = make_float4(X0[2 * i], X1[2 * i], X0[2 * i + 1], X1[2 * i + 1]);
     }
-    if (a.AT) {   // the CTA's two samples are neighbours on the sample-minor axis: one 8-byte store per entry
-      const int b0 = blockIdx.x * 2;
-      float* at = a.AT + (size_t)(b0 >> 5) * 12 * J * 32 + (b0 & 31);
-      for (int i = threadIdx.x; i < 12 * J; i += POSE_THREADS)
-        *reinterpret_cast<float2*>(at + (size_t)i * 32) = make_float2(X0[i], X1[i]);
-    }
     const int nb2 = (a.pp_blk - PPB * J - 8) >> 1;
     for (int i = threadIdx.x; i < 2 * nb2; i += POSE_THREADS) {
       const int k = i >> 1, h = i & 1;
@@ -378,21 +374,22 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_bwd_kernel(DevModel m, Pose
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (a.gA_dense) acc = reinterpret_cast<const float4*>(a.gA_dense)[(long long)b * 3 * J + e];
     if (a.gA_slots) {
-      const float4* sl = reinterpret_cast<const float4*>(a.gA_slots) + (long long)b * a.nslots * 3 + r;
-      int si = m.sb_ptr[j];
-      const int se = m.sb_ptr[j + 1];
+      const float4* sl = reinterpret_cast<const float4*>(a.gA_slots) + (long long)b * a.slot_bstride + r;
+      const long long ss = a.slot_sstride;
+      int si = a.sb_ptr[j];
+      const int se = a.sb_ptr[j + 1];
       for (; si + 3 < se; si += 4) {   // four independent loads in flight (the slots live in L2 / HBM)
-        const float4 t0 = sl[si * 3], t1 = sl[si * 3 + 3], t2 = sl[si * 3 + 6], t3 = sl[si * 3 + 9];
+        const float4 t0 = sl[si * ss], t1 = sl[(si + 1) * ss], t2 = sl[(si + 2) * ss], t3 = sl[(si + 3) * ss];
         acc.x += (t0.x + t1.x) + (t2.x + t3.x); acc.y += (t0.y + t1.y) + (t2.y + t3.y);
         acc.z += (t0.z + t1.z) + (t2.z + t3.z); acc.w += (t0.w + t1.w) + (t2.w + t3.w);
       }
       if (si + 1 < se) {
-        const float4 t0 = sl[si * 3], t1 = sl[si * 3 + 3];
+        const float4 t0 = sl[si * ss], t1 = sl[(si + 1) * ss];
         acc.x += t0.x + t1.x; acc.y += t0.y + t1.y; acc.z += t0.z + t1.z; acc.w += t0.w + t1.w;
         si += 2;
       }
       if (si < se) {
-        const float4 t = sl[si * 3];
+        const float4 t = sl[si * ss];
         acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
       }
     }
@@ -684,22 +681,24 @@ __global__ void __launch_bounds__(POSE_THREADS, 14) pose_bwd_lean_kernel(DevMode
   for (int e = l; e < 3 * J; e += 32) {
     const int j = e / 3, r = e - 3 * j;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.gA_dense) acc = reinterpret_cast<const float4*>(a.gA_dense)[(long long)b * 3 * J + e];   // slots already summed
     if (a.gA_slots) {
-      const float4* sl = reinterpret_cast<const float4*>(a.gA_slots) + (long long)b * a.nslots * 3 + r;
-      int si = m.sb_ptr[j];
-      const int se = m.sb_ptr[j + 1];
+      const float4* sl = reinterpret_cast<const float4*>(a.gA_slots) + (long long)b * a.slot_bstride + r;
+      const long long ss = a.slot_sstride;
+      int si = a.sb_ptr[j];
+      const int se = a.sb_ptr[j + 1];
       for (; si + 3 < se; si += 4) {
-        const float4 t0 = sl[si * 3], t1 = sl[si * 3 + 3], t2 = sl[si * 3 + 6], t3 = sl[si * 3 + 9];
+        const float4 t0 = sl[si * ss], t1 = sl[(si + 1) * ss], t2 = sl[(si + 2) * ss], t3 = sl[(si + 3) * ss];
         acc.x += (t0.x + t1.x) + (t2.x + t3.x); acc.y += (t0.y + t1.y) + (t2.y + t3.y);
         acc.z += (t0.z + t1.z) + (t2.z + t3.z); acc.w += (t0.w + t1.w) + (t2.w + t3.w);
       }
       if (si + 1 < se) {
-        const float4 t0 = sl[si * 3], t1 = sl[si * 3 + 3];
+        const float4 t0 = sl[si * ss], t1 = sl[(si + 1) * ss];
         acc.x += t0.x + t1.x; acc.y += t0.y + t1.y; acc.z += t0.z + t1.z; acc.w += t0.w + t1.w;
         si += 2;
       }
       if (si < se) {
-        const float4 t = sl[si * 3];
+        const float4 t = sl[si * ss];
         acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
       }
     }

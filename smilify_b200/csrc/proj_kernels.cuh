@@ -29,7 +29,9 @@ __device__ __forceinline__ Cam load_cam(const SmilProjArgs& a, int b, int v) {
   for (int q = 0; q < 9; ++q) c.R[q] = R[q];
   c.T[0] = T[0]; c.T[1] = T[1]; c.T[2] = T[2];
   const float fov = a.fov_deg[(long long)b * a.fov_bstride + (long long)v * a.fov_vstride];
-  c.f = tanf(fov * 0.00872664625997164788f);  // pi/360
+  // tan in fp64: an error of a few ulp in f scales EVERY ndc of the view the same way and does not average out over
+  // the joints (tanf's 4 ulp showed up as 2e-5 relative on the shared-camera gradients)
+  c.f = (float)tan((double)fov * 0.00872664625997164788);  // pi/360
   const float asp = a.aspect ? a.aspect[(long long)b * a.asp_bstride + (long long)v * a.asp_vstride] : 1.0f;
   c.fa = c.f * asp;
   return c;
@@ -54,37 +56,41 @@ __device__ __forceinline__ Proj project(const Cam& c, const float* X, float half
 // Per-element loss terms shared by forward and backward.
 struct Term {
   float q0, q1;      // value entering the squared error (after normalise / clamp / nan_to_num / -1 fill)
+  float e0, e1;      // residual q - target, evaluated WITHOUT the ~256 px intermediate: q = k - k ndc (k = S/2 for pixels,
+                     // S/2/norm otherwise), so e = (k - t) - k ndc is one fused rounding of a small quantity instead of
+                     // the difference of two fp32 pixel coordinates (3x less error on the gradients, PIN_REPORT.json)
   float d0, d1;      // d q / d p   (0 where clamped, non-finite or masked)
-  float t0, t1;      // target (after the -1 fill for FITTER)
   float w;           // mask * joint weight
   bool valid;        // mask alone (a zero joint weight still counts as a valid joint)
 };
-__device__ __forceinline__ Term loss_term(const SmilProjArgs& a, int b, int v, int j, float p0, float p1) {
+__device__ __forceinline__ Term loss_term(const SmilProjArgs& a, int b, int v, int j, float half, float xn, float yn) {
   Term t;
   const long long e = ((long long)b * a.num_views + v) * a.num_joints + j;
   const float vis = a.visibility ? a.visibility[e] : 1.f;
-  t.t0 = a.target[2 * e]; t.t1 = a.target[2 * e + 1];
+  const float t0 = a.target[2 * e], t1 = a.target[2 * e + 1];
   if (a.kind == SMIL_LOSS_FITTER) {
     const bool on = vis != 0.f;
-    t.q0 = on ? p0 : -1.f; t.q1 = on ? p1 : -1.f;
-    t.t0 = on ? t.t0 : -1.f; t.t1 = on ? t.t1 : -1.f;
+    t.q0 = on ? fmaf(-half, yn, half) : -1.f; t.q1 = on ? fmaf(-half, xn, half) : -1.f;
+    t.e0 = on ? fmaf(-half, yn, half - t0) : 0.f; t.e1 = on ? fmaf(-half, xn, half - t1) : 0.f;   // -1 - (-1) = 0
     t.d0 = on ? 1.f : 0.f; t.d1 = t.d0;
     t.w = 1.f;
     t.valid = true;
     return t;
   }
   const float inv = 1.0f / a.norm_size;
-  float n0 = p0 * inv, n1 = p1 * inv;
+  const float k = half * inv;
+  float n0 = fmaf(-k, yn, k), n1 = fmaf(-k, xn, k);
+  float e0 = fmaf(-k, yn, k - t0), e1 = fmaf(-k, xn, k - t1);
   t.d0 = (n0 >= a.clamp_lo && n0 <= a.clamp_hi) ? inv : 0.f;
   t.d1 = (n1 >= a.clamp_lo && n1 <= a.clamp_hi) ? inv : 0.f;
-  n0 = fminf(fmaxf(n0, a.clamp_lo), a.clamp_hi);  // NaN propagates through clamp like torch.clamp
-  n1 = fminf(fmaxf(n1, a.clamp_lo), a.clamp_hi);
-  if (p0 != p0) n0 = p0;
-  if (p1 != p1) n1 = p1;
-  if (!isfinite(n0)) { n0 = 0.f; t.d0 = 0.f; }  // nan_to_num(nan=0, posinf=0, neginf=0)
-  if (!isfinite(n1)) { n1 = 0.f; t.d1 = 0.f; }
+  if (n0 < a.clamp_lo) { n0 = a.clamp_lo; e0 = n0 - t0; } else if (n0 > a.clamp_hi) { n0 = a.clamp_hi; e0 = n0 - t0; }
+  if (n1 < a.clamp_lo) { n1 = a.clamp_lo; e1 = n1 - t1; } else if (n1 > a.clamp_hi) { n1 = a.clamp_hi; e1 = n1 - t1; }
+  // NaN propagates through torch.clamp; nan_to_num(nan=0, posinf=0, neginf=0) then zeroes it (infinities were clamped)
+  if (!isfinite(n0)) { n0 = 0.f; e0 = -t0; t.d0 = 0.f; }
+  if (!isfinite(n1)) { n1 = 0.f; e1 = -t1; t.d1 = 0.f; }
   t.q0 = n0; t.q1 = n1;
-  bool valid = vis != 0.f && t.t0 >= 0.f && t.t0 <= 1.f && t.t1 >= 0.f && t.t1 <= 1.f;
+  t.e0 = e0; t.e1 = e1;
+  bool valid = vis != 0.f && t0 >= 0.f && t0 <= 1.f && t1 >= 0.f && t1 <= 1.f;
   if (a.view_mask) valid = valid && a.view_mask[(long long)b * a.num_views + v] != 0.f;
   if (a.sample_mask) valid = valid && a.sample_mask[b] != 0.f;
   t.w = valid ? (a.joint_weights ? a.joint_weights[j] : 1.f) : 0.f;
@@ -104,13 +110,12 @@ __global__ void proj_fwd_kernel(SmilProjArgs a) {
   for (int j = lane; j < a.num_joints; j += 32) {
     const float* X = a.joints + (long long)b * a.joints_stride + 3 * j;
     const Proj pr = project(c, X, half);
-    const Term t = loss_term(a, b, v, j, pr.p0, pr.p1);
+    const Term t = loss_term(a, b, v, j, half, pr.xn, pr.yn);
     if (a.proj) {
       const long long e = ((long long)b * a.num_views + v) * a.num_joints + j;
       a.proj[2 * e] = t.q0; a.proj[2 * e + 1] = t.q1;
     }
-    const float e0 = t.q0 - t.t0, e1 = t.q1 - t.t1;
-    num = fmaf(t.w, fmaf(e0, e0, e1 * e1), num);
+    num = fmaf(t.w, fmaf(t.e0, t.e0, t.e1 * t.e1), num);
     ws += t.w;
     cnt += t.valid ? 1.f : 0.f;
   }
@@ -178,8 +183,8 @@ __device__ __forceinline__ void term_grad(const SmilProjArgs& a, const Term& t, 
     const float pw = a.partials[3 * w + 1], pc = a.partials[3 * w + 2];
     s = pc > 0.f ? s / (pw * 2.f + 1e-8f) : 0.f;
   }
-  g0 = s * (t.q0 - t.t0) * t.d0;
-  g1 = s * (t.q1 - t.t1) * t.d1;
+  g0 = s * t.e0 * t.d0;
+  g1 = s * t.e1 * t.d1;
 }
 
 // (g_p0, g_p1) -> gradient on the view-space point and on f = tan(fov/2)
@@ -205,31 +210,31 @@ __global__ void proj_bwd_kernel(SmilProjArgs a) {
   if (a.g_joints) {
     for (int j = threadIdx.x; j < a.num_joints; j += blockDim.x) {
       const float* X = a.joints + (long long)b * a.joints_stride + 3 * j;
-      float gx = 0.f, gy = 0.f, gz = 0.f;
+      double gx = 0.0, gy = 0.0, gz = 0.0;   // fp64 sums: the terms are differences of ~256 px coordinates and cancel
       for (int v = 0; v < a.num_views; ++v) {
         const Cam c = load_cam(a, b, v);
         const Proj pr = project(c, X, half);
-        const Term t = loss_term(a, b, v, j, pr.p0, pr.p1);
+        const Term t = loss_term(a, b, v, j, half, pr.xn, pr.yn);
         float g0, g1, gXv[3], gf;
         term_grad(a, t, gl, scale, (long long)b * a.num_views + v, g0, g1);
         if (g0 == 0.f && g1 == 0.f) continue;
         proj_vjp(c, pr, half, g0, g1, gXv, gf);
-        gx += c.R[0] * gXv[0] + c.R[1] * gXv[1] + c.R[2] * gXv[2];
-        gy += c.R[3] * gXv[0] + c.R[4] * gXv[1] + c.R[5] * gXv[2];
-        gz += c.R[6] * gXv[0] + c.R[7] * gXv[1] + c.R[8] * gXv[2];
+        gx += (double)(c.R[0] * gXv[0] + c.R[1] * gXv[1] + c.R[2] * gXv[2]);
+        gy += (double)(c.R[3] * gXv[0] + c.R[4] * gXv[1] + c.R[5] * gXv[2]);
+        gz += (double)(c.R[6] * gXv[0] + c.R[7] * gXv[1] + c.R[8] * gXv[2]);
       }
       float* o = a.g_joints + ((long long)b * a.num_joints + j) * 3;
-      o[0] = gx; o[1] = gy; o[2] = gz;
+      o[0] = (float)gx; o[1] = (float)gy; o[2] = (float)gz;
     }
   }
   if (a.g_cam_R || a.g_cam_T || a.g_fov) {
     for (int v = threadIdx.x; v < a.num_views; v += blockDim.x) {
       const Cam c = load_cam(a, b, v);
-      float gR[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, gT[3] = {0, 0, 0}, gfs = 0.f;
+      double gR[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, gT[3] = {0, 0, 0}, gfs = 0.0;   // fp64 sums over the joints (see above)
       for (int j = 0; j < a.num_joints; ++j) {
         const float* X = a.joints + (long long)b * a.joints_stride + 3 * j;
         const Proj pr = project(c, X, half);
-        const Term t = loss_term(a, b, v, j, pr.p0, pr.p1);
+        const Term t = loss_term(a, b, v, j, half, pr.xn, pr.yn);
         float g0, g1, gXv[3], gf;
         term_grad(a, t, gl, scale, (long long)b * a.num_views + v, g0, g1);
         if (g0 == 0.f && g1 == 0.f) continue;
@@ -237,18 +242,18 @@ __global__ void proj_bwd_kernel(SmilProjArgs a) {
 #pragma unroll
         for (int r = 0; r < 3; ++r)
 #pragma unroll
-          for (int q = 0; q < 3; ++q) gR[3 * r + q] = fmaf(X[r], gXv[q], gR[3 * r + q]);
-        gT[0] += gXv[0]; gT[1] += gXv[1]; gT[2] += gXv[2];
-        gfs += gf;
+          for (int q = 0; q < 3; ++q) gR[3 * r + q] += (double)X[r] * (double)gXv[q];
+        gT[0] += (double)gXv[0]; gT[1] += (double)gXv[1]; gT[2] += (double)gXv[2];
+        gfs += (double)gf;
       }
       const long long w = (long long)b * a.num_views + v;
       if (a.g_cam_R) {
 #pragma unroll
-        for (int q = 0; q < 9; ++q) a.g_cam_R[9 * w + q] = gR[q];
+        for (int q = 0; q < 9; ++q) a.g_cam_R[9 * w + q] = (float)gR[q];
       }
-      if (a.g_cam_T) { a.g_cam_T[3 * w] = gT[0]; a.g_cam_T[3 * w + 1] = gT[1]; a.g_cam_T[3 * w + 2] = gT[2]; }
+      if (a.g_cam_T) { a.g_cam_T[3 * w] = (float)gT[0]; a.g_cam_T[3 * w + 1] = (float)gT[1]; a.g_cam_T[3 * w + 2] = (float)gT[2]; }
       // f = tan(fov * pi/360): df/dfov = pi/360 * (1 + f^2); the aspect factor cancels in d/df of x_ndc
-      if (a.g_fov) a.g_fov[w] = gfs * 0.00872664625997164788f * (1.f + c.f * c.f);
+      if (a.g_fov) a.g_fov[w] = (float)(gfs * 0.00872664625997164788 * (1.0 + (double)c.f * (double)c.f));
     }
   }
 }

@@ -11,7 +11,10 @@
 #include "fused_kernels.cuh"
 #include "generic_kernels.cuh"
 #include "pose_kernels.cuh"
+#include "pose_kernels2.cuh"
 #include "proj_kernels.cuh"
+#include "skin_bwd_vm.cuh"
+#include "tri_kernels.cuh"
 #include "smil_common.cuh"
 
 using namespace smil;
@@ -26,16 +29,6 @@ namespace {
 struct ProfSlot { const char* name; cudaEvent_t beg, end; };
 std::atomic<long long> g_launches{0};
 std::atomic<int> g_prof_on{0};
-int g_fwd_topsync = -1;  // SMIL_FWD_TOPSYNC: extra CTA barrier at the top of every forward group (-1 = by group size)
-int g_fwd_gp = 0;   // tuning override (SMIL_FWD_GP): sample pairs per TMA group of the fused forward pass
-int g_fwd_direct = 0;  // tuning override (SMIL_FWD_DIRECT): register -> global stores instead of the TMA staging ring
-int g_bwd_stages = 1;  // SMIL_BWD_STAGES: 1 = single-buffered g_verts rows (more CTAs per SM), 2 = double-buffered
-int g_bwd_cps = 0;     // SMIL_BWD_CPS
-int g_pose_lean = 1;  // SMIL_POSE_LEAN=0: always use the general backward pose kernel.
-int g_fwd_v3 = 0;      // SMIL_FWD_V3=1: lane-per-sample forward skin pass (K <= 2 rigs) instead of the thread-per-vertex pass.
-                       // Measured on B200 (STICK, B=4096): 98 us vs 85 us, plus 9 us in the pose pass for the sample-minor
-                       // copy of the transforms, so it is off by default; kept as the evaluated alternative.
-int g_fwd_cps = 0;  // tuning override (SMIL_FWD_CPS): resident CTAs per SM the forward grid is sized for
 std::mutex g_prof_mu;
 std::vector<ProfSlot> g_prof_slots;   // event pairs, created by smil_profile_enable
 size_t g_prof_used = 0;
@@ -87,6 +80,18 @@ inline int nbt_of(int nb) {
   return 0;
 }
 
+// beta-count template instances of the fused kernels (packer.NBT_VALUES).  -DSMIL_FAST_BUILD compiles only the two
+// the shipped rigs use (nB = 3, 5): a development switch, never the shipped library.
+#ifdef SMIL_FAST_BUILD
+#define SMIL_NBT_CASES(fn) case 3: return fn<3>(m, a, st); case 5: return fn<5>(m, a, st);
+#else
+#define SMIL_NBT_CASES(fn)                                                                                      \
+  case 1: return fn<1>(m, a, st); case 2: return fn<2>(m, a, st); case 3: return fn<3>(m, a, st);               \
+  case 4: return fn<4>(m, a, st); case 5: return fn<5>(m, a, st); case 6: return fn<6>(m, a, st);               \
+  case 8: return fn<8>(m, a, st); case 10: return fn<10>(m, a, st); case 13: return fn<13>(m, a, st);           \
+  case 16: return fn<16>(m, a, st);
+#endif
+
 template <typename Kern>
 int set_smem(Kern k, size_t bytes) {
   if (bytes > 227 * 1024) return fail(SMIL_EUNSUPPORTED, "kernel needs %zu bytes of shared memory (> 227 KB)", bytes);
@@ -104,9 +109,25 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
   const size_t smem = (size_t)((fl + 3) & ~3) * sizeof(float) * POSE_WPB;
   const int grid = (a.B + POSE_WPB - 1) / POSE_WPB;
   int rc = SMIL_OK;
-  const bool lean = backward && g_pose_lean && a.beta_final && a.pp_saved && !a.ls && !a.g_newJ && !a.gA_dense &&
+  const bool lean = backward && m.tune.pose_lean != 2 && a.beta_final && a.pp_saved && !a.ls && !a.g_newJ &&
                     !a.g_jrest && !a.g_Rs2 && (a.jrest_mode == 1 || (a.jrest_mode == 2 && a.jrest_in));
-  if (lean) {   // no per-joint scales: half the shared memory, the whole batch resident in one wave
+  if (lean && m.tune.pose_v2 == 1 && a.nb <= 16 && L.nbp + 3 <= 32) {
+    // several samples per warp (pose_kernels2.cuh): 4 when every tree level fits 8 lanes per sample, else 2
+    const int spw = m.max_width <= 8 ? 4 : 2;
+    const int ps = pose2_bwd_floats(m.J, L.nbp, pairs_mode ? m.npairs_pad : 0);
+    const size_t smem2 = (size_t)POSE2_WPB * spw * ps * sizeof(float);
+    const int grid2 = (a.B + POSE2_WPB * spw - 1) / (POSE2_WPB * spw);
+    const bool nb8 = a.nb <= 8;
+    prof_begin("pose_bwd_lean_kernel", st);
+#define SMIL_POSE_BWD2(SPW_, NB_)                                                                   \
+    do {                                                                                             \
+      if ((rc = set_smem(pose_bwd2_kernel<SPW_, NB_>, smem2)) != SMIL_OK) return rc;                  \
+      pose_bwd2_kernel<SPW_, NB_><<<grid2, 32 * POSE2_WPB, smem2, st>>>(m, a, L.nbp, pairs_mode);     \
+    } while (0)
+    if (spw == 4) { if (nb8) SMIL_POSE_BWD2(4, 8); else SMIL_POSE_BWD2(4, 16); }
+    else { if (nb8) SMIL_POSE_BWD2(2, 8); else SMIL_POSE_BWD2(2, 16); }
+#undef SMIL_POSE_BWD2
+  } else if (lean) {   // no per-joint scales: half the shared memory, the whole batch resident in one wave
     PoseSmemLean LL;
     LL.J = m.J;
     LL.nbp = L.nbp;
@@ -118,6 +139,20 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
     if ((rc = set_smem(pose_bwd_kernel, smem)) != SMIL_OK) return rc;
     prof_begin("pose_bwd_kernel", st);
     pose_bwd_kernel<<<grid, POSE_THREADS, smem, st>>>(m, a, L, pairs_mode);
+  } else if (m.tune.pose_v2 == 1) {
+    // several samples per warp: 4 when every tree level fits 8 lanes per sample, else 2
+    const int spw = m.max_width <= 8 ? 4 : 2;
+    const int ps = pose2_fwd_floats(m.J, L.nbp, (a.joints && a.joints_mode == 1) ? m.npairs_pad : 0);
+    const size_t smem2 = (size_t)POSE2_WPB * spw * ps * sizeof(float);
+    const int grid2 = (a.B + POSE2_WPB * spw - 1) / (POSE2_WPB * spw);
+    prof_begin("pose_fwd_kernel", st);
+    if (spw == 4) {
+      if ((rc = set_smem(pose_fwd2_kernel<4>, smem2)) != SMIL_OK) return rc;
+      pose_fwd2_kernel<4><<<grid2, 32 * POSE2_WPB, smem2, st>>>(m, a, L.nbp);
+    } else {
+      if ((rc = set_smem(pose_fwd2_kernel<2>, smem2)) != SMIL_OK) return rc;
+      pose_fwd2_kernel<2><<<grid2, 32 * POSE2_WPB, smem2, st>>>(m, a, L.nbp);
+    }
   } else {
     if ((rc = set_smem(pose_fwd_kernel, smem)) != SMIL_OK) return rc;
     prof_begin("pose_fwd_kernel", st);
@@ -128,33 +163,32 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
 }
 
 // ---- fused skin launchers ----------------------------------------------------------------------
-template <int NBT, int K, bool ALIGNED, bool DIRECT>
+template <int NBT, int K, bool ALIGNED>
 int launch_skin_fwd_inst2(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
-  const size_t smem = skin_fwd_smem_bytes(a.GP, a.blk, SKIN_FWD_THREADS, DIRECT);
-  int rc = set_smem(skin_fwd_kernel<NBT, K, ALIGNED, DIRECT>, smem);
+  const size_t smem = skin_fwd_smem_bytes(a.GP, a.blk, SKIN_FWD_THREADS);
+  int rc = set_smem(skin_fwd_kernel<NBT, K, ALIGNED>, smem);
   if (rc != SMIL_OK) return rc;
   // persistent CTAs: as many per vertex chunk as fit the machine in one wave; each walks its share of the pair groups
   static thread_local size_t occ_smem = 0;
   static thread_local int occ = 0;
   if (occ_smem != smem) {
-    SMIL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, skin_fwd_kernel<NBT, K, ALIGNED, DIRECT>, SKIN_FWD_THREADS, smem));
+    SMIL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, skin_fwd_kernel<NBT, K, ALIGNED>, SKIN_FWD_THREADS, smem));
     occ_smem = smem;
   }
   const int ngroups = ((a.B + 1) / 2 + a.GP - 1) / a.GP;
-  const int cps = std::min(g_fwd_cps > 0 ? g_fwd_cps : 3, std::max(occ, 1));
+  const int cps = std::min(m.tune.fwd_cps > 0 ? m.tune.fwd_cps : 3, std::max(occ, 1));
   const int Y = std::max(1, std::min(ngroups, (m.sm_count * cps) / std::max(m.fwd_nchunk, 1)));
   dim3 grid(m.fwd_nchunk, Y);
   prof_begin("skin_fwd_kernel", st);
-  skin_fwd_kernel<NBT, K, ALIGNED, DIRECT><<<grid, SKIN_FWD_THREADS, smem, st>>>(m, a);
+  skin_fwd_kernel<NBT, K, ALIGNED><<<grid, SKIN_FWD_THREADS, smem, st>>>(m, a);
   SMIL_LAUNCH_CHECK("skin_fwd_kernel");
   return SMIL_OK;
 }
 template <int NBT, int K>
 int launch_skin_fwd_inst(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
   // rows are 16-byte aligned in the output tensors iff 3V % 4 == 0 (chunks are 256 vertices = 3072 bytes)
-  if (g_fwd_direct) return launch_skin_fwd_inst2<NBT, K, false, true>(m, a, st);
-  if ((3 * m.V) % 4 == 0) return launch_skin_fwd_inst2<NBT, K, true, false>(m, a, st);
-  return launch_skin_fwd_inst2<NBT, K, false, false>(m, a, st);
+  if ((3 * m.V) % 4 == 0) return launch_skin_fwd_inst2<NBT, K, true>(m, a, st);
+  return launch_skin_fwd_inst2<NBT, K, false>(m, a, st);
 }
 template <int NBT>
 int launch_skin_fwd_k(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
@@ -164,16 +198,7 @@ int launch_skin_fwd_k(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) 
 }
 int launch_skin_fwd(const DevModel& m, const SkinFwdArgs& a, cudaStream_t st) {
   switch (nbt_of(a.nb)) {
-    case 1: return launch_skin_fwd_k<1>(m, a, st);
-    case 2: return launch_skin_fwd_k<2>(m, a, st);
-    case 3: return launch_skin_fwd_k<3>(m, a, st);
-    case 4: return launch_skin_fwd_k<4>(m, a, st);
-    case 5: return launch_skin_fwd_k<5>(m, a, st);
-    case 6: return launch_skin_fwd_k<6>(m, a, st);
-    case 8: return launch_skin_fwd_k<8>(m, a, st);
-    case 10: return launch_skin_fwd_k<10>(m, a, st);
-    case 13: return launch_skin_fwd_k<13>(m, a, st);
-    case 16: return launch_skin_fwd_k<16>(m, a, st);
+    SMIL_NBT_CASES(launch_skin_fwd_k)
   }
   return fail(SMIL_EUNSUPPORTED, "fused forward: %d betas not covered", a.nb);
 }
@@ -191,7 +216,7 @@ int launch_skin_bwd_inst2(const DevModel& m, const SkinBwdArgs& a, cudaStream_t 
   }
   // persistent CTAs: one wave; every CTA keeps its tile's constants and walks its share of the sample groups
   const int ngroups = (a.B + SKIN_BWD_G - 1) / SKIN_BWD_G;
-  const int cps = g_bwd_cps > 0 ? std::min(g_bwd_cps, std::max(occ, 1)) : std::max(occ, 1);
+  const int cps = m.tune.bwd_cps > 0 ? std::min(m.tune.bwd_cps, std::max(occ, 1)) : std::max(occ, 1);
   const int Y = std::max(1, std::min(ngroups, (m.sm_count * cps) / std::max(m.bwd_ntile, 1)));
   dim3 grid(m.bwd_ntile, Y);
   prof_begin("skin_bwd_kernel", st);
@@ -200,60 +225,41 @@ int launch_skin_bwd_inst2(const DevModel& m, const SkinBwdArgs& a, cudaStream_t 
   return SMIL_OK;
 }
 template <int NBT>
-int launch_skin_fwd3_inst(const DevModel& m, const SkinFwd3Args& a, cudaStream_t st) {
-  const size_t smem = skin_fwd3_smem_bytes(m.f3_recf, m.f3_max_runs);
-  int rc = set_smem(skin_fwd3_kernel<NBT>, smem);
+int launch_skin_bwd_vm_inst(const DevModel& m, const SkinBwdVmArgs& a, cudaStream_t st) {
+  const size_t smem = skin_bwd_vm_smem_bytes(m.vm_chunk, m.vm_nphase, m.vm_warps, m.vm_recf, a.max_tile_recs, a.max_tile_segs, NBT);
+  int rc = set_smem(skin_bwd_vm_kernel<NBT>, smem);
   if (rc != SMIL_OK) return rc;
   static thread_local size_t occ_smem = 0;
   static thread_local int occ = 0;
   if (occ_smem != smem) {
-    SMIL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, skin_fwd3_kernel<NBT>, 32 * F3_WARPS, smem));
+    SMIL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, skin_bwd_vm_kernel<NBT>, 32 * m.vm_warps, smem));
     occ_smem = smem;
   }
-  // persistent CTAs, one wave: a CTA keeps its tile's constants and walks its share of the 32-sample groups
-  const int ngroups = (a.B + 31) / 32;
-  const int ymax = (ngroups + F3_WARPS - 1) / F3_WARPS;
-  const int cps = g_fwd_cps > 0 ? std::min(g_fwd_cps, std::max(occ, 1)) : std::max(occ, 1);
-  const int Y = std::max(1, std::min(ymax, (m.sm_count * cps) / std::max(m.f3_ntile, 1)));
-  dim3 grid(m.f3_ntile, Y);
-  prof_begin("skin_fwd_kernel", st);
-  skin_fwd3_kernel<NBT><<<grid, 32 * F3_WARPS, smem, st>>>(m, a);
-  SMIL_LAUNCH_CHECK("skin_fwd3_kernel");
+  // persistent CTAs: one wave; every CTA keeps its tile's constants and walks its share of the sample groups
+  const int ngroups = (a.B + SKIN_BWD_G - 1) / SKIN_BWD_G;
+  const int cps = m.tune.bwd_cps > 0 ? std::min(m.tune.bwd_cps, std::max(occ, 1)) : std::max(occ, 1);
+  const int Y = std::max(1, std::min(ngroups, (m.sm_count * cps) / std::max(m.vm_ntile, 1)));
+  dim3 grid(m.vm_ntile, Y);
+  prof_begin("skin_bwd_vm_kernel", st);
+  skin_bwd_vm_kernel<NBT><<<grid, 32 * m.vm_warps, smem, st>>>(m, a);
+  SMIL_LAUNCH_CHECK("skin_bwd_vm_kernel");
   return SMIL_OK;
 }
-int launch_skin_fwd3(const DevModel& m, const SkinFwd3Args& a, cudaStream_t st) {
-  switch (nbt_of(a.nb > 0 ? std::max(a.nb, m.nB) : m.nB)) {
-    case 1: return launch_skin_fwd3_inst<1>(m, a, st);
-    case 2: return launch_skin_fwd3_inst<2>(m, a, st);
-    case 3: return launch_skin_fwd3_inst<3>(m, a, st);
-    case 4: return launch_skin_fwd3_inst<4>(m, a, st);
-    case 5: return launch_skin_fwd3_inst<5>(m, a, st);
-    case 6: return launch_skin_fwd3_inst<6>(m, a, st);
-    case 8: return launch_skin_fwd3_inst<8>(m, a, st);
-    case 10: return launch_skin_fwd3_inst<10>(m, a, st);
-    case 13: return launch_skin_fwd3_inst<13>(m, a, st);
-    case 16: return launch_skin_fwd3_inst<16>(m, a, st);
+int launch_skin_bwd_vm(const DevModel& m, const SkinBwdVmArgs& a, cudaStream_t st) {
+  switch (nbt_of(m.nB)) {   // records are laid out for the MODEL's beta count; unused betas enter as zeros
+    SMIL_NBT_CASES(launch_skin_bwd_vm_inst)
   }
-  return fail(SMIL_EUNSUPPORTED, "lane-per-sample forward: %d betas not covered", m.nB);
+  return fail(SMIL_EUNSUPPORTED, "vertex-major fused backward: %d betas not covered", m.nB);
 }
 
 template <int NBT>
 int launch_skin_bwd_inst(const DevModel& m, const SkinBwdArgs& a, cudaStream_t st) {
-  if (g_bwd_stages == 1) return launch_skin_bwd_inst2<NBT, 1>(m, a, st);
+  if (m.tune.bwd_stages != 2) return launch_skin_bwd_inst2<NBT, 1>(m, a, st);
   return launch_skin_bwd_inst2<NBT, 2>(m, a, st);
 }
 int launch_skin_bwd(const DevModel& m, const SkinBwdArgs& a, cudaStream_t st) {
   switch (nbt_of(a.nb)) {
-    case 1: return launch_skin_bwd_inst<1>(m, a, st);
-    case 2: return launch_skin_bwd_inst<2>(m, a, st);
-    case 3: return launch_skin_bwd_inst<3>(m, a, st);
-    case 4: return launch_skin_bwd_inst<4>(m, a, st);
-    case 5: return launch_skin_bwd_inst<5>(m, a, st);
-    case 6: return launch_skin_bwd_inst<6>(m, a, st);
-    case 8: return launch_skin_bwd_inst<8>(m, a, st);
-    case 10: return launch_skin_bwd_inst<10>(m, a, st);
-    case 13: return launch_skin_bwd_inst<13>(m, a, st);
-    case 16: return launch_skin_bwd_inst<16>(m, a, st);
+    SMIL_NBT_CASES(launch_skin_bwd_inst)
   }
   return fail(SMIL_EUNSUPPORTED, "fused backward: %d betas not covered", a.nb);
 }
@@ -291,9 +297,7 @@ size_t saved_A_bytes(const DevModel& m, int B) {
   return align_up((size_t)((B + 1) / 2) * std::max(pair_blk(m), PPB * m.J) * 4, 256);
 }
 size_t saved_jrest_bytes(const DevModel& m, int B) { return align_up((size_t)B * m.J * 3 * 4, 256); }
-// sample-minor copy of the bone transforms for the lane-per-sample forward skin pass: [ceil(B/32)][J][12][32]
-size_t saved_AT_bytes(const DevModel& m, int B) { return m.f3_ok ? (size_t)((B + 31) / 32) * m.J * 12 * 32 * 4 : 0; }
-size_t saved_bytes_for(const DevModel& m, int B) { return saved_A_bytes(m, B) + saved_jrest_bytes(m, B) + saved_AT_bytes(m, B); }
+size_t saved_bytes_for(const DevModel& m, int B) { return saved_A_bytes(m, B) + saved_jrest_bytes(m, B); }
 
 PoseArgs base_pose_args(const DevModel& m, const SmilFwdArgs& f, const Plan& p) {
   PoseArgs a;
@@ -399,14 +403,7 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
                nbt_of(d.nB) > 0 && d.P == 0 && s->bwd_chunk > 0 &&
                s->bwd_rec == skin_bwd_rec_floats(nbt_of(d.nB)) && d.J <= 64 && d.h_max_tile_units <= SKIN_BWD_MAXU;
   d.device = s->device;
-  if (const char* e = getenv("SMIL_FWD_GP")) g_fwd_gp = atoi(e);
-  if (const char* e = getenv("SMIL_FWD_TOPSYNC")) g_fwd_topsync = atoi(e);
-  if (const char* e = getenv("SMIL_FWD_CPS")) g_fwd_cps = atoi(e);
-  if (const char* e = getenv("SMIL_BWD_STAGES")) g_bwd_stages = atoi(e);
-  if (const char* e = getenv("SMIL_BWD_CPS")) g_bwd_cps = atoi(e);
-  if (const char* e = getenv("SMIL_FWD_V3")) g_fwd_v3 = atoi(e);
-  if (const char* e = getenv("SMIL_POSE_LEAN")) g_pose_lean = atoi(e);
-  if (const char* e = getenv("SMIL_FWD_DIRECT")) g_fwd_direct = atoi(e);
+  d.tune = s->tuning;
   SMIL_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, s->device));
 
   const size_t V = d.V, J = d.J, nB = d.nB, K = d.K, np = std::max(d.npairs, 1);
@@ -469,54 +466,6 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
     ap.add(reinterpret_cast<const float4*>(pjrec4.data()), pjrec4.size() / 4, &d.pjrec4);
     ap.add(reinterpret_cast<const float4*>(pbrec4.data()), pbrec4.size() / 4, &d.pbrec4);
   }
-  // ---- tables of the lane-per-sample forward skin pass (K <= 2 rigs) ---------------------------------
-  std::vector<float> f3rec;
-  std::vector<int> f3runs, f3ptr;
-  d.f3_ok = 0;
-  if (V && K <= 2 && nbt_of(d.nB) > 0 && s->v_template && s->skin_idx && s->skin_w && (nB == 0 || s->shapedirs)) {
-    const int NBTm = std::max(nbt_of(d.nB), 1);
-    d.f3_recf = ((3 + 3 * NBTm + 3) + 3) & ~3;
-    d.f3_ntile = (int)((V + F3_TILE - 1) / F3_TILE);
-    f3rec.assign((size_t)d.f3_ntile * F3_TILE * d.f3_recf, 0.f);
-    f3ptr.push_back(0);
-    d.f3_max_runs = 0;
-    for (int t = 0; t < d.f3_ntile; ++t) {
-      const int v0 = t * F3_TILE, v1 = std::min<int>((int)V, v0 + F3_TILE);
-      struct Key { int b0, b1, v; };
-      std::vector<Key> ks;
-      for (int v = v0; v < v1; ++v) {
-        int b0 = s->skin_idx[v * K], b1 = -1;
-        if (K > 1 && s->skin_w[v * K + 1] != 0.f) b1 = s->skin_idx[v * K + 1];
-        ks.push_back({b0, b1, v});
-      }
-      std::sort(ks.begin(), ks.end(), [](const Key& x, const Key& y) {
-        return x.b0 != y.b0 ? x.b0 < y.b0 : (x.b1 != y.b1 ? x.b1 < y.b1 : x.v < y.v);
-      });
-      int nruns = 0;
-      for (size_t i = 0; i < ks.size(); ++i) {
-        const int v = ks[i].v;
-        float* r = f3rec.data() + ((size_t)t * F3_TILE + i) * d.f3_recf;
-        for (int c = 0; c < 3; ++c) r[c] = s->v_template[v * 3 + c];
-        for (size_t k = 0; k < nB; ++k)
-          for (int c = 0; c < 3; ++c) r[3 + 3 * k + c] = s->shapedirs[k * 3 * V + (size_t)v * 3 + c];
-        r[3 + 3 * NBTm] = s->skin_w[v * K];
-        r[4 + 3 * NBTm] = ks[i].b1 >= 0 ? s->skin_w[v * K + 1] : 0.f;
-        const int lv3 = 3 * (v - v0);
-        memcpy(&r[5 + 3 * NBTm], &lv3, 4);
-        if (i == 0 || ks[i].b0 != ks[i - 1].b0 || ks[i].b1 != ks[i - 1].b1) {
-          f3runs.insert(f3runs.end(), {ks[i].b0 * 12, ks[i].b1 >= 0 ? ks[i].b1 * 12 : -1, (int)i, 0});
-          ++nruns;
-        }
-        ++f3runs[f3runs.size() - 1];
-      }
-      d.f3_max_runs = std::max(d.f3_max_runs, nruns);
-      f3ptr.push_back((int)(f3runs.size() / 4));
-    }
-    ap.add(f3rec.data(), f3rec.size(), &d.f3_rec);
-    ap.add(reinterpret_cast<const int4*>(f3runs.data()), f3runs.size() / 4, &d.f3_runs);
-    ap.add(f3ptr.data(), f3ptr.size(), &d.f3_tile_run_ptr);
-    d.f3_ok = 1;
-  }
   ap.add(s->pb_ptr, V ? J + 1 : 0, &d.pb_ptr);
   ap.add(s->pb_pair, V ? np : 0, &d.pb_pair);
   d.pbrec_floats = (6 + 3 * d.nB + 3) / 4 * 4;
@@ -536,6 +485,19 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   ap.add(s->tjv_v, d.num_units ? (size_t)std::max(d.jreg_nnz, 1) : 0, &d.tjv_v);
   ap.add(s->sb_ptr, d.num_units ? J + 1 : 0, &d.sb_ptr);
   ap.add(s->unit_slot, (size_t)d.num_units, &d.unit_slot);
+  d.vm_ok = s->vm_ok && d.fused_ok && d.K <= 2 && s->vm_rec && s->vm_seg && s->vm_tile_rec_ptr && s->vm_warp_seg_ptr &&
+            s->vm_sb_ptr && s->vm_slot_bone && s->vm_ntile > 0 && s->vm_recf == vm_rec_floats(std::max(nbt_of(d.nB), 1)) && (s->vm_warps == 1 || s->vm_warps == 2 || s->vm_warps == 4) &&
+            s->vm_nphase >= 1 && s->vm_nphase <= 4 && s->vm_chunk % (4 * s->vm_nphase) == 0;
+  d.vm_warps = s->vm_warps; d.vm_nphase = s->vm_nphase; d.vm_chunk = s->vm_chunk; d.vm_ntile = s->vm_ntile; d.vm_recf = s->vm_recf; d.vm_nslots = s->vm_nslots;
+  d.h_vm_max_tile_recs = s->vm_max_tile_recs; d.h_vm_max_tile_segs = s->vm_max_tile_segs;
+  if (d.vm_ok) {
+    ap.add(s->vm_rec, (size_t)s->vm_tile_rec_ptr[s->vm_ntile] * d.vm_recf, &d.vm_rec);
+    ap.add(reinterpret_cast<const int4*>(s->vm_seg), (size_t)s->vm_nseg * 2, &d.vm_seg);
+    ap.add(s->vm_tile_rec_ptr, (size_t)d.vm_ntile + 1, &d.vm_tile_rec_ptr);
+    ap.add(s->vm_warp_seg_ptr, (size_t)d.vm_ntile * d.vm_nphase * d.vm_warps + 1, &d.vm_warp_seg_ptr);
+    ap.add(s->vm_sb_ptr, J + 1, &d.vm_sb_ptr);
+    ap.add(s->vm_slot_bone, (size_t)std::max(d.vm_nslots, 1), &d.vm_slot_bone);
+  }
 
   void* arena = nullptr;
   cudaError_t e = cudaMalloc(&arena, std::max<size_t>(ap.total, 256));
@@ -572,7 +534,7 @@ int smil_model_info(const SmilModel* model, SmilModelInfo* info) {
   info->num_verts = d.V; info->num_joints = d.J; info->num_betas = d.nB; info->num_pose_basis = d.P;
   info->skin_k = d.K; info->jreg_nnz = d.jreg_nnz; info->tree_depth = d.num_levels - 1;
   info->max_level_width = d.max_width; info->posedirs_zero = d.P == 0; info->joint_bone_pairs = d.npairs;
-  info->num_chunks = d.fwd_nchunk; info->num_ga_slots = d.num_units;
+  info->num_chunks = d.fwd_nchunk; info->num_ga_slots = (d.vm_ok && d.tune.bwd_vm != 2) ? d.vm_nslots : d.num_units;
   return SMIL_OK;
 }
 
@@ -595,12 +557,19 @@ size_t smil_bwd_scratch_bytes(const SmilModel* model, const SmilBwdArgs* g) {
   if (!model || !g || g->fwd.batch <= 0) return 0;
   const DevModel& m = model->d;
   const size_t B = g->fwd.batch;
+  // the same path test as smil_backward: the fused kernels need only the per-(tile, bone) slots and per-tile partials
+  // (DESIGN.md section 3), the generic ones three vertex-sized buffers -- never reserve both
+  Plan p;
+  const bool plan_ok = make_plan(m, g->fwd, &p) == SMIL_OK;
+  const bool fused = plan_ok && p.fused && !g->g_v_shaped && !g->g_del_v;
+  const size_t fused_b = align_up(B * std::max(std::max(m.num_units, m.vm_nslots), 1) * 48, 256) +
+                         align_up(B * std::max(std::max(m.bwd_ntile, m.vm_ntile), 1) * (m.nB + 3) * 4, 256) +
+                         align_up(B * m.J * 48, 256) + align_up(B * (m.nB + 3) * 4, 256);   // + summed slots / partials
+  if (fused) return fused_b + 256;
   const size_t vb = align_up(B * m.V * 3 * 4, 256);
-  const size_t fused = align_up(B * std::max(m.num_units, 1) * 48, 256) +
-                       align_up(B * std::max(m.bwd_ntile, 1) * (m.nB + 3) * 4, 256);
   const size_t generic = 3 * vb + 2 * align_up(B * m.J * 48, 256) + align_up(B * m.J * 36, 256) +
                          align_up(B * m.J * 12, 256) + align_up(B * 12, 256);
-  return std::max(fused, generic) + 256;
+  return generic + 256;
 }
 
 int smil_forward(const SmilModel* model, const SmilFwdArgs* f, void* stream) {
@@ -631,26 +600,15 @@ int smil_forward(const SmilModel* model, const SmilFwdArgs* f, void* stream) {
   if (p.fused) {
     pa.joints_mode = p.is_static ? 2 : 1;
     if (!p.is_static) pa.jrest_out = jrest;   // the backward reads the rest joints back instead of re-deriving them
-    const bool v3 = m.f3_ok && g_fwd_v3 && !p.joints_only;
-    float* AT = reinterpret_cast<float*>(static_cast<char*>(f->saved) + saved_A_bytes(m, B) + saved_jrest_bytes(m, B));
-    if (v3) pa.AT = AT;
     if ((rc = launch_pose(m, pa, false, st)) != SMIL_OK) return rc;
-    if (v3) {
-      SkinFwd3Args sa;
-      sa.B = B; sa.nb = f->num_betas_used;
-      sa.beta = f->beta; sa.beta_stride = f->beta_stride;
-      sa.trans = f->trans; sa.trans_stride = f->trans_stride;
-      sa.AT = AT; sa.verts = f->verts; sa.v_shaped = f->v_shaped;
-      return launch_skin_fwd3(m, sa, st);
-    }
     if (!p.joints_only) {
       SkinFwdArgs sa;
       sa.B = B; sa.nb = f->num_betas_used;
-      sa.GP = g_fwd_gp > 0 ? std::min(g_fwd_gp, SKIN_FWD_GPMAX) : 2;
+      sa.GP = m.tune.fwd_gp > 0 ? std::min(m.tune.fwd_gp, SKIN_FWD_GPMAX) : 2;
       sa.blk = pair_blk(m);
       // measured on B200 at B = 4096: with the barrier 74.6 vs 76.5 us on STICK (J = 55: 12.5 KB of transforms per TMA
       // group), without it 224 vs 238 us on the mouse rig (J = 31: 7 KB per group) -> keep it for large groups only
-      sa.top_sync = g_fwd_topsync >= 0 ? g_fwd_topsync : ((size_t)sa.GP * sa.blk * sizeof(float) > 10 * 1024 ? 1 : 0);
+      sa.top_sync = m.tune.fwd_topsync ? (m.tune.fwd_topsync == 1) : ((size_t)sa.GP * sa.blk * sizeof(float) > 10 * 1024 ? 1 : 0);
       sa.pp = A; sa.verts = f->verts; sa.v_shaped = f->v_shaped;
       if ((rc = launch_skin_fwd(m, sa, st)) != SMIL_OK) return rc;
     }
@@ -729,8 +687,35 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
 
   if (fused) {
     float* slots = reinterpret_cast<float*>(sc);
-    float* part = reinterpret_cast<float*>(sc + align_up((size_t)B * std::max(m.num_units, 1) * 48, 256));
-    if (g->g_verts) {
+    float* part = reinterpret_cast<float*>(sc + align_up((size_t)B * std::max(std::max(m.num_units, m.vm_nslots), 1) * 48, 256));
+    pa.sb_ptr = m.sb_ptr;
+    if (g->g_verts && m.vm_ok && m.tune.bwd_vm != 2) {
+      if (((uintptr_t)g->g_verts) & 15) return fail(SMIL_EINVAL, "g_verts must be 16-byte aligned");
+      SkinBwdVmArgs sa;
+      sa.B = B; sa.nb = nb;
+      sa.max_tile_recs = m.h_vm_max_tile_recs; sa.max_tile_segs = m.h_vm_max_tile_segs;
+      sa.beta = f->beta; sa.beta_stride = f->beta_stride;
+      sa.pp = A; sa.blk = pair_blk(m); sa.g_verts = g->g_verts;
+      sa.total_floats = (long long)B * m.V * 3;
+      sa.gA_slots = slots; sa.gbt_part = part;
+      sa.gA_dense = nullptr; sa.gbt_sum = nullptr; sa.J = m.J;
+      sa.stagger_ns = m.tune.bwd_stagger_ns < 0 ? 0 : (m.tune.bwd_stagger_ns > 0 ? m.tune.bwd_stagger_ns : 0);
+      char* q = reinterpret_cast<char*>(part) + align_up((size_t)B * std::max(std::max(m.bwd_ntile, m.vm_ntile), 1) * (m.nB + 3) * 4, 256);
+      const size_t dense_b = align_up((size_t)B * m.J * 48, 256);
+      if (m.tune.bwd_atomic != 2) {   // dense dL/dA and (g_beta, g_trans) sums accumulated by reductions: zero them first
+        sa.gA_dense = reinterpret_cast<float*>(q);
+        sa.gbt_sum = reinterpret_cast<float*>(q + dense_b);
+        SMIL_CUDA(cudaMemsetAsync(q, 0, dense_b + (size_t)B * (nb + 3) * 4, st));
+      }
+      if ((rc = launch_skin_bwd_vm(m, sa, st)) != SMIL_OK) return rc;
+      if (sa.gA_dense) {
+        pa.gA_dense = sa.gA_dense; pa.gbt_part = sa.gbt_sum; pa.ntile = 1;
+      } else {
+        pa.gA_slots = slots; pa.nslots = m.vm_nslots; pa.sb_ptr = m.vm_sb_ptr;
+        pa.slot_bstride = 3; pa.slot_sstride = 3LL * B;
+        pa.gbt_part = part; pa.ntile = m.vm_ntile;
+      }
+    } else if (g->g_verts) {
       if (((uintptr_t)g->g_verts) & 15) return fail(SMIL_EINVAL, "g_verts must be 16-byte aligned");
       SkinBwdArgs sa;
       sa.B = B; sa.nb = nb;
@@ -741,7 +726,25 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
       sa.gA_slots = slots; sa.gbt_part = part;
       if ((rc = launch_skin_bwd(m, sa, st)) != SMIL_OK) return rc;
       pa.gA_slots = slots; pa.nslots = m.num_units;
+      pa.slot_bstride = 3LL * m.num_units; pa.slot_sstride = 3;
       pa.gbt_part = part; pa.ntile = m.bwd_ntile;
+    }
+    if (pa.gA_slots && m.tune.bwd_slot_reduce != 2) {
+      // the partial slots and per-tile partials are summed by a streaming pass; the pose backward reads dense sums
+      char* q = reinterpret_cast<char*>(part) + align_up((size_t)B * std::max(std::max(m.bwd_ntile, m.vm_ntile), 1) * (m.nB + 3) * 4, 256);
+      float* dense = reinterpret_cast<float*>(q);
+      float* gsum = reinterpret_cast<float*>(q + align_up((size_t)B * m.J * 48, 256));
+      SlotReduceArgs ra;
+      ra.B = B; ra.J = m.J; ra.ne = nb + 3; ra.ntile = pa.ntile;
+      ra.gA_slots = pa.gA_slots; ra.slot_bstride = pa.slot_bstride; ra.slot_sstride = pa.slot_sstride;
+      ra.sb_ptr = pa.sb_ptr; ra.gbt_part = pa.gbt_part; ra.gA_dense = dense; ra.gbt_sum = gsum;
+      const long long nthr = std::max(3LL * B, (long long)B * ra.ne);
+      dim3 grid(blocks_for(nthr, 256), m.J + 1);
+      prof_begin("slot_reduce_kernel", st);
+      slot_reduce_kernel<<<grid, 256, 0, st>>>(ra);
+      SMIL_LAUNCH_CHECK("slot_reduce_kernel");
+      pa.gA_slots = nullptr; pa.gA_dense = dense;
+      pa.gbt_part = gsum; pa.ntile = 1;
     }
     pa.joints_mode = p.is_static ? 2 : 1;
     pa.g_beta = g->g_beta; pa.g_trans = g->g_trans;
@@ -921,6 +924,55 @@ int smil_keypoint3d_loss_backward(const SmilKp3dArgs* a, void* stream) {
   prof_begin("kp3d_bwd_kernel", static_cast<cudaStream_t>(stream));
   kp3d_bwd_kernel<<<blocks_for((long long)a->batch * a->num_joints, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(*a);
   SMIL_LAUNCH_CHECK("kp3d_bwd_kernel");
+  return SMIL_OK;
+}
+
+// ---- DLT triangulation, 6-D rotations ---------------------------------------------------------------------
+static int check_tri(const SmilTriArgs* a) {
+  if (!a) return fail(SMIL_EINVAL, "SmilTriArgs is NULL");
+  if (a->batch <= 0 || a->num_views <= 0 || a->num_joints <= 0) return fail(SMIL_EINVAL, "batch/num_views/num_joints must be positive");
+  if (!a->keypoints || !a->visibility || !a->cam_R || !a->cam_T || !a->fov_deg)
+    return fail(SMIL_EINVAL, "keypoints, visibility, cam_R, cam_T and fov_deg are required");
+  if (!(a->image_size > 0.f)) return fail(SMIL_EINVAL, "image_size must be positive");
+  return SMIL_OK;
+}
+int smil_triangulate_dlt_forward(const SmilTriArgs* a, void* stream) {
+  int rc = check_tri(a);
+  if (rc != SMIL_OK) return rc;
+  if (!a->tri) return fail(SMIL_EINVAL, "tri output is NULL");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  prof_begin("tri_fwd_kernel", st);
+  tri_fwd_kernel<<<blocks_for((long long)a->batch * a->num_joints, 128), 128, 0, st>>>(*a);
+  SMIL_LAUNCH_CHECK("tri_fwd_kernel");
+  return SMIL_OK;
+}
+int smil_triangulate_dlt_backward(const SmilTriArgs* a, void* stream) {
+  int rc = check_tri(a);
+  if (rc != SMIL_OK) return rc;
+  if (!a->g_tri) return fail(SMIL_EINVAL, "g_tri is NULL");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int threads = std::min(128, std::max(32, ((std::max(a->num_joints, a->num_views) + 31) / 32) * 32));
+  const size_t smem = (size_t)a->num_joints * 6 * sizeof(float);
+  if ((rc = set_smem(tri_bwd_kernel, smem)) != SMIL_OK) return rc;
+  prof_begin("tri_bwd_kernel", st);
+  tri_bwd_kernel<<<a->batch, threads, smem, st>>>(*a);
+  SMIL_LAUNCH_CHECK("tri_bwd_kernel");
+  return SMIL_OK;
+}
+int smil_rot6d_to_rotmat_forward(const float* d6, float* R, int64_t n, int32_t columns, void* stream) {
+  if (n <= 0) return SMIL_OK;
+  if (!d6 || !R) return fail(SMIL_EINVAL, "smil_rot6d_to_rotmat_forward: NULL argument");
+  prof_begin("rot6d_fwd_kernel", static_cast<cudaStream_t>(stream));
+  rot6d_fwd_kernel<<<blocks_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d6, R, n, columns);
+  SMIL_LAUNCH_CHECK("rot6d_fwd_kernel");
+  return SMIL_OK;
+}
+int smil_rot6d_to_rotmat_backward(const float* d6, const float* g_R, float* g_d6, int64_t n, int32_t columns, void* stream) {
+  if (n <= 0) return SMIL_OK;
+  if (!d6 || !g_R || !g_d6) return fail(SMIL_EINVAL, "smil_rot6d_to_rotmat_backward: NULL argument");
+  prof_begin("rot6d_bwd_kernel", static_cast<cudaStream_t>(stream));
+  rot6d_bwd_kernel<<<blocks_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d6, g_R, g_d6, n, columns);
+  SMIL_LAUNCH_CHECK("rot6d_bwd_kernel");
   return SMIL_OK;
 }
 

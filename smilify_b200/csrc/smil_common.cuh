@@ -83,14 +83,14 @@ struct DevModel {
   const float* rec2;
   const int *unit_bone, *unit_ptr, *unit_tile, *tile_unit_ptr, *warp_unit_ptr, *warp_unit, *tjv_ptr, *tjv_v;
   const int *sb_ptr, *unit_slot;
-  // lane-per-sample forward skin pass (fused_kernels.cuh::skin_fwd3_kernel): tiles of F3_TILE consecutive vertices,
-  // inside a tile the vertices are ordered by their bone pair so that a run shares its bone transforms
-  const float* f3_rec;        // [f3_ntile * F3_TILE][f3_recf]: T(3) | S[NBT][3] | w0 | w1 | 3*local vertex (int bits) | pad
-  const int4* f3_runs;        // (bone0 * 12, bone1 * 12 or -1 for a single-bone run, first slot in the tile, slots)
-  const int* f3_tile_run_ptr; // [f3_ntile + 1]
-  int f3_ntile, f3_recf, f3_max_runs, f3_ok;
+  // vertex-major backward skin pass (skin_bwd_vm.cuh)
+  int vm_ok, vm_chunk, vm_nphase, vm_warps, vm_ntile, vm_recf, vm_nslots, h_vm_max_tile_recs, h_vm_max_tile_segs;
+  const float* vm_rec;
+  const int4* vm_seg;
+  const int *vm_tile_rec_ptr, *vm_warp_seg_ptr, *vm_sb_ptr, *vm_slot_bone;
   // host copies needed by launch logic
   int h_max_tile_pairs, h_max_jv, h_max_je, h_max_tile_units;
+  SmilTuning tune;   // per-model kernel variant switches (host-side launch logic only)
   void* arena;  // single device allocation that backs every table
 };
 
@@ -99,7 +99,6 @@ struct DevModel {
 // of 24 makes 8 consecutive bones start in 8 different 16-byte bank groups, so the per-thread float4
 // gathers of the forward skin pass collide only for bones that are congruent mod 8 (not mod 4).
 constexpr int PPB = 28;
-constexpr int F3_TILE = 16;   // vertices per tile of the lane-per-sample forward skin pass
 
 // ---- small device math ------------------------------------------------------------------------
 struct f3 {

@@ -100,33 +100,57 @@ class ShardedFitterStep:
 
 
 class GraphedShardedFitterStep(ShardedFitterStep):
-    """:class:`ShardedFitterStep` with the local part -- loss, backward through the CUDA path, packing of the
-    shared gradients -- captured ONCE in a CUDA graph and replayed per step; only the all-reduce stays an eager
-    NCCL call on the same stream.  An optimiser loop over a fixed window of frames (fitter.py:150-296 runs the
-    same shapes for hundreds of epochs) then costs one graph launch + one collective instead of ~40 Python-side
-    launches, which is what bounds the step once the frames are spread over 8 GPUs (8 192 frames per GPU take
-    ~0.45 ms of kernels).  Leaves keep their storage: update them in place (``p.data.add_``, a captured or foreach
+    """:class:`ShardedFitterStep` with the whole step -- loss, backward through the CUDA path, packing of the shared
+    gradients, the NCCL all-reduce and the write-back into ``.grad`` -- captured ONCE in a CUDA graph and replayed
+    per step.  An optimiser loop over a fixed window of frames (fitter.py:150-296 runs the same shapes for hundreds
+    of epochs) then costs one graph launch instead of ~40 Python-side launches plus an eager collective, which is
+    what bounds the step once the frames are spread over 8 GPUs (8 192 frames per GPU take ~0.45 ms of kernels).
+    NCCL collectives are stream-capturable once the communicator exists, so one eager all-reduce is issued before the
+    capture; ``capture_collective=False`` (or a backend that cannot be captured) keeps the all-reduce as an eager call
+    after the replay.  Leaves keep their storage: update them in place (``p.data.add_``, a captured or foreach
     optimiser); ``.grad`` tensors are allocated during capture and rewritten by every replay.  CUDA only."""
 
-    def __init__(self, frame_params, shared_params, loss_fn, num_frames_total, group=None, warmup=3):
+    def __init__(self, frame_params, shared_params, loss_fn, num_frames_total, group=None, warmup=3,
+                 capture_collective=True):
         super().__init__(frame_params, shared_params, loss_fn, num_frames_total, group)
         leaves = list(frame_params.values()) + list(shared_params.values())
         if not leaves or not all(p.is_cuda for p in leaves):
             raise RuntimeError("GraphedShardedFitterStep needs CUDA leaf tensors (there is no CPU fallback)")
         dev = leaves[0].device
         self._shared = list(shared_params.values())
+        self._distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
             for _ in range(max(1, warmup)):
-                self._local()
+                buf = self._local()
+                if self._distributed:
+                    dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)   # also creates the communicator
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
+        self.collective_in_graph = False
+        if self._distributed and capture_collective:
+            try:
+                self._capture(True)
+                self.collective_in_graph = True
+            except Exception:   # a backend / build whose collectives cannot be stream-captured
+                torch.cuda.synchronize(dev)
+                self._capture(False)
+        else:
+            self._capture(False)
+        self._leaves = leaves
+        self._grads = [p.grad for p in leaves]   # static: every replay rewrites these tensors
+        if self._distributed:
+            self.collective_bytes = self._buf.numel() * 4
+
+    def _capture(self, with_collective):
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self._buf = self._local()
-        self._leaves = leaves
-        self._grads = [p.grad for p in leaves]   # static: every replay rewrites these tensors
+            if with_collective:
+                dist.all_reduce(self._buf, op=dist.ReduceOp.SUM, group=self.group)
+                for p, g in zip(self._shared, unpack_grads(self._buf[:-1], self._shared)):
+                    p.grad.copy_(g)
 
     def _local(self):
         for p in list(self.frame_params.values()) + list(self.shared_params.values()):
@@ -137,17 +161,17 @@ class GraphedShardedFitterStep(ShardedFitterStep):
                           local.detach().reshape(1).to(torch.float32)])
 
     def __call__(self) -> torch.Tensor:
+        """Returns the GLOBAL loss as a view of the step's static buffer (valid until the next call)."""
         self.graph.replay()
         for p, g in zip(self._leaves, self._grads):   # re-attach (a caller may have reset .grad since the capture)
             p.grad = g
         buf = self._buf
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+        if self._distributed and not self.collective_in_graph:
             dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=self.group)
-            self.collective_bytes = buf.numel() * 4
             with torch.no_grad():
                 for p, g in zip(self._shared, unpack_grads(buf[:-1], self._shared)):
                     p.grad.copy_(g)
-        return buf[-1].clone()
+        return buf[-1]
 
 
 def smal_joint_loss_fn(model, cam_R, cam_T, target_yx, visibility, joint_ids=None, image_size=512, w_j2d=1.0,

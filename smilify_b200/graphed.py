@@ -20,16 +20,26 @@ import torch
 
 class GraphedStep:
     def __init__(self, model, batch, num_betas=None, with_scale=False, with_trans_offsets=False,
-                 propagate_scaling=False, shared_betas=False, warmup=3):
+                 propagate_scaling=False, shared_betas=False, warmup=3, packed_io=False):
         dev = model._device
         J, V = model._tables["J"], model._tables["V"]
         nb = model.num_betas if num_betas is None else num_betas
         opts = dict(device=dev, dtype=torch.float32)
         self.model, self.batch = model, batch
         self.shared_betas = shared_betas
-        self.beta = torch.zeros((1 if shared_betas else batch, nb), **opts).requires_grad_(True)
-        self.theta = torch.zeros((batch, J, 3), **opts).requires_grad_(True)
-        self.trans = torch.zeros((batch, 3), **opts).requires_grad_(True)
+        nbeta = (1 if shared_betas else batch) * nb
+        # packed_io: beta | theta | trans are views of ONE device buffer (one host->device copy feeds a step) and the
+        # parameter gradients + posed joints are gathered into ONE device buffer inside the captured graph
+        self.packed_in = torch.zeros(nbeta + batch * J * 3 + batch * 3, **opts) if packed_io else None
+        if packed_io:
+            o1, o2 = nbeta, nbeta + batch * J * 3
+            self.beta = self.packed_in[:o1].view(1 if shared_betas else batch, nb).requires_grad_(True)
+            self.theta = self.packed_in[o1:o2].view(batch, J, 3).requires_grad_(True)
+            self.trans = self.packed_in[o2:].view(batch, 3).requires_grad_(True)
+        else:
+            self.beta = torch.zeros((1 if shared_betas else batch, nb), **opts).requires_grad_(True)
+            self.theta = torch.zeros((batch, J, 3), **opts).requires_grad_(True)
+            self.trans = torch.zeros((batch, 3), **opts).requires_grad_(True)
         self.logscale = torch.zeros((batch, J, 3), **opts).requires_grad_(True) if with_scale else None
         self.btrans = torch.zeros((batch, J, 3), **opts).requires_grad_(True) if with_trans_offsets else None
         self.g_verts = torch.zeros((batch, V, 3), **opts)
@@ -43,9 +53,16 @@ class GraphedStep:
                 self._run()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
+        self.packed_out = None
+        self.out_layout = None
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             outs, grads = self._run()
+            if packed_io:   # (grad_beta | grad_theta | grad_trans | joints) contiguous, gathered on the device
+                parts = [grads[0], grads[1], grads[2], outs[1]]
+                self.packed_out = torch.cat([t.reshape(-1) for t in parts])
+                self.out_layout = [("grad_beta", tuple(parts[0].shape)), ("grad_theta", tuple(parts[1].shape)),
+                                   ("grad_trans", tuple(parts[2].shape)), ("joints", tuple(parts[3].shape))]
         self.verts, self.joints, self.Rs, self.v_shaped = outs
         it = iter(grads)
         self.grad_beta = next(it)
@@ -70,14 +87,21 @@ class HostPipeline:
 
     ``depth`` device buffer sets, each a :class:`GraphedStep` on its own CUDA stream: the host->device
     copy of batch i+1 and the device->host copy of batch i-1 overlap the kernels of batch i, so a
-    stream of batches runs at ``max(copy, compute)`` per batch instead of their sum.  Upstream gradients
-    (``slot.g_verts`` / ``slot.g_joints``) stay on the device -- in a fit they come from a loss computed there.
+    stream of batches runs at ``max(copy, compute)`` per batch instead of their sum.  Per step there is ONE
+    host->device copy (beta | theta | trans packed in one pinned buffer) and ONE device->host copy (parameter
+    gradients | posed joints, gathered on the device inside the captured graph).  Upstream gradients
+    (``slot.g_verts`` / ``slot.g_joints``) and the posed vertices stay on the device -- in a fit the loss lives there.
 
         pipe = HostPipeline(model, B)
-        for batch in batches:                       # pinned CPU tensors
-            done = pipe.submit(batch.beta, batch.theta, batch.trans)
-            if done is not None: consume(done)      # dict of pinned CPU tensors of an EARLIER batch
+        buf, (beta, theta, trans) = pipe.new_input() # pinned, packed: fill the views per batch ...
+        for batch in batches:
+            done = pipe.submit_packed(buf)          # ... or pipe.submit(beta, theta, trans) with three pinned tensors
+            if done is not None: consume(done)      # dict of pinned CPU views of an EARLIER batch
         for done in pipe.drain(): consume(done)
+
+    A dict handed out by ``submit`` / ``drain`` stays valid until the SECOND following ``submit`` that reuses its slot:
+    every slot owns two host output sets and alternates between them, so the copies queued by the submit that returns
+    ``done`` never touch ``done``'s memory.
     """
 
     OUT = ("grad_beta", "grad_theta", "grad_trans", "joints")
@@ -88,33 +112,64 @@ class HostPipeline:
         for _ in range(depth):
             st = torch.cuda.Stream(device=dev)
             with torch.cuda.stream(st):
-                gs = GraphedStep(model, batch, **step_kwargs)
+                gs = GraphedStep(model, batch, packed_io=True, **step_kwargs)
             st.synchronize()
-            host = {k: torch.empty(getattr(gs, k).shape, dtype=torch.float32).pin_memory() for k in self.OUT}
-            self.slots.append(dict(step=gs, stream=st, event=torch.cuda.Event(), host=host, busy=False))
+            n_out = gs.packed_out.numel()
+            hosts = []
+            for _h in range(2):
+                flat = torch.empty(n_out, dtype=torch.float32).pin_memory()
+                flat.zero_()      # first touch after the rank's CPU affinity is set: pages land on the local NUMA node
+                views, o = {}, 0
+                for name, shape in gs.out_layout:
+                    n = 1
+                    for d in shape:
+                        n *= d
+                    views[name] = flat[o:o + n].view(shape)
+                    o += n
+                hosts.append((flat, views))
+            self.slots.append(dict(step=gs, stream=st, event=torch.cuda.Event(), hosts=hosts, cur=0, busy=False))
         self._n = 0
-        self.h2d_bytes = 0
-        self.d2h_bytes = sum(t.numel() * 4 for t in self.slots[0]["host"].values())
+        self.h2d_bytes = self.slots[0]["step"].packed_in.numel() * 4
+        self.d2h_bytes = self.slots[0]["hosts"][0][0].numel() * 4
 
-    def submit(self, beta, theta, trans):
+    def new_input(self):
+        """A pinned host buffer in the packed input layout plus its ``(beta, theta, trans)`` views: fill the views,
+        hand the buffer to :meth:`submit_packed` (ONE host->device copy per step, nothing staged on the host)."""
+        gs = self.slots[0]["step"]
+        flat = torch.empty(gs.packed_in.numel(), dtype=torch.float32).pin_memory()
+        flat.zero_()
+        o1 = gs.beta.numel()
+        o2 = o1 + gs.theta.numel()
+        return flat, (flat[:o1].view(gs.beta.shape), flat[o1:o2].view(gs.theta.shape), flat[o2:].view(gs.trans.shape))
+
+    def _launch(self, copy_in):
         s = self.slots[self._n % len(self.slots)]
         self._n += 1
         done = None
         if s["busy"]:
-            s["event"].synchronize()      # the batch that used this slot is complete: its outputs are in s["host"]
-            done = s["host"]
+            s["event"].synchronize()      # the batch that used this slot is complete: its outputs are in hosts[cur]
+            done = s["hosts"][s["cur"]][1]
+            s["cur"] ^= 1                 # the new batch writes the OTHER host set
         gs = s["step"]
         with torch.cuda.stream(s["stream"]), torch.no_grad():
+            copy_in(gs)
+            gs.replay()
+            s["hosts"][s["cur"]][0].copy_(gs.packed_out, non_blocking=True)
+            s["event"].record(s["stream"])
+        s["busy"] = True
+        return done
+
+    def submit_packed(self, packed):
+        """``packed``: a pinned buffer from :meth:`new_input` (the caller keeps it untouched until the step has run)."""
+        return self._launch(lambda gs: gs.packed_in.copy_(packed, non_blocking=True))
+
+    def submit(self, beta, theta, trans):
+        """Three separate (ideally pinned) host tensors: three host->device copies into the packed device buffer."""
+        def copy_in(gs):
             gs.beta.copy_(beta, non_blocking=True)
             gs.theta.copy_(theta, non_blocking=True)
             gs.trans.copy_(trans, non_blocking=True)
-            gs.replay()
-            for k in self.OUT:
-                s["host"][k].copy_(getattr(gs, k), non_blocking=True)
-            s["event"].record(s["stream"])
-        s["busy"] = True
-        self.h2d_bytes = (beta.numel() + theta.numel() + trans.numel()) * 4
-        return done
+        return self._launch(copy_in)
 
     def drain(self):
         out = []
@@ -124,5 +179,5 @@ class HostPipeline:
             if s["busy"]:
                 s["event"].synchronize()
                 s["busy"] = False
-                out.append(s["host"])
+                out.append(s["hosts"][s["cur"]][1])
         return out

@@ -235,6 +235,9 @@ def pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J
     t["tjv_ptr"] = _i32(tjv_ptr)
     t["tjv_v"] = _i32(tjv_v + [0] * (max(t["jreg_nnz"], 1) - len(tjv_v)))  # padded to the size the library copies
     t["fused_ok"] = bool(K <= MAX_FUSED_K and nbt_of(nB) > 0 and P == 0)
+    t["vm_ok"] = False
+    if t["fused_ok"] and K <= 2 and _os.environ.get("SMIL_BWD_VM", "1") != "0":
+        t.update(pack_backward_vm(vt, S3, idx, val, nnz_row, J, nB))
     return t
 
 
@@ -290,7 +293,7 @@ def _refine_anchor_warps(a0, a1, members, sweeps=4, w_load=0.77, w_store=0.61):
 
     by_anchor = {}
     for i in sorted(wof):
-        by_anchor.setdefault(a0[i], []).append(i)
+        by_anchor.setdefault((a0[i], a1[i] >= 0), []).append(i)   # never trade a two-bone vertex into a single-bone warp
     costs = [cost(w) for w in range(nw)]
     for _ in range(sweeps):
         improved = False
@@ -299,7 +302,7 @@ def _refine_anchor_warps(a0, a1, members, sweeps=4, w_load=0.77, w_store=0.61):
             if cr[wa].get(i & 31, 0) < 2:
                 continue
             best = None
-            for j in by_anchor[a0[i]]:
+            for j in by_anchor[(a0[i], a1[i] >= 0)]:
                 wb = wof[j]
                 if wb == wa:
                     continue
@@ -330,7 +333,7 @@ def forward_thread_assignment_anchor(idx, val, nnz_row, V, chunk):
     import hashlib
 
     key = hashlib.sha1(np.ascontiguousarray(idx).tobytes() + np.ascontiguousarray(val).tobytes() +
-                       np.ascontiguousarray(nnz_row).tobytes() + repr((V, chunk, _os.environ.get("SMIL_FWD_REFINE", "1"))).encode()
+                       np.ascontiguousarray(nnz_row).tobytes() + repr((V, chunk, _os.environ.get("SMIL_FWD_REFINE", "1"), _os.environ.get("SMIL_FWD_SINGLE_FIRST", "1"))).encode()
                        ).hexdigest()
     if key not in _ANCHOR_MEMO:
         _ANCHOR_MEMO[key] = _forward_thread_assignment_anchor(idx, val, nnz_row, V, chunk)
@@ -371,7 +374,12 @@ def _forward_thread_assignment_anchor(idx, val, nnz_row, V, chunk):
                 a1.append(t[1 - k]); w1.append(w[1 - k])
             else:
                 a1.append(-1); w1.append(0.0)
-        order = sorted(range(n), key=lambda i: (prio[a0[i]], a1[i] < 0, a1[i], i))
+        if _os.environ.get("SMIL_FWD_SINGLE_FIRST", "1") != "0":
+            # single-bone vertices first (grouped by bone), then the two-bone ones by (anchor, partner): whole warps of
+            # single-bone vertices skip the second skinning slot in the kernel (a warp-uniform branch)
+            order = sorted(range(n), key=lambda i: (a1[i] >= 0, prio[a0[i]], a1[i], i))
+        else:
+            order = sorted(range(n), key=lambda i: (prio[a0[i]], a1[i] < 0, a1[i], i))
         members = [order[w * 32:(w + 1) * 32] for w in range((n + 31) // 32)]
         if _os.environ.get("SMIL_FWD_REFINE", "1") != "0":
             members = _refine_anchor_warps(a0, a1, members)
@@ -552,6 +560,224 @@ def forward_thread_assignment_spread(idx, val, nnz_row, V, chunk):
                     pos[c * chunk + w * 32 + r] = grid[w][r] - v0
     owner = np.where(pos >= 0, pos + (np.arange(nchunk * chunk) // chunk) * chunk, -1)
     return pos, owner
+
+
+# ---------------------------------------------------------------------------------------------------
+# fused backward pass, vertex-major tables (rigs with at most two skinning weights per vertex)
+# ---------------------------------------------------------------------------------------------------
+VM_CHUNK = int(_os.environ.get("SMIL_VM_CHUNK", "168"))   # upper bound of the vertices per tile (4 CTAs per SM on STICK)
+VM_PHASES = int(_os.environ.get("SMIL_VM_PHASES", "1"))
+VM_WARPS = int(_os.environ.get("SMIL_VM_WARPS", "4"))       # warps of a CTA that share one tile (1: every warp owns a small tile)   # sub-ranges of a tile with their own row buffer (double buffering)
+VM_MODE_PACKED, VM_MODE_X, VM_MODE_Y = 0, 1, 2
+VM_CUT_TOL = float(_os.environ.get("SMIL_VM_CUT_TOL", "0.15"))   # how far a warp cut may move from the equal split
+
+
+def vm_rec_floats(nbt: int) -> int:
+    """Floats per vertex record: (wX, wY, 3*local vertex, T0) | T1 T2 | S[nbt][3], padded to whole float4s."""
+    return (6 + 3 * nbt + 3) // 4 * 4
+
+
+def _vm_order_runs(combos, X=None, Y=None, lv0=0):
+    """Order in which a stretch of vertices is processed by a warp that keeps TWO bones resident in registers (slots X
+    and Y: rotation + 3x4 gradient accumulator each).  Vertices that share their bone set form a run; a run needs its
+    bones resident; evicting a bone that is needed again later costs one more partial slot, so the runs are chained
+    greedily along shared bones (the bone-pair graph of a skinned mesh is close to its skeleton tree, and a walk along
+    it replaces one bone at a time).  ``X`` / ``Y``: the bones resident on entry (from the stretch before).
+    Returns [(X, Y, run bones, [vertex indices lv0 + i])] and the resident pair on exit."""
+    runs = {}
+    for lv, c in enumerate(combos):
+        runs.setdefault(tuple(sorted(c)), []).append(lv0 + lv)
+    remaining = dict(runs)
+    left = {}
+    for c in remaining:
+        for b in c:
+            left[b] = left.get(b, 0) + 1
+    ops = []
+    while remaining:
+        res = {b for b in (X, Y) if b is not None}
+        best = None
+        for c in sorted(remaining):
+            need = [b for b in c if b not in res]
+            evict = max(0, len(need) - (2 - len(res)))
+            ev_cost = 0
+            if evict:
+                cand = sorted((b for b in res if b not in c), key=lambda b: (left.get(b, 0), b))
+                ev_cost = sum(1 for b in cand[:evict] if left.get(b, 0) > 0)
+            key = (ev_cost, -len(set(c) & res), evict, -len(remaining[c]), c)
+            if best is None or key < best[0]:
+                best = (key, c)
+        c = best[1]
+        for b in c:
+            if b in (X, Y):
+                continue
+            if X is None:
+                X = b
+            elif Y is None:
+                Y = b
+            else:
+                slot = min((s for s in (0, 1) if (X, Y)[s] not in c), key=lambda s: (left.get((X, Y)[s], 0), s))
+                if slot == 0:
+                    X = b
+                else:
+                    Y = b
+        for b in c:
+            left[b] -= 1
+        ops.append((X, Y, c, remaining.pop(c)))
+    return ops, (X, Y)
+
+
+def pack_backward_vm(vt, S3, idx, val, nnz_row, J, nB, chunk=None, nwarps=None, nphase=None):
+    """Vertex-major tables of the fused backward skin pass (``skin_bwd_vm_kernel``).
+
+    A tile is ``chunk`` consecutive vertices cut into ``nphase`` PHASES (sub-ranges that start on a multiple of four
+    vertices).  The ``g_verts`` rows of one phase arrive by one TMA bulk copy per sample into that phase's own buffer,
+    so while the CTA works on phase p the copy of phase p+1 (or of phase 0 of the next sample group) is in flight:
+    the staging is double-buffered without a second tile-sized buffer.  Inside a phase the vertices are ordered by
+    :func:`_vm_order_runs` and cut into ``nwarps`` shares; a warp walks its share of phase 0, then of phase 1, ... and its
+    two resident bones survive the phase switch.  Every share is a list of SEGMENTS -- stretches with the same two
+    resident bones.  A segment descriptor is 8 ints:
+    ``(load X: bone or -1, load Y, first record, records | flush X: slot or -1, flush Y, mode, the warp's next
+    segment or -1)``; a flush
+    writes the slot's 3x4 partial of dL/dA to its own global slot (no atomics; slots are numbered bone-major so that
+    the pose backward sums ``sb_ptr[k] .. sb_ptr[k+1]``).  Per vertex the shape blend, ``R^T g`` and the dL/dbeta
+    contraction are evaluated ONCE (the item-major tables of :func:`pack_backward_items` evaluate them per bone)."""
+    V = vt.shape[0]
+    nphase = VM_PHASES if nphase is None else nphase
+    nwarps = VM_WARPS if nwarps is None else nwarps
+    chunk = backward_chunk(V, VM_CHUNK) if chunk is None else chunk
+    q = 4 * nphase
+    chunk = max(q, (chunk + q - 1) // q * q)   # phases start on 16-byte boundaries of a row when 3V % 4 == 0
+    pw = chunk // nphase                       # vertices per phase
+    ntile = (V + chunk - 1) // chunk
+    nbt = max(nbt_of(nB), 1)
+    recf = vm_rec_floats(nbt)
+    Sv = S3.transpose(1, 0, 2)  # (V, nB, 3)
+    recs, segs = [], []
+    tile_rec_ptr, warp_seg_ptr = [0], [0]        # warp_seg_ptr: [(tile * nphase + phase) * nwarps + warp]
+    flush_bone = []          # bone of every flush, in creation order; slot ids are assigned bone-major afterwards
+    max_tile_recs = max_tile_segs = 0
+    for ti in range(ntile):
+        v0, v1 = ti * chunk, min(V, (ti + 1) * chunk)
+        wts = [{int(idx[v, s]): float(val[v, s]) for s in range(int(nnz_row[v]))} for v in range(v0, v1)]
+        tile_first_seg = len(segs)
+        cur = [[None, None] for _ in range(nwarps)]       # bones in the warps' slots X / Y
+        dirty = [[False, False] for _ in range(nwarps)]   # ... that hold an unflushed accumulator
+        last_seg = [-1] * nwarps                          # the warp's latest segment (flushes are attached to it)
+        X = Y = None
+        for ph in range(nphase):
+            p0, p1 = min(v1 - v0, ph * pw), min(v1 - v0, (ph + 1) * pw)
+            combos = [tuple(int(idx[v0 + lv, s]) for s in range(max(int(nnz_row[v0 + lv]), 1))) for lv in range(p0, p1)]
+            ops, (X, Y) = _vm_order_runs(combos, X, Y, lv0=p0)
+            flat = [(lv, x, y) for x, y, _c, lvs in ops for lv in lvs]
+            n = len(flat)
+            # cut points between the shares: near the equal split, but preferably where the resident bones change
+            # anyway (a cut inside a stretch with the same two bones costs two extra partial slots, at a boundary where
+            # one bone changes one, where both change none)
+            cuts = [0]
+            tol = max(1, int(VM_CUT_TOL * n / nwarps))
+            for w in range(1, nwarps):
+                ideal = (n * w) // nwarps
+                best = None
+                for pos in range(max(cuts[-1] + 1, ideal - tol), min(n - (nwarps - w), ideal + tol) + 1):
+                    same = int(flat[pos - 1][1] == flat[pos][1]) + int(flat[pos - 1][2] == flat[pos][2])
+                    key = (same, abs(pos - ideal))
+                    if best is None or key < best[0]:
+                        best = (key, pos)
+                cuts.append(best[1] if best else min(max(ideal, cuts[-1]), n))
+            cuts.append(n)
+            shares = [flat[cuts[k]:cuts[k + 1]] for k in range(nwarps)]
+            # which warp takes which share is free: give every share to the warp that already holds its bones
+            def used_bones(share):
+                out = set()
+                for lv, x, y in share:
+                    out |= {b for b in (x, y) if b is not None and wts[lv].get(b, 0.0) != 0.0}
+                return out
+            ub = [used_bones(sh) for sh in shares]
+            import itertools
+            best_perm, best_score = tuple(range(nwarps)), -1
+            for perm in itertools.permutations(range(nwarps)):
+                score = sum(len(ub[perm[w]] & {b for b, d in zip(cur[w], dirty[w]) if d and b is not None}) for w in range(nwarps))
+                if score > best_score:
+                    best_perm, best_score = perm, score
+            for w in range(nwarps):
+                part = shares[best_perm[w]]
+                curX, curY = cur[w]
+                i = 0
+                while i < len(part):
+                    Xs, Ys = part[i][1], part[i][2]
+                    j = i
+                    while j < len(part) and part[j][1] == Xs and part[j][2] == Ys:
+                        j += 1
+                    # the planner's slot labels are per sequence; a warp may hold the bones in the other slots already
+                    bones = [b for b in (Xs, Ys) if b is not None]
+                    if curY in bones and curX not in bones and (Xs == curY or Ys == curY):
+                        if Ys != curY:
+                            Xs, Ys = Ys, Xs
+                    elif curX in bones and Xs != curX:
+                        Xs, Ys = Ys, Xs
+                    seg_first = len(recs) - tile_rec_ptr[-1]
+                    anyX = anyY = False
+                    for lv, _x, _y in part[i:j]:
+                        wX = wts[lv].get(Xs, 0.0) if Xs is not None else 0.0
+                        wY = wts[lv].get(Ys, 0.0) if Ys is not None else 0.0
+                        anyX |= wX != 0.0
+                        anyY |= wY != 0.0
+                        r = np.zeros(recf, dtype=np.float32)
+                        r[0], r[1] = wX, wY
+                        r[2] = np.int32(3 * (lv - ph * pw)).view(np.float32)    # float offset inside the PHASE's row
+                        v = v0 + lv
+                        r[3:6] = vt[v]
+                        r[6:6 + 3 * nB] = Sv[v].reshape(-1)
+                        recs.append(r)
+                    # a slot whose bone changes is flushed by the warp's PREVIOUS segment (patched below) and loaded here
+                    loadX = Xs if (Xs is not None and Xs != curX and anyX) else -1
+                    loadY = Ys if (Ys is not None and Ys != curY and anyY) else -1
+                    if loadX >= 0 and dirty[w][0]:
+                        segs[last_seg[w]][4] = len(flush_bone); flush_bone.append(curX); dirty[w][0] = False
+                    if loadY >= 0 and dirty[w][1]:
+                        segs[last_seg[w]][5] = len(flush_bone); flush_bone.append(curY); dirty[w][1] = False
+                    if loadX >= 0:
+                        curX = Xs
+                    if loadY >= 0:
+                        curY = Ys
+                    if anyX and Xs != curX:
+                        raise AssertionError("vertex-major packer: slot X holds a stale bone")
+                    if anyY and Ys != curY:
+                        raise AssertionError("vertex-major packer: slot Y holds a stale bone")
+                    dirty[w][0] |= anyX
+                    dirty[w][1] |= anyY
+                    mode = VM_MODE_X if not anyY else VM_MODE_PACKED   # a Y-only stretch (rare): packed path with w_X = 0
+                    if last_seg[w] >= 0:
+                        segs[last_seg[w]][7] = len(segs) - tile_first_seg    # link: the warp's next segment (tile-local)
+                    last_seg[w] = len(segs)
+                    segs.append([loadX, loadY, seg_first, j - i, -1, -1, mode, -1])
+                    i = j
+                cur[w] = [curX, curY]
+                if ph == nphase - 1:   # end of the warp's work on this tile: what is still accumulating goes out with its
+                    if dirty[w][0]:    # latest segment (which may sit in an earlier phase when the last share is empty)
+                        segs[last_seg[w]][4] = len(flush_bone); flush_bone.append(curX)
+                    if dirty[w][1]:
+                        segs[last_seg[w]][5] = len(flush_bone); flush_bone.append(curY)
+                warp_seg_ptr.append(len(segs))
+        tile_rec_ptr.append(len(recs))
+        max_tile_recs = max(max_tile_recs, tile_rec_ptr[-1] - tile_rec_ptr[-2])
+        max_tile_segs = max(max_tile_segs, len(segs) - tile_first_seg)
+    fb = np.asarray(flush_bone, dtype=np.int64)
+    order = np.argsort(fb, kind="stable")
+    slot_of = np.empty(len(fb), dtype=np.int64)
+    slot_of[order] = np.arange(len(fb))
+    seg_arr = np.asarray(segs, dtype=np.int64).reshape(-1, 8)
+    for col in (4, 5):
+        m = seg_arr[:, col] >= 0
+        seg_arr[m, col] = slot_of[seg_arr[m, col]]
+    sb_ptr = np.concatenate([[0], np.cumsum(np.bincount(fb, minlength=J))])
+    return dict(
+        vm_rec=_f32(np.stack(recs)) if recs else np.zeros((0, recf), np.float32), vm_recf=recf, vm_chunk=chunk,
+        vm_nphase=nphase, vm_warps=nwarps, vm_ntile=ntile, vm_seg=_i32(seg_arr), vm_nseg=int(seg_arr.shape[0]),
+        vm_tile_rec_ptr=_i32(tile_rec_ptr), vm_warp_seg_ptr=_i32(warp_seg_ptr), vm_sb_ptr=_i32(sb_ptr),
+        vm_nslots=int(len(fb)), vm_slot_bone=_i32(fb[order]), vm_max_tile_recs=int(max_tile_recs),
+        vm_max_tile_segs=int(max_tile_segs), vm_ok=True,
+    )
 
 
 def _interleave_for_streams(items):

@@ -121,7 +121,85 @@ def fast_forward(t, beta, theta, trans, ls, bt, propagate, static, rotmat=False)
     return dict(verts=verts, joints=joints, Rs=R, v_shaped=vs, J_transformed=f["Gt"], chain=f, Jrest=Jrest)
 
 
-def fast_backward(t, beta, theta, trans, ls, bt, propagate, static, fw, g_verts, g_joints, g_Rs=None, rotmat=False):
+def skin_backward_vm(t, beta, GR, gv):
+    """Vertex-major backward skin pass (csrc/skin_bwd_vm.cuh) driven by the ``vm_*`` tables: per tile and warp share a
+    list of segments; two resident bones (slots X, Y) with a 3x4 accumulator each; per vertex the shape blend,
+    u = sum_k w_k R_k^T g and the dL/dbeta contraction once; flushes write bone-major numbered partial slots."""
+    B = beta.shape[0]
+    J, nB = t["J"], t["nB"]
+    nb = beta.shape[1]
+    recf = t["vm_recf"]
+    rec = t["vm_rec"].astype(np.float64)
+    seg = t["vm_seg"]
+    slots = np.zeros((t["vm_nslots"], B, 3, 4))
+    written = np.zeros(t["vm_nslots"], dtype=int)
+    g_beta = np.zeros((B, nb))
+    g_trans = np.zeros((B, 3))
+    C = t["vm_chunk"]
+    seen = np.zeros(t["V"], dtype=int)
+    NPH, NW = t["vm_nphase"], t["vm_warps"]
+    PW = C // NPH
+    wsp = t["vm_warp_seg_ptr"]
+    for ti in range(t["vm_ntile"]):
+        rbase = t["vm_tile_rec_ptr"][ti]
+        tile_seg0 = wsp[ti * NPH * NW]
+        for w in range(NW):
+            acc = np.zeros((2, B, 3, 4))
+            bone = [None, None]
+            prev = None
+            for ph in range(NPH):
+                for sg in range(wsp[(ti * NPH + ph) * NW + w], wsp[(ti * NPH + ph) * NW + w + 1]):
+                    lx, ly, first, cnt, fx, fy, mode, nxt = (int(x) for x in seg[sg])
+                    if prev is not None:
+                        assert prev == sg - tile_seg0, "segment links do not follow the warp's processing order"
+                    prev = nxt if nxt >= 0 else None
+                    if lx >= 0:
+                        assert not acc[0].any(), "slot X reloaded with an unflushed accumulator"
+                        bone[0] = lx
+                    if ly >= 0:
+                        assert not acc[1].any(), "slot Y reloaded with an unflushed accumulator"
+                        bone[1] = ly
+                    for it in range(rbase + first, rbase + first + cnt):
+                        r = rec[it]
+                        wX, wY = r[0], r[1]
+                        lv = int(t["vm_rec"][it, 2].view(np.int32)) // 3
+                        assert 0 <= lv < PW
+                        v = ti * C + ph * PW + lv
+                        seen[v] += 1
+                        g = gv[:, v]
+                        S_ = r[6:6 + 3 * nB].reshape(nB, 3)[:nb]
+                        vs = r[3:6][None] + beta @ S_
+                        g_trans += g
+                        u = np.zeros((B, 3))
+                        for s_, wgt in ((0, wX), (1, wY)):
+                            if mode == 1 and s_ == 1:
+                                assert wgt == 0.0
+                                continue
+                            if wgt == 0.0:
+                                continue
+                            wg = wgt * g
+                            acc[s_][:, :, :3] += wg[:, :, None] * vs[:, None, :]
+                            acc[s_][:, :, 3] += wg
+                            u += np.einsum("bki,bk->bi", GR[:, bone[s_]], wg)
+                        g_beta += u @ S_.T
+                    for s_, fl in ((0, fx), (1, fy)):
+                        if fl >= 0:
+                            assert t["vm_slot_bone"][fl] == bone[s_], "flush slot belongs to another bone"
+                            slots[fl] = acc[s_]
+                            written[fl] += 1
+                            acc[s_] = 0.0
+            assert prev is None
+            assert not acc.any(), "a warp share ended with an unflushed accumulator"
+    assert (written == 1).all() and (seen == 1).all()
+    gA = np.zeros((B, J, 3, 4))
+    for k in range(J):
+        for si in range(t["vm_sb_ptr"][k], t["vm_sb_ptr"][k + 1]):
+            gA[:, k] += slots[si]
+    return gA, g_beta, g_trans
+
+
+def fast_backward(t, beta, theta, trans, ls, bt, propagate, static, fw, g_verts, g_joints, g_Rs=None, rotmat=False,
+                  vertex_major=False):
     """Item-major backward of the fused path (what skin_bwd + pose_bwd compute)."""
     B = theta.shape[0]
     V, J, nB = t["V"], t["J"], t["nB"]
@@ -154,6 +232,8 @@ def fast_backward(t, beta, theta, trans, ls, bt, propagate, static, fw, g_verts,
     for k in range(J):
         for si in range(t["sb_ptr"][k], t["sb_ptr"][k + 1]):
             gA[:, k] += slots[:, si]
+    if vertex_major:
+        gA, g_beta, g_trans = skin_backward_vm(t, beta, f["GR"], gv)
     g_newJ = None
     if static:
         g_newJ = g_joints

@@ -85,11 +85,62 @@ SYNTH_SPECS = {
 }
 
 
+def padded_rig(base, nB=None, J=None, seed=13):
+    """Stand-ins for the two BASELINE rigs whose pickles are missing:
+    ``nB``: the base rig's geometry with its shape space padded to ``nB`` directions -- random directions made
+    orthogonal to each other, scaled to the abs-max of the rig's own shapedirs (config 4: SMIL_OmniAnt has nB = 13);
+    ``J``: extra LEAF joints hung on random existing joints, no vertex bound to them (config 3: the Falkner mouse has
+    J = 40, 9 more than the rig present); scaledirs / transdirs are padded alike."""
+    from oracle.smal_oracle import load_model_dict
+
+    dd = dict(load_model_dict(REAL_RIGS[base]))
+    rs = np.random.RandomState(seed)
+    sd = np.asarray(dd["shapedirs"], dtype=np.float64)            # (V, 3, nB0)
+    V, _, nB0 = sd.shape
+    J0 = np.asarray(dd["kintree_table"]).shape[1]
+    if nB is not None and nB > nB0:
+        extra = rs.standard_normal((3 * V, nB - nB0))
+        q, _r = np.linalg.qr(extra)
+        q = q / np.abs(q).max(axis=0, keepdims=True) * np.abs(sd).max()
+        dd["shapedirs"] = np.concatenate([sd, q.reshape(V, 3, nB - nB0)], axis=2)
+        for k in ("scaledirs", "transdirs"):
+            if k in dd:
+                a = np.asarray(dd[k], dtype=np.float64)           # (nB0, J, 3)
+                dd[k] = np.concatenate([a, rs.normal(0, np.abs(a).std() + 1e-3, (nB - nB0,) + a.shape[1:])], axis=0)
+    if J is not None and J > J0:
+        add = J - J0
+        kt = np.asarray(dd["kintree_table"]).astype(np.int64)
+        par = list(kt[0])
+        for _ in range(add):
+            par.append(int(rs.randint(0, J0)))
+        dd["kintree_table"] = np.stack([np.asarray(par), np.arange(J)]).astype(np.int32)
+        dd["weights"] = np.concatenate([np.asarray(dd["weights"]), np.zeros((V, add), np.float32)], axis=1)
+        jr = np.asarray(dd["J_regressor"])
+        jr = jr if jr.shape[0] == J0 else jr.T                      # (J0, V)
+        dd["J_regressor"] = np.concatenate([jr, np.zeros((add, V), jr.dtype)], axis=0)
+        Jl = np.asarray(dd["J"], dtype=np.float64)
+        dd["J"] = np.concatenate([Jl, Jl[np.asarray(par[J0:])] + rs.normal(0, 0.05, (add, 3))], axis=0)
+        dd["J_names"] = list(dd["J_names"]) + ["pad%d" % i for i in range(add)]
+        for k in ("scaledirs", "transdirs"):
+            if k in dd:
+                a = np.asarray(dd[k], dtype=np.float64)
+                dd[k] = np.concatenate([a, np.zeros((a.shape[0], add, 3))], axis=1)
+    return dd
+
+
+PADDED_SPECS = {
+    "stick13": dict(base="stick", nB=13),    # config 4 stand-in for SMIL_OmniAnt (J = 55, nB = 13)
+    "mouse40": dict(base="mouse", J=40),     # config 3 stand-in for the Falkner mouse (J = 40)
+}
+
+
 def get_rig(name):
     if name in REAL_RIGS:
         from oracle.smal_oracle import load_model_dict
 
         return load_model_dict(REAL_RIGS[name])
+    if name in PADDED_SPECS:
+        return padded_rig(**PADDED_SPECS[name])
     return synthetic_rig(**SYNTH_SPECS[name])
 
 
@@ -180,6 +231,14 @@ CASES = [
     _c("syn_chain", "syn_chain", 4, dict(with_scale=True, with_trans_off=True), dict(propagate_scaling=True),
        up_all=True),
     _c("syn_j35_legacy", "syn_j35", 2, dict(), cfg=dict(ignore_hardcoded_body=False), stride=8),
+    # odd batches (sample-pair tails), betas_trans without log-scales on the fused backward
+    _c("stick_odd5", "stick", 5, stride=8),
+    _c("stick_btrans", "stick", 5, dict(with_trans_off=True), stride=8),
+    _c("mouse_odd7", "mouse", 7, dict(with_trans_off=True), stride=16),
+    # stand-ins for the missing BASELINE rigs: nB = 13 (OmniAnt), J = 40 (Falkner mouse)
+    _c("stick13_base", "stick13", 6, stride=8),
+    _c("stick13_full", "stick13", 3, dict(with_scale=True, with_trans_off=True), dict(propagate_scaling=True), stride=8),
+    _c("mouse40_base", "mouse40", 3, dict(with_trans_off=True), stride=16),
 ]
 CASE_BY_NAME = {c["name"]: c for c in CASES}
 
@@ -228,6 +287,8 @@ LOSS_SCENES = {
     "mv_b64_v5_j55": (64, 5, 55, 7, False),
     "mv_b5_v3_j11_shared": (5, 3, 11, 7, True),
     "mv_b3_v18_j40_shared": (3, 18, 40, 7, True),
+    "mv_b2_v1_j55_shared": (2, 1, 55, 7, True),
+    "mv_b64_v5_j55_shared": (64, 5, 55, 7, True),
 }
 
 

@@ -49,6 +49,12 @@ def test_fast_path_matches_oracle(rig, B, propagate, nb_used):
     for k in ("beta", "theta", "trans", "betas_logscale", "betas_trans"):
         ref = tt[k].grad.numpy() if tt[k].grad is not None else np.zeros_like(a[k])
         assert rel(g[k], ref) < 5e-6, (k, rel(g[k], ref))
+    if t.get("vm_ok"):   # the vertex-major tables (two resident bones per warp) give the same gradients
+        g = E.fast_backward(t, a["beta"], a["theta"], a["trans"], a["betas_logscale"], a["betas_trans"], propagate, static,
+                            fw, up["g_verts"].astype(np.float64), up["g_joints"].astype(np.float64), g_Rs, vertex_major=True)
+        for k in ("beta", "theta", "trans", "betas_logscale", "betas_trans"):
+            ref = tt[k].grad.numpy() if tt[k].grad is not None else np.zeros_like(a[k])
+            assert rel(g[k], ref) < 5e-6, ("vertex-major", k, rel(g[k], ref))
 
 
 def test_rodrigues_backward_at_zero():

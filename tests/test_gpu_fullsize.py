@@ -149,7 +149,7 @@ def test_multiview_training_loss_fullsize(rig, static, nviews, Bs, reps, propaga
     assert abs(loss - ref_loss) <= TOL * abs(ref_loss)
     assert set(g) == set(ref_g)   # a static-joint rig has no beta gradient through its joints (smal_torch.py:257-260)
     for k, v in ref_g.items():
-        assert rel(g[k], v) <= 1e-4, k      # loss gradients: differences of O(1e2)-pixel terms (see test_gpu_losses)
+        assert rel(g[k], v) <= 2e-5, k      # per-frame parameters through SMAL + projection + loss (see test_gpu_losses)
     # k copies of the batch: same loss, 1/k of every per-frame gradient
     loss_k, g_k = _cuda_multiview(model, dd, p, cam, tgt, vis, propagate, with_pca, reps=reps)
     assert abs(loss_k - loss) <= 2e-6 * abs(loss)

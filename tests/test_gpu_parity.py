@@ -32,15 +32,26 @@ def test_parent_indices_bit_exact():
         assert model.faces.dtype == torch.int64
 
 
-@pytest.mark.parametrize("name", ["stick_base", "stick_full", "stick_beta3", "mouse_full", "stick_b1_nobeta"])
-def test_lane_per_sample_forward_variant(name, monkeypatch):
-    """The alternative forward skin pass (SMIL_FWD_V3=1, read at model creation) meets the same bar."""
-    monkeypatch.setenv("SMIL_FWD_V3", "1")
-    try:
-        rows = compare_case(rigs.CASE_BY_NAME[name])
-    finally:
-        monkeypatch.setenv("SMIL_FWD_V3", "0")
-        from tests.common import make_cuda_model
-        make_cuda_model(rigs.CASE_BY_NAME["stick_base"])   # the switch is process-wide: put it back
+VARIANTS = {
+    # per-model tuning switches (SmilTuning, read from SMIL_* at model creation): every kernel variant kept in the
+    # library meets the same bar as the default path
+    "item_major_bwd": {"SMIL_BWD_VM": "0"},
+    "vm_slots_summed": {"SMIL_BWD_ATOMIC": "0"},
+    "vm_slots_gathered": {"SMIL_BWD_ATOMIC": "0", "SMIL_BWD_SLOT_REDUCE": "0"},
+    "pose_samples_per_warp": {"SMIL_POSE_V2": "1"},
+    "pose_general_bwd": {"SMIL_POSE_LEAN": "0"},
+    "item_major_double_buffered": {"SMIL_BWD_VM": "0", "SMIL_BWD_STAGES": "2"},
+    "fwd_topsync_on": {"SMIL_FWD_TOPSYNC": "1"},
+    "fwd_topsync_off": {"SMIL_FWD_TOPSYNC": "0"},
+}
+
+
+@pytest.mark.parametrize("variant", list(VARIANTS))
+@pytest.mark.parametrize("name", ["stick_base", "stick_full", "stick_beta3", "mouse_full", "stick_b1_nobeta", "syn_wide",
+                                  "syn_chain"])
+def test_kernel_variants(name, variant, monkeypatch):
+    for k, v in VARIANTS[variant].items():
+        monkeypatch.setenv(k, v)   # per MODEL (the drop-in builds a fresh model per case), nothing process-wide
+    rows = compare_case(rigs.CASE_BY_NAME[name])
     bad = [(n, e, g) for n, e, g in rows if not (e <= TOL) or (g is not None and not (g <= 2 * TOL))]
     assert not bad, "tolerance %g exceeded: %s" % (TOL, bad)

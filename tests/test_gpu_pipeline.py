@@ -30,10 +30,24 @@ def test_host_pipeline_matches_eager():
         inp = rigs.make_inputs(dd, B, seed=100 + i)
         batches.append({k: torch.from_numpy(inp[k]).pin_memory() for k in ("beta", "theta", "trans")})
     got = []
-    for b in batches:
-        done = pipe.submit(b["beta"], b["theta"], b["trans"])
-        if done is not None:
-            got.append({k: v.clone() for k, v in done.items()})
+    # a slow consumer: the previous round's dict is read only AFTER the following submit has queued its copies and a
+    # long GPU operation has run (a slot must never write into the host set it has just handed out)
+    pending = None
+    big = torch.randn(4096, 4096, device=dev)
+    bufs = [pipe.new_input() for _ in range(2)]
+    for i, b in enumerate(batches):
+        if i % 2 == 0:
+            done = pipe.submit(b["beta"], b["theta"], b["trans"])
+        else:   # the packed route: one host->device copy
+            flat, (hb, ht, htr) = bufs[(i // 2) % 2]
+            hb.copy_(b["beta"]); ht.copy_(b["theta"]); htr.copy_(b["trans"])
+            done = pipe.submit_packed(flat)
+        if pending is not None:
+            (big @ big).sum().item()
+            got.append({k: v.clone() for k, v in pending.items()})
+        pending = done
+    if pending is not None:
+        got.append({k: v.clone() for k, v in pending.items()})
     got += [{k: v.clone() for k, v in d.items()} for d in pipe.drain()]
     assert len(got) == len(batches)
     for b, g in zip(batches, got):
@@ -41,4 +55,5 @@ def test_host_pipeline_matches_eager():
         verts, joints, _, _ = model(t["beta"], t["theta"], trans=t["trans"])
         gb, gt, gtr = torch.autograd.grad([verts, joints], [t["beta"], t["theta"], t["trans"]], [gv, gj])
         for name, ref in (("grad_beta", gb), ("grad_theta", gt), ("grad_trans", gtr), ("joints", joints.detach())):
-            assert torch.equal(g[name], ref.cpu()), name
+            # same kernels, same inputs: equal up to the summation order of the backward's vector reductions
+            assert torch.allclose(g[name], ref.cpu(), rtol=2e-6, atol=2e-6 * float(ref.abs().max())), name

@@ -10,7 +10,8 @@ or, for the single-GPU line, ``python tools_gpu/fitter_multigpu.py``.
 Every frame's parameters and targets are generated from the GLOBAL frame index, so every world size solves the same
 problem.  After the timed region rank 0 re-evaluates ALL frames alone (8192-frame chunks, gradients accumulated) and
 reports how far the all-reduced shared gradients and the loss of the sharded run are from that single-process result.
-OmniAnt's pickle is not in the repository: the STICK rig stands in (J = 55, nB = 5).
+OmniAnt's pickle is not in the repository: the default rig is its stand-in "stick13" (STICK
+geometry, J = 55, shape space padded to nB = 13 by tests/rigs.py::padded_rig).
 Prints one JSON line on rank 0."""
 import argparse
 import json
@@ -47,21 +48,13 @@ def frame_block(lo, hi, J, block=4096):
     return {k: np.concatenate(v) for k, v in out.items()}
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--frames", type=int, default=65536)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--graph", type=int, default=1, help="1: replay the local part from a CUDA graph")
-    ap.add_argument("--get-skin", type=int, default=1, help="1: pose the mesh too, as fitter.py:262 does")
-    args = ap.parse_args()
-    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
-    local = int(os.environ.get("LOCAL_RANK", 0))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    smilify_b200.configure(rigs.REAL_RIGS["stick"])
+def run_fitter(frames, steps, warmup, rank, world, dev, rig="stick13", graph=True, get_skin=True, check=True):
+    """One frame-sharded SMALFitter-style step timed on this rank's device (the process group, if any, is initialised
+    by the caller).  Returns the result dict on rank 0 (None elsewhere).  ``rig``: "stick13" is the OmniAnt stand-in of
+    SURVEY.md section 8(d) config 4 (STICK geometry, shape space padded to nB = 13)."""
+    from tests.common import rig_file
+
+    smilify_b200.configure(rig_file(rig))
     model = SMAL(dev)
     J, nB = model._tables["J"], model.num_betas
     # the fitter's default camera, look_at_view_transform(2.7, 0, 0) (p3d_renderer.py:34-37)
@@ -75,63 +68,99 @@ def main():
         sp = dict(betas=torch.from_numpy(rs.normal(0, 0.5, (nB,)).astype(np.float32)).to(dev).requires_grad_(True),
                   fov=torch.tensor([60.0], device=dev, requires_grad=True))
         fn = FS.smal_joint_loss_fn(model, R, T, torch.from_numpy(d["target"]).to(dev), torch.from_numpy(d["vis"]).to(dev),
-                                   get_skin=bool(args.get_skin))
+                                   get_skin=bool(get_skin))
         return fp, sp, fn
 
-    lo, hi = FS.shard_range(args.frames, rank, world)
+    lo, hi = FS.shard_range(frames, rank, world)
     fp, sp, fn = build(lo, hi)
     c0 = _lib.launch_count()
-    FS.ShardedFitterStep(fp, sp, fn, args.frames)()          # one eager step: counts the kernels a step launches
+    FS.ShardedFitterStep(fp, sp, fn, frames)()          # one eager step: counts the kernels a step launches
     per_step = _lib.launch_count() - c0
-    step = (FS.GraphedShardedFitterStep if args.graph else FS.ShardedFitterStep)(fp, sp, fn, args.frames)
+    step = (FS.GraphedShardedFitterStep if graph else FS.ShardedFitterStep)(fp, sp, fn, frames)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         loss = step()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         loss = step()
     e1.record()
     barrier()
-    ms = e0.elapsed_time(e1) / args.steps
-    launches = per_step * args.steps   # a graph replay launches the same kernels the eager step does
+    ms = e0.elapsed_time(e1) / steps
+    # the collective alone (same packed buffer size), device-timed
+    ar_us = None
     if world > 1:
-        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        buf = torch.zeros(nB + 2, device=dev)
+        for _ in range(5):
+            dist.all_reduce(buf)
+        torch.cuda.synchronize()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(20):
+            dist.all_reduce(buf)
+        a1.record()
+        torch.cuda.synchronize()
+        ar_us = a0.elapsed_time(a1) / 20 * 1e3
+        t = torch.tensor([ms, ar_us], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        ms, ar_us = float(t[0].item()), float(t[1].item())
     g_sharded = {k: v.grad.detach().clone() for k, v in sp.items()}
     loss_sharded = float(loss)
 
     # single-process run over ALL frames on rank 0 (chunked accumulation): what the sharded gradients must equal
-    check = None
-    if rank == 0 and world > 1:
+    chk = None
+    if rank == 0 and world > 1 and check:
         acc = {k: torch.zeros_like(v) for k, v in sp.items()}
         tot = 0.0
-        for c0 in range(0, args.frames, 8192):
-            fpc, spc, fnc = build(c0, min(args.frames, c0 + 8192))
-            part = fnc(fpc, spc) / args.frames
+        for c0 in range(0, frames, 8192):
+            fpc, spc, fnc = build(c0, min(frames, c0 + 8192))
+            part = fnc(fpc, spc) / frames
             part.backward()
             tot += float(part.detach())
             for k in acc:
                 acc[k] += spc[k].grad
-        check = {k: float((g_sharded[k] - acc[k]).abs().max() / acc[k].abs().max().clamp_min(1e-30)) for k in acc}
-        check["loss"] = abs(loss_sharded - tot) / abs(tot)
+        chk = {k: float((g_sharded[k] - acc[k]).abs().max() / acc[k].abs().max().clamp_min(1e-30)) for k in acc}
+        chk["loss"] = abs(loss_sharded - tot) / abs(tot)
+    if rank != 0:
+        return None
+    in_graph = bool(getattr(step, "collective_in_graph", False))
+    return {
+        "metric": "SMALFitter-style frames/s (SMAL fwd+bwd + joint reprojection loss, shared betas/fov)",
+        "value": frames / ms * 1e3, "frames_per_s": frames / ms * 1e3, "unit": "frames/s", "n_gpus": world, "ms_per_step": ms,
+        "steps": steps, "warmup": warmup, "frames_total": frames, "frames_per_gpu": hi - lo, "scaling": "strong",
+        "collective": "1 all_reduce(SUM) per step, %d bytes (g_betas, g_fov, loss)" % step.collective_bytes,
+        "collective_bytes": step.collective_bytes, "allreduce_us": ar_us,
+        "backend": "nccl" if world > 1 else "none", "rig": "%s (J = %d, nB = %d)" % (rig, J, nB), "get_skin": bool(get_skin),
+        "launch": ("cuda-graph replay incl. the NCCL all_reduce" if in_graph else "cuda-graph replay + eager all_reduce")
+                  if graph else "eager",
+        "gpu_launches": per_step * steps, "loss": loss_sharded, "sharded_vs_single_rel_err": chk}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--frames", type=int, default=65536)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--graph", type=int, default=1, help="1: replay the step from a CUDA graph")
+    ap.add_argument("--get-skin", type=int, default=1, help="1: pose the mesh too, as fitter.py:262 does")
+    ap.add_argument("--rig", default="stick13", help="stick13 = OmniAnt stand-in (nB padded to 13), stick, mouse40, ...")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    out = run_fitter(args.frames, args.steps, args.warmup, rank, world, dev, rig=args.rig, graph=bool(args.graph),
+                     get_skin=bool(args.get_skin))
     if rank == 0:
-        print(json.dumps({
-            "metric": "SMALFitter-style frames/s (SMAL fwd+bwd + joint reprojection loss, shared betas/fov)",
-            "value": args.frames / ms * 1e3, "unit": "frames/s", "n_gpus": world, "ms_per_step": ms, "steps": args.steps,
-            "warmup": args.warmup, "frames_total": args.frames, "frames_per_gpu": hi - lo, "scaling": "strong",
-            "collective": "1 all_reduce(SUM) per step, %d bytes (g_betas, g_fov, loss)" % step.collective_bytes,
-            "backend": "nccl" if world > 1 else "none", "rig": "stick (OmniAnt stand-in)", "get_skin": bool(args.get_skin),
-            "launch": "cuda-graph replay + eager all_reduce" if args.graph else "eager",
-            "gpu_launches": launches, "loss": loss_sharded,
-            "sharded_vs_single_process_rel_err": check}))
+        print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
