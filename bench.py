@@ -172,8 +172,9 @@ def torch_gpu_baseline(rig_path, B, dev, seed=0, warmup=3, iters=10):
     gv, gj = torch.from_numpy(x["g_verts"]).to(dev), torch.from_numpy(x["g_joints"]).to(dev)
 
     def step():
-        verts, joints, _Rs, _vs = SO.smal_forward(m, beta, theta, trans)
-        torch.autograd.backward([verts, joints], [gv, gj])
+        with torch.device(dev):   # the oracle's helper tensors (eye, zeros, ...) are created on the default device
+            verts, joints, _Rs, _vs = SO.smal_forward(m, beta, theta, trans)
+            torch.autograd.backward([verts, joints], [gv, gj])
         beta.grad = theta.grad = trans.grad = None
 
     for _ in range(warmup):

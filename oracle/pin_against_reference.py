@@ -658,6 +658,49 @@ def pin_triangulation(ref, report):
     np.savez_compressed(os.path.join(rigs.GOLDEN, "triangulation_pins.npz"), **flat)
 
 
+def pin_caller(ref, report):
+    """Row 13: the UNMODIFIED ``fitter_3d/trainer.py::SMAL3DFitter`` driven over the reference's own ``SMAL`` on the CPU
+    (import-time-only names stubbed, see tests/test_gpu_reference_caller.py); its outputs and parameter gradients are
+    frozen so that the GPU box -- which has no reference tree -- can check the drop-in against the real caller."""
+    import importlib
+
+    from tests import test_gpu_reference_caller as T
+
+    saved_modules, saved_path, saved_cwd = dict(sys.modules), list(sys.path), os.getcwd()
+    try:
+        for name in T.STUBS:
+            sys.modules[name] = T._Anything(name)
+        sys.modules["nibabel.eulerangles"].euler2angle_axis = T._euler2angle_axis
+        sys.modules["nibabel"].eulerangles = sys.modules["nibabel.eulerangles"]
+        if ref not in sys.path:
+            sys.path.insert(0, ref)
+        os.chdir(ref)
+        T._purge()
+        install_config_shim(ref, os.path.join(ref, "3D_model_prep", "SMILy_STICK.pkl"))
+        trainer = importlib.import_module("fitter_3d.trainer")
+        assert trainer.SMAL.__module__ == "smal_model.smal_torch"
+        vals, gv, gj = T.caller_inputs()
+        B = gv.shape[0]
+        fit = trainer.SMAL3DFitter(batch_size=B, device="cpu")
+        with torch.no_grad():
+            for k, v in vals.items():
+                getattr(fit, k).copy_(torch.from_numpy(v).float())
+        verts, joints = fit.forward(return_joints=True)
+        ((verts * torch.from_numpy(gv)).sum() + (joints * torch.from_numpy(gj)).sum()).backward()
+        out = {"out_verts": verts.detach().numpy(), "out_joints": joints.detach().numpy()}
+        out.update({"grad_" + k: getattr(fit, k).grad.numpy() for k in vals})
+    finally:
+        os.chdir(saved_cwd)
+        sys.path[:] = saved_path
+        for k in list(sys.modules):
+            if k not in saved_modules:
+                del sys.modules[k]
+        sys.modules.update(saved_modules)
+    np.savez_compressed(os.path.join(rigs.GOLDEN, "caller_smal3dfitter.npz"), **out)
+    report["caller_smal3dfitter"] = {k: list(v.shape) for k, v in out.items()}
+    print("froze SMAL3DFitter.forward over the reference SMAL:", {k: v.shape for k, v in out.items()})
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ref", default="/root/reference")
@@ -671,6 +714,7 @@ def main():
     pin_losses(a.ref, report)
     pin_loss_chains(a.ref, report)
     pin_triangulation(a.ref, report)
+    pin_caller(a.ref, report)
     with open(os.path.join(rigs.GOLDEN, "PIN_REPORT.json"), "w") as fh:
         json.dump(report, fh, indent=1, sort_keys=True)
     print("pinned:", json.dumps(report["worst"]))

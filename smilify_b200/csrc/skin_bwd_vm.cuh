@@ -21,6 +21,7 @@
 
 namespace smil {
 
+constexpr int VM_WARPS = 4, VM_PHASES = 1;   // what the kernel is compiled for (the packer can emit other splits)
 constexpr int VM_MODE_PACKED = 0, VM_MODE_X = 1;   // == packer.VM_MODE_* (Y-only stretches are packed with w_X = 0)
 
 struct SkinBwdVmArgs {
@@ -54,7 +55,10 @@ __host__ inline size_t skin_bwd_vm_smem_bytes(int chunk, int nphase, int nwarps,
 
 template <int NBT>
 __global__ void __launch_bounds__(128) skin_bwd_vm_kernel(DevModel m, SkinBwdVmArgs a) {
-  const int NW = m.vm_warps;   // warps per CTA (blockDim.x / 32): 4 share a tile, 1 = every warp owns its own small tile
+  // Warps per CTA that share a tile, and phases (sub-ranges of a tile with their own row buffer) are COMPILE-TIME here:
+  // 1 / 2 warps per tile and 2 / 3 phases were measured slower on B200 (107-135 us and 116-126 us
+  // against 95-97 us), and as run-time values they cost the default configuration 5 us.
+  constexpr int NW = VM_WARPS;
   static_assert(SKIN_BWD_STREAMS == 2, "the vertex-major pass is written for 16 samples x 2 vertex streams per warp");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int RECF = (6 + 3 * NBT + 3) & ~3;
@@ -62,7 +66,8 @@ __global__ void __launch_bounds__(128) skin_bwd_vm_kernel(DevModel m, SkinBwdVmA
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane & (SKIN_BWD_G - 1), st = lane / SKIN_BWD_G;
   const int ti = blockIdx.x;
-  const int C = m.vm_chunk, V = m.V, NPH = m.vm_nphase;
+  constexpr int NPH = VM_PHASES;
+  const int C = m.vm_chunk, V = m.V;
   const int PW = C / NPH;                       // vertices per phase (a multiple of 4)
   const int RF = skin_bwd_row_floats(PW);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);  // [NPH <= 4]
@@ -84,9 +89,9 @@ __global__ void __launch_bounds__(128) skin_bwd_vm_kernel(DevModel m, SkinBwdVmA
   {   // tile constants -> shared memory (once per CTA, reused by every sample group)
     const float4* src = reinterpret_cast<const float4*>(m.vm_rec + (long long)rec_base * RECF);
     float4* dst = reinterpret_cast<float4*>(sRec);
-    for (int i = tid; i < rec_cnt * NQ; i += blockDim.x) dst[i] = src[i];
+    for (int i = tid; i < rec_cnt * NQ; i += 32 * NW) dst[i] = src[i];
     const int4* ssrc = m.vm_seg + 2ll * seg_base;
-    for (int i = tid; i < 2 * seg_cnt; i += blockDim.x) {
+    for (int i = tid; i < 2 * seg_cnt; i += 32 * NW) {
       int4 d = ssrc[i];
       if ((i & 1) == 0) {   // bones -> float offsets into a pair block
         d.x = d.x >= 0 ? d.x * PPB : -1;
@@ -366,6 +371,7 @@ __global__ void __launch_bounds__(128) skin_bwd_vm_kernel(DevModel m, SkinBwdVmA
           for (int e = lane & 7; e < ne; e += 8) {
             const int src = (e < a.nb) ? e : NBT + (e - a.nb);
             float sum = 0.f;
+#pragma unroll
             for (int wv = 0; wv < NW; ++wv) sum += sRed[((size_t)wv * SKIN_BWD_G + gg) * (NBT + 4) + src];
             if (a.gbt_sum) atomicAdd(a.gbt_sum + (long long)(b0 + gg) * ne + e, sum);
             else a.gbt_part[((long long)(b0 + gg) * m.vm_ntile + ti) * ne + e] = sum;

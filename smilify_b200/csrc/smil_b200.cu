@@ -372,13 +372,24 @@ int smil_profile_collect(SmilProfileEntry* out, int max_entries, int* num_entrie
   return SMIL_OK;
 }
 
+namespace {
+struct DeviceGuard {   // the caller's current CUDA device is restored on every exit path
+  int prev = -1;
+  explicit DeviceGuard(int dev) { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; cudaSetDevice(dev); }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+}  // namespace
+
 int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   if (!s || !out) return fail(SMIL_EINVAL, "smil_model_create: NULL argument");
   *out = nullptr;
   if (s->num_joints <= 0) return fail(SMIL_EINVAL, "num_joints must be positive");
   if (!s->parents || !s->order || !s->level_ptr || !s->child_ptr)
     return fail(SMIL_EINVAL, "tree tables (parents/order/level_ptr/child_ptr) are required");
-  SMIL_CUDA(cudaSetDevice(s->device));
+  int ndev = 0;
+  SMIL_CUDA(cudaGetDeviceCount(&ndev));
+  if (s->device < 0 || s->device >= ndev) return fail(SMIL_EINVAL, "device %d outside [0,%d)", s->device, ndev);
+  DeviceGuard guard(s->device);
   SmilModel* M = new (std::nothrow) SmilModel();
   if (!M) return fail(SMIL_ENOMEM, "out of host memory");
   DevModel& d = M->d;
@@ -486,8 +497,7 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
   ap.add(s->sb_ptr, d.num_units ? J + 1 : 0, &d.sb_ptr);
   ap.add(s->unit_slot, (size_t)d.num_units, &d.unit_slot);
   d.vm_ok = s->vm_ok && d.fused_ok && d.K <= 2 && s->vm_rec && s->vm_seg && s->vm_tile_rec_ptr && s->vm_warp_seg_ptr &&
-            s->vm_sb_ptr && s->vm_slot_bone && s->vm_ntile > 0 && s->vm_recf == vm_rec_floats(std::max(nbt_of(d.nB), 1)) && (s->vm_warps == 1 || s->vm_warps == 2 || s->vm_warps == 4) &&
-            s->vm_nphase >= 1 && s->vm_nphase <= 4 && s->vm_chunk % (4 * s->vm_nphase) == 0;
+            s->vm_sb_ptr && s->vm_slot_bone && s->vm_ntile > 0 && s->vm_recf == vm_rec_floats(std::max(nbt_of(d.nB), 1)) && s->vm_warps == VM_WARPS && s->vm_nphase == VM_PHASES && s->vm_chunk % (4 * s->vm_nphase) == 0;
   d.vm_warps = s->vm_warps; d.vm_nphase = s->vm_nphase; d.vm_chunk = s->vm_chunk; d.vm_ntile = s->vm_ntile; d.vm_recf = s->vm_recf; d.vm_nslots = s->vm_nslots;
   d.h_vm_max_tile_recs = s->vm_max_tile_recs; d.h_vm_max_tile_segs = s->vm_max_tile_segs;
   if (d.vm_ok) {
@@ -524,7 +534,7 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
 
 void smil_model_destroy(SmilModel* model) {
   if (!model) return;
-  if (model->d.arena) cudaFree(model->d.arena);
+  if (model->d.arena) cudaFree(model->d.arena);   // cudaFree takes the pointer's own device: no device switch needed
   delete model;
 }
 

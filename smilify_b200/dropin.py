@@ -20,8 +20,21 @@ def install(force: bool = False):
         raise RuntimeError("install() must run before smal_fitter / fitter_3d are imported (or pass force=True)")
     pkg = sys.modules.get("smal_model")
     if pkg is None:
+        # keep the REAL package importable for everything that is not replaced (smal_model.smal_basics, ...): a bare
+        # namespace module only when the reference is not on sys.path at all
+        import importlib.util
+        import os
+
         pkg = types.ModuleType("smal_model")
         pkg.__path__ = []
+        for entry in sys.path:
+            cand = os.path.join(entry or ".", "smal_model")
+            if os.path.isdir(cand) and os.path.exists(os.path.join(cand, "smal_torch.py")):
+                pkg.__path__.append(cand)
+                init = os.path.join(cand, "__init__.py")
+                if os.path.exists(init):
+                    pkg.__file__ = init
+                break
         sys.modules["smal_model"] = pkg
     smal_torch.__smilify_b200__ = True
     batch_lbs.__smilify_b200__ = True

@@ -183,7 +183,10 @@ class SmalFunction(torch.autograd.Function):
             g = g.to(torch.float32)
             if tuple(g.shape) != shape:
                 g = g.expand(shape)
-            return g.contiguous()
+            g = g.contiguous()
+            if g.data_ptr() % 16:   # a contiguous VIEW with a storage offset (narrow() of a cat / stack gradient): the TMA
+                g = g.clone()       # bulk copies of the fused backward need 16-byte aligned rows
+            return g
 
         with torch.cuda.device(dev):
             g = _lib.SmilBwdArgs()

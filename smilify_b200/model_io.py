@@ -32,11 +32,19 @@ class _ChArray:
     def __array__(self, dtype=None, copy=None):
         return np.asarray(self.payload, dtype=dtype)
 
+    @property
+    def r(self):      # chumpy's accessor for the underlying data (smal_torch.py:55-58)
+        return self.payload
+
+    @property
+    def data(self):   # the attribute name the reference's ChumpyWrapper uses
+        return self.payload
+
 
 class _RigUnpickler(pickle.Unpickler):
     def find_class(self, module, name):
         if module.startswith("chumpy"):
-            return _ChArray
+            return getattr(type(self), "ChumpyWrapper", _ChArray)
         return super().find_class(module, name)
 
 
@@ -65,7 +73,58 @@ def load_rig(path) -> dict:
     for k in REQUIRED_KEYS:
         if k not in dd:
             raise KeyError("rig file %s lacks key %r" % (path, k))
+    validate_rig(dd, path)
     return dd
+
+
+def validate_rig(dd: dict, path="<rig>") -> None:
+    """Schema check of an SMPL-style rig (the keys ``SMAL.__init__`` reads, smal_torch.py:92-196, written by
+    3D_model_prep/SMPL_exporter.py): shapes that must agree, a kinematic table whose parents precede their children
+    (the chain indexes a growing list with it, batch_lbs.py:157,179), finite numbers, skinning weights that sum to one.
+    Raises ValueError naming the file and the offending key."""
+
+    def bad(msg):
+        raise ValueError("rig file %s: %s" % (path, msg))
+
+    vt = np.asarray(dd["v_template"])
+    if vt.ndim != 2 or vt.shape[1] != 3 or vt.shape[0] == 0:
+        bad("v_template has shape %s, expected (V, 3)" % (vt.shape,))
+    V = vt.shape[0]
+    sd = np.asarray(dd["shapedirs"])
+    if sd.ndim != 3 or sd.shape[:2] != (V, 3):
+        bad("shapedirs has shape %s, expected (%d, 3, nB)" % (sd.shape, V))
+    kt = np.asarray(dd["kintree_table"])
+    if kt.ndim != 2 or kt.shape[0] < 1:
+        bad("kintree_table has shape %s, expected (2, J)" % (kt.shape,))
+    J = kt.shape[1]
+    par = kt[0].astype(np.int64)
+    for i in range(1, J):
+        if not (0 <= par[i] < i):
+            bad("kintree_table[0][%d] = %d: a parent must precede its child (0 <= parent < index)" % (i, par[i]))
+    W = np.asarray(dd["weights"])
+    if W.shape != (V, J):
+        bad("weights has shape %s, expected (%d, %d)" % (W.shape, V, J))
+    jr = np.asarray(_plain(dd["J_regressor"]))
+    if jr.shape != (J, V):
+        bad("J_regressor has shape %s, expected (%d, %d)" % (jr.shape, J, V))
+    pd = np.asarray(dd["posedirs"])
+    if pd.size and (pd.ndim != 3 or pd.shape[:2] != (V, 3) or pd.shape[2] != 9 * (J - 1)):
+        bad("posedirs has shape %s, expected (%d, 3, %d) or empty" % (pd.shape, V, 9 * (J - 1)))
+    f = np.asarray(dd["f"])
+    if f.ndim != 2 or f.shape[1] != 3 or (f.size and (f.min() < 0 or f.max() >= V)):
+        bad("f (faces) has shape %s / indices outside [0, %d)" % (f.shape, V))
+    if bool(dd.get("static_joint_locs", False)):
+        if "J" not in dd or np.asarray(dd["J"]).shape != (J, 3):
+            bad("static_joint_locs is set but J is missing or not (%d, 3)" % J)
+    for k in ("scaledirs", "transdirs"):
+        if k in dd and np.asarray(dd[k]).shape[1:] != (J, 3):
+            bad("%s has shape %s, expected (C, %d, 3)" % (k, np.asarray(dd[k]).shape, J))
+    for k, a in (("v_template", vt), ("shapedirs", sd), ("weights", W), ("J_regressor", jr)):
+        if not np.isfinite(a).all():
+            bad("%s holds non-finite values" % k)
+    rows = W.sum(axis=1)
+    if W.min() < 0 or np.abs(rows - 1.0).max() > 1e-3:
+        bad("weights: rows must be non-negative and sum to 1 (row sums in [%g, %g])" % (rows.min(), rows.max()))
 
 
 def reference_layout(dd: dict, static_joints: bool, shape_family_betas=None) -> dict:

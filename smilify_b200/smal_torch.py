@@ -17,7 +17,7 @@ from . import _lib
 from . import config as _config
 from . import packer
 from .functions import DeviceModel, SmalFunction
-from .model_io import load_rig, reference_layout
+from .model_io import _ChArray, _RigUnpickler, load_rig, reference_layout
 
 # smal_torch.py:353-365 -- legacy 35-joint dog rig: six extra "joints" picked from vertices
 _LEGACY_35_PICKS = (1863, 26, 2124, 150, 3055, 1097)
@@ -26,6 +26,27 @@ _LEGACY_35_PICKS = (1863, 26, 2124, 150, 3055, 1097)
 def load_smal_model(file_path):
     """Same name and contract as the reference helper (smal_torch.py:61-73)."""
     return load_rig(file_path)
+
+
+class CustomUnpickler(_RigUnpickler):
+    """Same name and call pattern as the reference's unpickler for legacy chumpy pickles (smal_torch.py:21-58):
+    ``CustomUnpickler(f).load()`` -- imported by smal_fitter/priors/pose_prior_35.py:8.  Chumpy arrays become inert
+    wrappers with ``.r`` / ``.data`` / ``__array__`` (no chumpy import)."""
+
+    ChumpyWrapper = _ChArray
+
+    def __init__(self, file, encoding="latin1"):
+        super().__init__(file, encoding=encoding)
+
+
+def undo_chumpy(x):
+    """smal_torch.py:78-84: the numeric payload of a chumpy variable, anything else unchanged."""
+    if isinstance(x, np.ndarray):
+        return x
+    try:
+        return x.r
+    except AttributeError:
+        return x
 
 
 class SMAL(nn.Module):
@@ -81,7 +102,7 @@ class SMAL(nn.Module):
         self.J_transformed = None
 
         self._device = device
-        self._tables = packer.pack_model(v_template, lay["shapedirs"], lay["posedirs"], lay["J_regressor"],
+        self._tables = packer.pack_model_cached(v_template, lay["shapedirs"], lay["posedirs"], lay["J_regressor"],
                                          lay["weights"], lay["parents"], lay["J"])
         self._dm = DeviceModel(self._tables, device)  # raises on non-CUDA devices / missing library
 

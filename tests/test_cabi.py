@@ -84,3 +84,89 @@ def test_packer_index_tables_bit_exact():
         pos[t["order"]] = np.arange(len(ref))
         assert sorted(t["order"].tolist()) == list(range(len(ref)))
         assert all(pos[ref[i]] < pos[i] for i in range(1, len(ref)))
+
+
+def test_dropin_reexports_and_real_package_path():
+    """After install(): the names other reference modules import from ``smal_model.smal_torch`` exist
+    (smal_fitter/priors/pose_prior_35.py:8 imports CustomUnpickler), and the REST of the real ``smal_model`` package
+    stays importable when the reference is on sys.path (``smal_model.smal_basics``, needed for ignore_sym=False)."""
+    import io
+    import os
+    import pickle
+    import sys
+
+    import numpy as np
+
+    import smilify_b200
+
+    saved = {k: v for k, v in sys.modules.items() if k.split(".")[0] == "smal_model"}
+    saved_path = list(sys.path)
+    for k in saved:
+        del sys.modules[k]
+    try:
+        ref = "/root/reference"
+        have_ref = os.path.isdir(os.path.join(ref, "smal_model"))
+        if have_ref:
+            sys.path.insert(0, ref)
+        smilify_b200.install(force=True)
+        from smal_model.smal_torch import CustomUnpickler, load_smal_model, undo_chumpy  # noqa: F401
+
+        buf = io.BytesIO()
+        pickle.dump({"a": np.arange(3)}, buf, protocol=2)
+        buf.seek(0)
+        assert np.array_equal(CustomUnpickler(buf).load()["a"], np.arange(3))
+        w = CustomUnpickler.ChumpyWrapper(np.arange(4.0))
+        assert np.array_equal(undo_chumpy(w), np.arange(4.0)) and np.array_equal(np.asarray(w), w.r)
+        assert undo_chumpy(3) == 3
+        if have_ref:
+            from oracle.pin_against_reference import install_config_shim
+
+            saved_cfg = sys.modules.get("config")
+            install_config_shim(ref, os.path.join(ref, "3D_model_prep", "SMILy_STICK.pkl"))   # its default rig is a missing blob
+            try:
+                import smal_model.smal_basics as sb   # not replaced: must resolve to the reference's file
+            finally:
+                if saved_cfg is None:
+                    sys.modules.pop("config", None)
+                else:
+                    sys.modules["config"] = saved_cfg
+            assert sb.__file__.startswith(ref)
+    finally:
+        sys.path[:] = saved_path
+        for k in [k for k in sys.modules if k.split(".")[0] == "smal_model"]:
+            del sys.modules[k]
+        sys.modules.update(saved)
+
+
+def test_rig_schema_validation_and_pack_cache(tmp_path):
+    """(f)3: the loader rejects rigs whose arrays disagree (instead of failing somewhere inside a kernel), and the packed
+    tables survive the flat on-disk cache bit for bit."""
+    import numpy as np
+    import pytest
+
+    from smilify_b200 import model_io, packer
+    from tests import rigs
+
+    dd = rigs.synthetic_rig(**rigs.SYNTH_SPECS["syn_k3"])
+    model_io.validate_rig(dd)
+    for key, mutate, msg in (
+        ("weights", lambda a: a[:, :-1], "weights has shape"),
+        ("kintree_table", lambda a: np.stack([np.r_[a[0][:3], [7], a[0][4:]], a[1]]), "must precede"),
+        ("shapedirs", lambda a: a[:-1], "shapedirs has shape"),
+        ("weights", lambda a: a * 0.5, "sum to 1"),
+        ("v_template", lambda a: np.where(np.arange(a.size).reshape(a.shape) == 5, np.nan, a), "non-finite"),
+    ):
+        broken = dict(dd)
+        broken[key] = mutate(np.asarray(dd[key]).copy())
+        with pytest.raises(ValueError, match=msg):
+            model_io.validate_rig(broken, "broken.pkl")
+    lay = model_io.reference_layout(dd, static_joints=False)
+    args = (lay["v_template"], lay["shapedirs"], lay["posedirs"], lay["J_regressor"], lay["weights"], lay["parents"], lay["J"])
+    first = packer.pack_model_cached(*args, cache_dir=str(tmp_path))
+    again = packer.pack_model_cached(*args, cache_dir=str(tmp_path))     # from the file
+    direct = packer.pack_model(*args)
+    assert len(list(tmp_path.iterdir())) == 1
+    for k, v in direct.items():
+        for other in (first, again):
+            a, b = np.ascontiguousarray(np.asarray(v)), np.ascontiguousarray(np.asarray(other[k]))
+            assert a.shape == b.shape and a.dtype == b.dtype and a.tobytes() == b.tobytes(), k
