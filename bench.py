@@ -140,13 +140,42 @@ class ClockSampler:
         return out
 
 
-def pin_rank_to_cores(local_rank, world):
-    """Disjoint CPU cores per rank (the 8 ranks of a box otherwise share one affinity mask and their copy / launch
-    threads migrate over each other); pinned host buffers are first-touched AFTER this, so they land on the local node."""
+def gpu_local_cores(index):
+    """CPU cores on the NUMA node the GPU hangs off (NVML's ideal affinity), or None."""
     try:
-        cores = sorted(os.sched_getaffinity(0))
-        per = max(1, len(cores) // max(world, 1))
-        mine = cores[local_rank * per:(local_rank + 1) * per] or cores
+        import pynvml
+
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            tok = vis.split(",")[index].strip()
+            h = pynvml.nvmlDeviceGetHandleByIndex(int(tok)) if tok.isdigit() else pynvml.nvmlDeviceGetHandleByUUID(tok)
+        else:
+            h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        return {w * 64 + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1}
+    except Exception:
+        return None
+
+
+def pin_rank_to_cores(local_rank, world):
+    """Disjoint CPU cores per rank, taken from the cores local to the rank's GPU where NVML reports them (the 8 ranks of
+    a box otherwise share one affinity mask, their copy / launch threads migrate over each other and pinned buffers land
+    on the far NUMA node); pinned host buffers are first-touched AFTER this, so they land on the local node."""
+    try:
+        allowed = sorted(os.sched_getaffinity(0))
+        local = [gpu_local_cores(r) for r in range(world)]
+        mine_set = local[local_rank]
+        if mine_set and (set(allowed) & mine_set):
+            # ranks whose GPUs share a node split that node's cores between them
+            sharers = [r for r in range(world) if local[r] == mine_set]
+            cores = sorted(set(allowed) & mine_set)
+            per = max(1, len(cores) // len(sharers))
+            k = sharers.index(local_rank)
+            mine = cores[k * per:(k + 1) * per] or cores
+        else:
+            per = max(1, len(allowed) // max(world, 1))
+            mine = allowed[local_rank * per:(local_rank + 1) * per] or allowed
         os.sched_setaffinity(0, mine)
         return len(mine)
     except (AttributeError, OSError):
@@ -407,6 +436,21 @@ def run_ours(args, rank, world, local_rank):
     e2e_wall = (time.perf_counter() - t0) * 1e3
     barrier()
     e2e_ms = max_over_ranks(e2e_wall)
+    if os.environ.get("SMIL_BENCH_DIAG"):
+        hbuf = torch.empty(max(h2d, d2h), dtype=torch.uint8).pin_memory()
+        dbuf = torch.empty(max(h2d, d2h), dtype=torch.uint8, device=dev)
+        for name, nbytes, to_dev in (("h2d", h2d, True), ("d2h", d2h, False)):
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier(); ev0.record()
+            for _ in range(50):
+                (dbuf[:nbytes].copy_(hbuf[:nbytes], non_blocking=True) if to_dev else hbuf[:nbytes].copy_(dbuf[:nbytes], non_blocking=True))
+            ev1.record(); torch.cuda.synchronize()
+            us = ev0.elapsed_time(ev1) * 1e3 / 50
+            print("[diag] rank %d %s %d B: %.1f us/copy, %.1f GB/s" % (rank, name, nbytes, us, nbytes / us / 1e3), file=sys.stderr, flush=True)
+        for n in (K, 10 * K):
+            barrier(); t1 = time.perf_counter(); e2e_run(n); torch.cuda.synchronize()
+            print("[diag] rank %d e2e %d steps: %.4f ms/step, cores %s" % (rank, n, (time.perf_counter() - t1) * 1e3 / n,
+                                                                            sorted(os.sched_getaffinity(0))), file=sys.stderr, flush=True)
     clocks = sampler.stop() if sampler else None
 
     # --- per-kernel device time (eager, event pair around every launch) -> roofline of the dominant kernel

@@ -53,6 +53,12 @@ def tree_only_model(parents: np.ndarray, device: torch.device) -> DeviceModel:
     return DeviceModel(t, device)
 
 
+def _empty(*size, **kw):
+    """Every device buffer handed to the library (outputs, saved state, scratch) is allocated here, so that
+    tests/test_gpu_guards.py can swap in an allocator with poisoned contents and guard bands."""
+    return torch.empty(*size, **kw)
+
+
 def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
@@ -129,24 +135,24 @@ class SmalFunction(torch.autograd.Function):
                 keep.append(vt)
                 a.v_template = vt.data_ptr()
             opts = dict(device=dev, dtype=torch.float32)
-            joints = torch.empty((B, J, 3), **opts)
-            Jt = torch.empty((B, J, 3), **opts)
+            joints = _empty((B, J, 3), **opts)
+            Jt = _empty((B, J, 3), **opts)
             verts = v_shaped = None
             if not joints_only:
-                verts = torch.empty((B, V, 3), **opts)
-                v_shaped = torch.empty((B, V, 3), **opts)
+                verts = _empty((B, V, 3), **opts)
+                v_shaped = _empty((B, V, 3), **opts)
                 a.verts, a.v_shaped = verts.data_ptr(), v_shaped.data_ptr()
             Rs = None
             if not rotmat:
-                Rs = torch.empty((B, J, 3, 3), **opts)
+                Rs = _empty((B, J, 3, 3), **opts)
                 a.Rs = Rs.data_ptr()
             a.joints, a.J_transformed = joints.data_ptr(), Jt.data_ptr()
-            saved = torch.empty(L.smil_saved_bytes(dm.handle, B, flags), device=dev, dtype=torch.uint8)
+            saved = _empty(L.smil_saved_bytes(dm.handle, B, flags), device=dev, dtype=torch.uint8)
             a.saved, a.saved_bytes = saved.data_ptr(), saved.numel()
             scratch = None
             nscratch = L.smil_fwd_scratch_bytes(dm.handle, C.byref(a))  # 0 on the fused path
             if nscratch:
-                scratch = torch.empty(nscratch, device=dev, dtype=torch.uint8)
+                scratch = _empty(nscratch, device=dev, dtype=torch.uint8)
                 a.scratch, a.scratch_bytes = scratch.data_ptr(), scratch.numel()
             _lib.check(L.smil_forward(dm.handle, C.byref(a), _stream()), "smil_forward")
             del scratch
@@ -223,19 +229,19 @@ class SmalFunction(torch.autograd.Function):
             # static-joint rigs: joints / Rs depend on neither the shape nor trans (smal_torch.py:257-260, 343-346),
             # so with no upstream gradient on the vertices those inputs get None, like the reference graph gives
             shape_path = not (bool(flags & _lib.F_STATIC_JOINTS) and gv is None and gvs is None)
-            o_beta = torch.empty((B, nb), **opts) if (need[3] and nb > 0 and shape_path) else None
-            o_theta = torch.empty(tuple(theta.shape), **opts) if need[4] else None
-            o_trans = torch.empty((B, 3), **opts) if (need[5] and trans is not None and shape_path) else None
-            o_delv = torch.empty((B, V, 3), **opts) if (need[6] and del_v is not None and shape_path) else None
-            o_ls = torch.empty((B, J, 3), **opts) if (need[7] and ls is not None) else None
-            o_bt = torch.empty((B, J, 3), **opts) if (need[8] and bt is not None) else None
+            o_beta = _empty((B, nb), **opts) if (need[3] and nb > 0 and shape_path) else None
+            o_theta = _empty(tuple(theta.shape), **opts) if need[4] else None
+            o_trans = _empty((B, 3), **opts) if (need[5] and trans is not None and shape_path) else None
+            o_delv = _empty((B, V, 3), **opts) if (need[6] and del_v is not None and shape_path) else None
+            o_ls = _empty((B, J, 3), **opts) if (need[7] and ls is not None) else None
+            o_bt = _empty((B, J, 3), **opts) if (need[8] and bt is not None) else None
             g.g_beta = o_beta.data_ptr() if o_beta is not None else None
             g.g_theta = o_theta.data_ptr() if o_theta is not None else None
             g.g_trans = o_trans.data_ptr() if o_trans is not None else None
             g.g_del_v = o_delv.data_ptr() if o_delv is not None else None
             g.g_logscale = o_ls.data_ptr() if o_ls is not None else None
             g.g_btrans = o_bt.data_ptr() if o_bt is not None else None
-            scratch = torch.empty(L.smil_bwd_scratch_bytes(dm.handle, C.byref(g)), device=dev, dtype=torch.uint8)
+            scratch = _empty(L.smil_bwd_scratch_bytes(dm.handle, C.byref(g)), device=dev, dtype=torch.uint8)
             g.scratch, g.scratch_bytes = scratch.data_ptr(), scratch.numel()
             _lib.check(L.smil_backward(dm.handle, C.byref(g), _stream()), "smil_backward")
         if o_delv is not None and ctx.del_v_shape != (B, V, 3):
@@ -251,7 +257,7 @@ class RodriguesFunction(torch.autograd.Function):
     def forward(ctx, theta):
         _check_cuda_f32("theta", theta, theta.device)
         th = theta.contiguous()
-        R = torch.empty((th.shape[0], 3, 3), device=th.device, dtype=torch.float32)
+        R = _empty((th.shape[0], 3, 3), device=th.device, dtype=torch.float32)
         with torch.cuda.device(th.device):
             _lib.check(_lib.lib().smil_rodrigues_forward(th.data_ptr(), R.data_ptr(), th.shape[0], _stream()),
                        "smil_rodrigues_forward")
@@ -282,8 +288,8 @@ class ChainFunction(torch.autograd.Function):
         Rs, Js = Rs.contiguous(), Js.contiguous()
         ls = ls.contiguous() if ls is not None else None
         bt = bt.contiguous() if bt is not None else None
-        newJ = torch.empty((B, J, 3), device=dm.device, dtype=torch.float32)
-        A = torch.empty((B, J, 3, 4), device=dm.device, dtype=torch.float32)
+        newJ = _empty((B, J, 3), device=dm.device, dtype=torch.float32)
+        A = _empty((B, J, 3, 4), device=dm.device, dtype=torch.float32)
         a = _lib.SmilChainArgs()
         a.batch, a.flags = B, flags
         a.Rs, a.Js = Rs.data_ptr(), Js.data_ptr()
@@ -312,9 +318,9 @@ class ChainFunction(torch.autograd.Function):
         gA = g_A.to(torch.float32).contiguous() if g_A is not None else None
         a.g_new_J = gJ.data_ptr() if gJ is not None else None
         a.g_A = gA.data_ptr() if gA is not None else None
-        o_Rs, o_Js = torch.empty((B, J, 3, 3), **opts), torch.empty((B, J, 3), **opts)
-        o_ls = torch.empty((B, J, 3), **opts) if ls is not None else None
-        o_bt = torch.empty((B, J, 3), **opts) if bt is not None else None
+        o_Rs, o_Js = _empty((B, J, 3, 3), **opts), _empty((B, J, 3), **opts)
+        o_ls = _empty((B, J, 3), **opts) if ls is not None else None
+        o_bt = _empty((B, J, 3), **opts) if bt is not None else None
         a.g_Rs, a.g_Js = o_Rs.data_ptr(), o_Js.data_ptr()
         a.g_logscale = o_ls.data_ptr() if o_ls is not None else None
         a.g_btrans = o_bt.data_ptr() if o_bt is not None else None

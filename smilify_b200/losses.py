@@ -23,6 +23,7 @@ import ctypes as C
 import torch
 
 from . import _lib
+from . import functions as _fn
 from .functions import _check_cuda_f32, _stream
 
 
@@ -64,9 +65,9 @@ class ProjectLossFunction(torch.autograd.Function):
         joint_weights = joint_weights.contiguous() if joint_weights is not None else None
         sample_mask = sample_mask.contiguous() if sample_mask is not None else None
         opts = dict(device=dev, dtype=torch.float32)
-        proj = torch.empty((B, V, Jc, 2), **opts)
-        loss = torch.empty((), **opts)
-        partials = torch.empty(B * V * 3 + 4, **opts)
+        proj = _fn._empty((B, V, Jc, 2), **opts)
+        loss = _fn._empty((), **opts)
+        partials = _fn._empty(B * V * 3 + 4, **opts)
         a = ProjectLossFunction._args(kind, image_size, norm_size, clamp_lo, clamp_hi, weight, joints, cam_R, cam_T, fov,
                                       aspect, target, visibility, view_mask, joint_weights, sample_mask, partials)
         a.proj, a.loss = proj.data_ptr(), loss.data_ptr()
@@ -117,10 +118,10 @@ class ProjectLossFunction(torch.autograd.Function):
         a = ProjectLossFunction._args(*ctx.consts, joints, cam_R, cam_T, fov, aspect, target, visibility, view_mask,
                                       joint_weights, sample_mask, partials)
         a.g_loss = gl.data_ptr()
-        g_j = torch.empty((B, Jc, 3), **opts) if need[6] else None
-        g_R = torch.empty((B, V, 3, 3), **opts) if need[7] else None
-        g_T = torch.empty((B, V, 3), **opts) if need[8] else None
-        g_f = torch.empty((B, V), **opts) if need[9] else None
+        g_j = _fn._empty((B, Jc, 3), **opts) if need[6] else None
+        g_R = _fn._empty((B, V, 3, 3), **opts) if need[7] else None
+        g_T = _fn._empty((B, V, 3), **opts) if need[8] else None
+        g_f = _fn._empty((B, V), **opts) if need[9] else None
         a.g_joints = g_j.data_ptr() if g_j is not None else None
         a.g_cam_R = g_R.data_ptr() if g_R is not None else None
         a.g_cam_T = g_T.data_ptr() if g_T is not None else None
@@ -144,8 +145,8 @@ class Keypoint3dLossFunction(torch.autograd.Function):
         joints, target = joints.contiguous(), target.contiguous()
         tens = [None if t is None else t.contiguous() for t in (visibility, joint_weights, sample_mask)]
         B, J = joints.shape[:2]
-        loss = torch.empty((), device=dev, dtype=torch.float32)
-        partials = torch.empty(B * 3 + 4, device=dev, dtype=torch.float32)
+        loss = _fn._empty((), device=dev, dtype=torch.float32)
+        partials = _fn._empty(B * 3 + 4, device=dev, dtype=torch.float32)
         a = Keypoint3dLossFunction._args(joints, target, *tens, partials)
         a.loss = loss.data_ptr()
         with torch.cuda.device(dev):

@@ -22,6 +22,7 @@ import ctypes as C
 import torch
 
 from . import _lib
+from . import functions as _fn
 from .functions import _check_cuda_f32, _stream
 from .losses import _cams, _f, _inner_contig
 
@@ -46,8 +47,8 @@ class TriangulateFunction(torch.autograd.Function):
         keypoints, visibility = keypoints.contiguous(), visibility.contiguous()
         cam_R, cam_T = _inner_contig(cam_R, 2), _inner_contig(cam_T, 1)
         view_mask = view_mask.contiguous() if view_mask is not None else None
-        tri = torch.empty((B, J, 3), device=dev, dtype=torch.float32)
-        valid = torch.empty((B, J), device=dev, dtype=torch.float32)
+        tri = _fn._empty((B, J, 3), device=dev, dtype=torch.float32)
+        valid = _fn._empty((B, J), device=dev, dtype=torch.float32)
         a = TriangulateFunction._args(image_size, keypoints, visibility, cam_R, cam_T, fov, aspect, view_mask)
         a.tri, a.valid = tri.data_ptr(), valid.data_ptr()
         with torch.cuda.device(dev):
@@ -83,9 +84,9 @@ class TriangulateFunction(torch.autograd.Function):
         g_tri = g_tri.to(torch.float32).contiguous()
         a = TriangulateFunction._args(ctx.image_size, keypoints, visibility, cam_R, cam_T, fov, aspect, view_mask)
         a.g_tri = g_tri.data_ptr()
-        gR = torch.empty((B, V, 3, 3), device=dev, dtype=torch.float32) if ctx.needs_input_grad[3] else None
-        gT = torch.empty((B, V, 3), device=dev, dtype=torch.float32) if ctx.needs_input_grad[4] else None
-        gf = torch.empty((B, V), device=dev, dtype=torch.float32) if ctx.needs_input_grad[5] else None
+        gR = _fn._empty((B, V, 3, 3), device=dev, dtype=torch.float32) if ctx.needs_input_grad[3] else None
+        gT = _fn._empty((B, V, 3), device=dev, dtype=torch.float32) if ctx.needs_input_grad[4] else None
+        gf = _fn._empty((B, V), device=dev, dtype=torch.float32) if ctx.needs_input_grad[5] else None
         a.g_cam_R = gR.data_ptr() if gR is not None else None
         a.g_cam_T = gT.data_ptr() if gT is not None else None
         a.g_fov = gf.data_ptr() if gf is not None else None
@@ -110,7 +111,7 @@ class Rot6dFunction(torch.autograd.Function):
     def forward(ctx, d6, columns):
         _check_cuda_f32("rotation_6d", d6, d6.device)
         flat = d6.reshape(-1, 6).contiguous()
-        R = torch.empty((flat.shape[0], 3, 3), device=d6.device, dtype=torch.float32)
+        R = _fn._empty((flat.shape[0], 3, 3), device=d6.device, dtype=torch.float32)
         with torch.cuda.device(d6.device):
             _lib.check(_lib.lib().smil_rot6d_to_rotmat_forward(flat.data_ptr(), R.data_ptr(), flat.shape[0], int(columns),
                                                                _stream()), "smil_rot6d_to_rotmat_forward")

@@ -8,7 +8,7 @@ import subprocess
 import sys
 import traceback
 
-ROOT = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 REPORT = os.path.join(ROOT, "gpurun_out", "parity_report.txt")
 

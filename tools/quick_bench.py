@@ -7,7 +7,7 @@ import time
 import numpy as np
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import smilify_b200  # noqa: E402
 from smilify_b200.smal_torch import SMAL  # noqa: E402
 from tests import rigs  # noqa: E402

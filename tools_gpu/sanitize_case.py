@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""The workload compute-sanitizer is run on (tools_gpu/r2_sanitizer.sh): fused forward + backward on both rigs at batch
+"""The workload compute-sanitizer is run on (`compute-sanitizer --tool X python tools_gpu/sanitize_case.py`; closed on this pool, see profiles/r02_sanitizer.md): fused forward + backward on both rigs at batch
 sizes that make the persistent passes wrap their rings (several sample groups per CTA, odd tails), plus the
 projection-loss, triangulation and 6-D rotation kernels.  Prints the relative error against the fp64 oracle of a subset,
 so a run that "passes" the tool but computes garbage is visible too."""
