@@ -55,6 +55,8 @@ def algorithmic_bytes(V, J, nB):
     assert sum(per_kernel.values()) == fwd + bwd
     per_kernel["pose_bwd_lean_kernel"] = per_kernel["pose_bwd_kernel"]   # the no-log-scale variant moves the same tensors
     per_kernel["skin_bwd_vm_kernel"] = per_kernel["skin_bwd_kernel"]     # vertex-major variant: the same contract tensor
+    per_kernel["pose_fwd_ls_kernel"] = per_kernel["pose_fwd_kernel"]     # lane-per-sample variants: the same tensors
+    per_kernel["pose_bwd_ls_kernel"] = per_kernel["pose_bwd_kernel"]
     return fwd, bwd, per_kernel
 
 

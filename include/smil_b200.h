@@ -59,7 +59,7 @@ typedef struct SmilTuning {
   int32_t bwd_stages;   /* g_verts row buffers of the backward skin pass: 0/1 = single, 2 = double */
   int32_t bwd_cps;      /* resident CTAs per SM the backward grid is sized for (0 = occupancy limit) */
   int32_t bwd_vm;       /* vertex-major backward skin pass for K <= 2 rigs: 0 = on, 2 = off (item-major) */
-  int32_t pose_v2;      /* several-samples-per-warp pose kernels (measured slower at B = 4096): 0 = off, 1 = on */
+  int32_t pose_v2;      /* pose kernel family: 0 = lane-per-sample where eligible (default), 1 = several samples per warp (measured slower), 2 = warp per sample everywhere */
   int32_t pose_lean;    /* log-scale-free backward pose kernel where it applies: 0 = on, 2 = off */
   int32_t bwd_atomic;      /* vertex-major pass adds its partials to a dense dL/dA with vector reductions instead of
                               writing per-(tile, bone) slots: 0 = on, 2 = off (deterministic slots + summing pass) */

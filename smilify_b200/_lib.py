@@ -255,7 +255,9 @@ def tuning_from_env(overrides=None) -> dict:
         v = os.environ.get("SMIL_" + name.upper())
         out[name] = 0 if v in (None, "") else (0 if int(v) else 2)
     v = os.environ.get("SMIL_POSE_V2")
-    out["pose_v2"] = 1 if v not in (None, "") and int(v) else 0
+    out["pose_v2"] = 1 if v not in (None, "") and int(v) else 0   # 1: several samples per warp (pose_kernels2.cuh)
+    if os.environ.get("SMIL_POSE_LS") == "0":
+        out["pose_v2"] = 2                                         # 2: warp per sample (pose_kernels.cuh) everywhere
     out.update(overrides or {})
     return out
 

@@ -12,6 +12,7 @@
 #include "generic_kernels.cuh"
 #include "pose_kernels.cuh"
 #include "pose_kernels2.cuh"
+#include "pose_kernels3.cuh"
 #include "proj_kernels.cuh"
 #include "skin_bwd_vm.cuh"
 #include "tri_kernels.cuh"
@@ -100,6 +101,28 @@ int set_smem(Kern k, size_t bytes) {
 }
 
 // ---- pose kernel launchers ---------------------------------------------------------------------
+// the lane-per-sample forward covers the headline configuration (see pose_kernels3.cuh); everything else keeps the
+// warp-per-sample kernel
+static bool pose_ls_fwd_ok(const DevModel& m, const PoseArgs& a) {
+  if (!m.ls_ok || !a.pp || a.A || a.ls || a.bt || (a.flags & SMIL_F_THETA_IS_ROTMAT)) return false;
+  if (a.jrest_mode == 2 || !a.joints || (a.joints_mode != 1 && a.joints_mode != 2) || a.nb > 16) return false;
+  if (!m.ls_blob[a.jrest_mode == 0 ? 0 : 1]) return false;
+  PoseLs L;
+  L.init_fwd(m);
+  return (size_t)L.total * sizeof(float) <= 227 * 1024;
+}
+
+static bool pose_ls_bwd_ok(const DevModel& m, const PoseArgs& a) {
+  if (!m.ls_ok || (a.flags & SMIL_F_THETA_IS_ROTMAT) || a.bt || a.g_bt || a.g_Rs || a.nb > 16) return false;
+  if (!a.gA_dense || a.gA_slots || (a.gbt_part && a.ntile != 1)) return false;
+  if (!(a.jrest_mode == 1 || (a.jrest_mode == 2 && a.jrest_in && a.jrest_closed))) return false;
+  if (!m.ls_blob[a.jrest_mode == 1 ? 1 : 0]) return false;
+  if (a.joints_mode != 1 && a.joints_mode != 2) return false;
+  PoseLs L;
+  L.init_bwd(m);
+  return (size_t)L.total * sizeof(float) <= 227 * 1024;
+}
+
 int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_t st) {
   PoseSmem L;
   L.J = m.J;
@@ -127,6 +150,20 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
     if (spw == 4) { if (nb8) SMIL_POSE_BWD2(4, 8); else SMIL_POSE_BWD2(4, 16); }
     else { if (nb8) SMIL_POSE_BWD2(2, 8); else SMIL_POSE_BWD2(2, 16); }
 #undef SMIL_POSE_BWD2
+  } else if (lean && m.tune.pose_v2 == 0 && pose_ls_bwd_ok(m, a)) {
+    // lane = sample (pose_kernels3.cuh): a CTA per 32 samples, its warps walk the chains of the tree
+    PoseLs LS;
+    LS.init_bwd(m);
+    const size_t smem3 = (size_t)LS.total * sizeof(float);
+    if (a.nb <= 8) {
+      if ((rc = set_smem(pose_bwd_ls_kernel<8>, smem3)) != SMIL_OK) return rc;
+      prof_begin("pose_bwd_ls_kernel", st);
+      pose_bwd_ls_kernel<8><<<(a.B + 31) / 32, LS_THREADS, smem3, st>>>(m, a, LS, pairs_mode);
+    } else {
+      if ((rc = set_smem(pose_bwd_ls_kernel<16>, smem3)) != SMIL_OK) return rc;
+      prof_begin("pose_bwd_ls_kernel", st);
+      pose_bwd_ls_kernel<16><<<(a.B + 31) / 32, LS_THREADS, smem3, st>>>(m, a, LS, pairs_mode);
+    }
   } else if (lean) {   // no per-joint scales: half the shared memory, the whole batch resident in one wave
     PoseSmemLean LL;
     LL.J = m.J;
@@ -139,6 +176,20 @@ int launch_pose(const DevModel& m, const PoseArgs& a, bool backward, cudaStream_
     if ((rc = set_smem(pose_bwd_kernel, smem)) != SMIL_OK) return rc;
     prof_begin("pose_bwd_kernel", st);
     pose_bwd_kernel<<<grid, POSE_THREADS, smem, st>>>(m, a, L, pairs_mode);
+  } else if (m.tune.pose_v2 == 0 && pose_ls_fwd_ok(m, a)) {
+    // lane = sample (pose_kernels3.cuh): a CTA per 32 samples, its warps split the joints
+    PoseLs LS;
+    LS.init_fwd(m);
+    const size_t smem3 = (size_t)LS.total * sizeof(float);
+    if (a.nb <= 8) {
+      if ((rc = set_smem(pose_fwd_ls_kernel<8>, smem3)) != SMIL_OK) return rc;
+      prof_begin("pose_fwd_ls_kernel", st);
+      pose_fwd_ls_kernel<8><<<(a.B + 31) / 32, LS_THREADS, smem3, st>>>(m, a, LS);
+    } else {
+      if ((rc = set_smem(pose_fwd_ls_kernel<16>, smem3)) != SMIL_OK) return rc;
+      prof_begin("pose_fwd_ls_kernel", st);
+      pose_fwd_ls_kernel<16><<<(a.B + 31) / 32, LS_THREADS, smem3, st>>>(m, a, LS);
+    }
   } else if (m.tune.pose_v2 == 1) {
     // several samples per warp: 4 when every tree level fits 8 lanes per sample, else 2
     const int spw = m.max_width <= 8 ? 4 : 2;
@@ -476,6 +527,145 @@ int smil_model_create(const SmilModelDesc* s, SmilModel** out) {
     fill(by_bone, pbrec4);
     ap.add(reinterpret_cast<const float4*>(pjrec4.data()), pjrec4.size() / 4, &d.pjrec4);
     ap.add(reinterpret_cast<const float4*>(pbrec4.data()), pbrec4.size() / 4, &d.pbrec4);
+  }
+  // ---- lane-per-sample pose kernels: chain schedule + re-laid tables (pose_kernels3.cuh) -------------------------
+  std::vector<int> ls_int;
+  std::vector<float> ls_blob0, ls_blob1;
+  d.ls_ok = 0;
+  if (V && J >= 2) {
+    const int Ji = (int)J;
+    std::vector<std::vector<int>> kids(J);
+    bool tree_ok = s->parents[0] < 0;
+    for (int j = 1; j < Ji && tree_ok; ++j) {
+      tree_ok = s->parents[j] >= 0 && s->parents[j] < j;   // parents precede children (the level tables assume it too)
+      if (tree_ok) kids[s->parents[j]].push_back(j);
+    }
+    if (tree_ok) {
+      std::vector<int> height(J, 1), heavy(J, -1);
+      for (int j = Ji - 1; j >= 0; --j)
+        for (int c : kids[j])
+          if (height[c] + 1 > height[j]) { height[j] = height[c] + 1; heavy[j] = c; }
+      // chains: every child of the root and every non-heavy child starts one and follows the heavy children
+      std::vector<int> chain_ptr{0}, chain_joint, chain_parent, chain_of(J, -1), chain_round;
+      for (int h = 1; h < Ji; ++h) {
+        const int p = s->parents[h];
+        if (p != 0 && heavy[p] == h) continue;
+        const int c = (int)chain_parent.size();
+        for (int i = h; i >= 0; i = heavy[i]) { chain_joint.push_back(i); chain_of[i] = c; }
+        chain_ptr.push_back((int)chain_joint.size());
+        chain_parent.push_back(p);
+        chain_round.push_back(p == 0 ? 0 : chain_round[chain_of[p]] + 1);   // heads are visited in increasing joint order
+      }
+      const int nchain = (int)chain_parent.size();
+      int nround = 0;
+      for (int r : chain_round) nround = std::max(nround, r + 1);
+      // per round: longest chains first onto the least loaded warp
+      std::vector<int> sched_ptr{0}, sched_chain;
+      for (int r = 0; r < nround; ++r) {
+        std::vector<int> cs;
+        for (int c = 0; c < nchain; ++c) if (chain_round[c] == r) cs.push_back(c);
+        std::stable_sort(cs.begin(), cs.end(), [&](int x, int y) {
+          return chain_ptr[x + 1] - chain_ptr[x] > chain_ptr[y + 1] - chain_ptr[y]; });
+        std::vector<std::vector<int>> per(LS_NW);
+        std::vector<int> load(LS_NW, 0);
+        for (int c : cs) {
+          const int wmin = (int)(std::min_element(load.begin(), load.end()) - load.begin());
+          per[wmin].push_back(c);
+          load[wmin] += chain_ptr[c + 1] - chain_ptr[c];
+        }
+        for (int wv = 0; wv < LS_NW; ++wv) {
+          for (int c : per[wv]) sched_chain.push_back(c);
+          sched_ptr.push_back((int)sched_chain.size());
+        }
+      }
+      std::vector<int> dep_ptr(J + 1, 0), dep_chain(nchain);
+      for (int c = 0; c < nchain; ++c) dep_ptr[chain_parent[c] + 1]++;
+      for (int j = 0; j < Ji; ++j) dep_ptr[j + 1] += dep_ptr[j];
+      {
+        std::vector<int> fillp(dep_ptr.begin(), dep_ptr.end() - 1);
+        for (int c = 0; c < nchain; ++c) dep_chain[fillp[chain_parent[c]]++] = c;
+      }
+      // closed-form joints: contiguous joint ranges per warp with about the same number of (joint, bone) pairs
+      std::vector<int> pair_jb(LS_NW + 1, Ji);
+      pair_jb[0] = 0;
+      if (d.npairs > 0 && s->pj_ptr) {
+        for (int wv = 1; wv < LS_NW; ++wv) {
+          const long long target = (long long)d.npairs * wv / LS_NW;
+          int j = pair_jb[wv - 1];
+          while (j < Ji && s->pj_ptr[j] < target) ++j;
+          pair_jb[wv] = j;
+        }
+      } else {
+        for (int wv = 1; wv < LS_NW; ++wv) pair_jb[wv] = (int)((long long)Ji * wv / LS_NW);
+      }
+      // backward: contiguous bone ranges per warp with about the same number of pairs (pairs visited by bone)
+      std::vector<int> bone_jb(LS_NW + 1, Ji);
+      bone_jb[0] = 0;
+      for (int wv = 1; wv < LS_NW; ++wv) {
+        if (d.npairs > 0 && s->pb_ptr) {
+          const long long target = (long long)d.npairs * wv / LS_NW;
+          int j = bone_jb[wv - 1];
+          while (j < Ji && s->pb_ptr[j] < target) ++j;
+          bone_jb[wv] = j;
+        } else {
+          bone_jb[wv] = (int)((long long)Ji * wv / LS_NW);
+        }
+      }
+      const std::vector<int>* parts[9] = {&chain_ptr, &chain_joint, &chain_parent, &sched_ptr, &sched_chain, &dep_ptr, &dep_chain, &pair_jb, &bone_jb};
+      for (int t = 0; t < 9; ++t) {
+        d.ls_off[t] = (int)ls_int.size();
+        ls_int.insert(ls_int.end(), parts[t]->begin(), parts[t]->end());
+      }
+      d.ls_nchain = nchain; d.ls_nround = nround;
+      d.ls_jsw = (1 + (int)nB + 3) & ~3;
+      d.ls_prf = (4 + 3 * (int)nB + 3) & ~3;
+      const bool have_pairs = d.npairs > 0 && s->pj_ptr && s->pj_bone && s->pj_joint && s->pj_c0 && s->pj_cm && s->pb_ptr && s->pb_pair;
+      const int npi = have_pairs ? d.npairs : 0;
+      auto build_blob = [&](bool is_static, std::vector<float>& blob) {
+        std::vector<int> w;   // 4-byte words; floats are stored by bit pattern
+        auto pad4 = [&]() { while (w.size() & 3) w.push_back(0); };
+        auto put_i = [&](const int* p, size_t n) { for (size_t i = 0; i < n; ++i) w.push_back(p ? p[i] : 0); };
+        auto put_f = [&](float v) { int b; memcpy(&b, &v, 4); w.push_back(b); };
+        int o[10];
+        o[LS_O_SCHED] = 0; put_i(ls_int.data(), ls_int.size());
+        o[LS_O_PAR] = (int)w.size(); put_i(s->parents, J);
+        o[LS_O_PJP] = (int)w.size(); if (have_pairs) put_i(s->pj_ptr, J + 1); else w.insert(w.end(), J + 1, 0);
+        o[LS_O_PJB] = (int)w.size(); put_i(s->pj_bone, npi);
+        o[LS_O_PBP] = (int)w.size(); if (have_pairs) put_i(s->pb_ptr, J + 1); else w.insert(w.end(), J + 1, 0);
+        o[LS_O_PBQ] = (int)w.size(); put_i(s->pb_pair, npi);
+        o[LS_O_PJJ] = (int)w.size(); put_i(s->pj_joint, npi);
+        pad4();
+        o[LS_O_RSUM] = (int)w.size();
+        for (size_t j = 0; j < J; ++j) put_f(s->jreg_rowsum ? s->jreg_rowsum[j] : 0.f);
+        pad4();
+        o[LS_O_JST] = (int)w.size();
+        for (size_t e = 0; e < 3 * J; ++e)
+          for (int k = 0; k < d.ls_jsw; ++k) {
+            float v = 0.f;
+            if (is_static) v = (k == 0) ? s->J_static[e] : 0.f;
+            else if (k == 0) v = s->JT[e];
+            else if ((size_t)k <= nB) v = s->JS[(size_t)(k - 1) * 3 * J + e];
+            put_f(v);
+          }
+        o[LS_O_PREC] = (int)w.size();
+        for (int pi = 0; pi < npi; ++pi)
+          for (int k = 0; k < d.ls_prf; ++k) {
+            float v = 0.f;
+            if (k < 4) v = s->pj_c0[pi * 4 + k];
+            else if ((size_t)(k - 4) < nB * 3) v = s->pj_cm[(size_t)pi * nB * 3 + (k - 4)];
+            put_f(v);
+          }
+        pad4();
+        for (int t = 0; t < 10; ++t) d.ls_o[t] = o[t];
+        d.ls_words = (int)w.size();
+        blob.resize(w.size());
+        memcpy(blob.data(), w.data(), w.size() * 4);
+      };
+      d.ls_blob[0] = d.ls_blob[1] = nullptr;
+      if (s->JT && (nB == 0 || s->JS)) { build_blob(false, ls_blob0); ap.add(ls_blob0.data(), ls_blob0.size(), &d.ls_blob[0]); }
+      if (d.has_static && s->J_static) { build_blob(true, ls_blob1); ap.add(ls_blob1.data(), ls_blob1.size(), &d.ls_blob[1]); }
+      d.ls_ok = (!ls_blob0.empty() || !ls_blob1.empty()) ? 1 : 0;   // the device pointers are filled in by the upload below
+    }
   }
   ap.add(s->pb_ptr, V ? J + 1 : 0, &d.pb_ptr);
   ap.add(s->pb_pair, V ? np : 0, &d.pb_pair);

@@ -88,6 +88,18 @@ struct DevModel {
   const float* vm_rec;
   const int4* vm_seg;
   const int *vm_tile_rec_ptr, *vm_warp_seg_ptr, *vm_sb_ptr, *vm_slot_bone;
+  // lane-per-sample pose kernels (pose_kernels3.cuh): ONE blob of 4-byte words per rest-joint mode, built at model
+  // creation and staged into shared memory with a single pass of 16-byte copies.  Word offsets in ls_o[]:
+  //   LS_O_SCHED  chain schedule: [chain_ptr (nchain+1) | chain_joint (J-1) | chain_parent (nchain) |
+  //               sched_ptr (nround*LS_NW+1) | sched_chain (nchain) | dep_ptr (J+1) | dep_chain (nchain) |
+  //               pair_jb (LS_NW+1) | bone_jb (LS_NW+1)], sub-offsets in ls_off[9]
+  //   LS_O_PAR parents (J) | LS_O_PJP pj_ptr (J+1) | LS_O_PJB pj_bone (np) | LS_O_PBP pb_ptr (J+1) | LS_O_PBQ pb_pair (np) |
+  //   LS_O_PJJ pj_joint (np) | LS_O_RSUM jreg_rowsum (J) | LS_O_JST [3J][ls_jsw] (JT | JS_0 .. | 0) per joint component
+  //   (static rigs: (J_static | 0)) | LS_O_PREC [np][ls_prf] (c0.xyz, c0.w | cm[nB][3] | 0) per (joint, bone) pair
+  int ls_ok, ls_nchain, ls_nround, ls_jsw, ls_prf, ls_words;
+  int ls_off[9];
+  int ls_o[10];
+  const float* ls_blob[2];   // [0] closed-form rest joints, [1] static rest joints (null when the rig has none)
   // host copies needed by launch logic
   int h_max_tile_pairs, h_max_jv, h_max_je, h_max_tile_units;
   SmilTuning tune;   // per-model kernel variant switches (host-side launch logic only)
@@ -99,6 +111,7 @@ struct DevModel {
 // of 24 makes 8 consecutive bones start in 8 different 16-byte bank groups, so the per-thread float4
 // gathers of the forward skin pass collide only for bones that are congruent mod 8 (not mod 4).
 constexpr int PPB = 28;
+enum { LS_O_SCHED = 0, LS_O_PAR, LS_O_PJP, LS_O_PJB, LS_O_PBP, LS_O_PBQ, LS_O_PJJ, LS_O_RSUM, LS_O_JST, LS_O_PREC };
 
 // ---- small device math ------------------------------------------------------------------------
 struct f3 {
