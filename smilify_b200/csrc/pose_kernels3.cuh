@@ -57,48 +57,65 @@ struct PoseLs {
   }
 };
 
-// the table blob -> shared memory: every thread issues its (up to 4) 16-byte loads before the first store, so the whole
-// blob costs one memory round trip
-__device__ __forceinline__ void ls_stage_blob(float* dst, const float* src, int words, int tid) {
+// Staging of the CTA's inputs.  Loads and stores are separate calls so that a kernel can issue EVERY global load of its
+// prologue before the first shared-memory store: the whole prologue then costs one memory round trip instead of one
+// per array (the stores of one array would otherwise sit between the loads of the next).
+struct LsBlobRegs { float4 v[4]; };
+__device__ __forceinline__ void ls_blob_load(LsBlobRegs& r, const float* src, int words, int i0, int tid) {
   const float4* s4 = reinterpret_cast<const float4*>(src);
+  const int n4 = words >> 2;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int i = i0 + u * LS_THREADS + tid;
+    r.v[u] = (i < n4) ? s4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+__device__ __forceinline__ void ls_blob_store(const LsBlobRegs& r, float* dst, int words, int i0, int tid) {
   float4* d4 = reinterpret_cast<float4*>(dst);
   const int n4 = words >> 2;
-  for (int i0 = 0; i0 < n4; i0 += 4 * LS_THREADS) {
-    float4 v[4];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int i = i0 + u * LS_THREADS + tid;
-      v[u] = (i < n4) ? s4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+  for (int u = 0; u < 4; ++u) {
+    const int i = i0 + u * LS_THREADS + tid;
+    if (i < n4) d4[i] = r.v[u];
+  }
+}
+// rows [e][sample] of a [B][n] global array for the CTA's 32 samples (2 per warp), 192 elements per call
+struct LsRowRegs { float v[2][6]; };
+__device__ __forceinline__ void ls_rows_load(LsRowRegs& r, const float* src, long long stride, int n, int e0, int b0, int B, int w, int l) {
+  static_assert(LS_NW == 16, "two sample rows per warp");
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int i = i0 + u * LS_THREADS + tid;
-      if (i < n4) d4[i] = v[u];
+  for (int ss = 0; ss < 2; ++ss) {
+    const float* row = src + (long long)min(b0 + w + LS_NW * ss, B - 1) * stride;
+#pragma unroll
+    for (int t = 0; t < 6; ++t) {
+      const int e = e0 + l + 32 * t;
+      r.v[ss][t] = (e < n) ? row[e] : 0.f;
     }
   }
 }
-// rows [e][sample] of a [B][n] global array for the CTA's 32 samples (2 per warp), loads first
-__device__ __forceinline__ void ls_stage_rows(float* dst, const float* src, long long stride, int n, int b0, int B, int w, int l) {
-  static_assert(LS_NW == 16, "two sample rows per warp");
-  for (int e0 = 0; e0 < n; e0 += 192) {
-    float v[2][6];
+__device__ __forceinline__ void ls_rows_store(const LsRowRegs& r, float* dst, int n, int e0, int w, int l) {
 #pragma unroll
-    for (int ss = 0; ss < 2; ++ss) {
-      const float* row = src + (long long)min(b0 + w + LS_NW * ss, B - 1) * stride;
+  for (int ss = 0; ss < 2; ++ss) {
 #pragma unroll
-      for (int t = 0; t < 6; ++t) {
-        const int e = e0 + l + 32 * t;
-        v[ss][t] = (e < n) ? row[e] : 0.f;
-      }
+    for (int t = 0; t < 6; ++t) {
+      const int e = e0 + l + 32 * t;
+      if (e < n) dst[e * LS_RS + w + LS_NW * ss] = r.v[ss][t];
     }
-#pragma unroll
-    for (int ss = 0; ss < 2; ++ss) {
-#pragma unroll
-      for (int t = 0; t < 6; ++t) {
-        const int e = e0 + l + 32 * t;
-        if (e < n) dst[e * LS_RS + w + LS_NW * ss] = v[ss][t];
-      }
-    }
+  }
+}
+// whatever the first call of each did not cover (J > 64, blobs above 32 KB): plain load-then-store chunks
+__device__ __forceinline__ void ls_blob_rest(float* dst, const float* src, int words, int tid) {
+  for (int i0 = 4 * LS_THREADS; i0 < (words >> 2); i0 += 4 * LS_THREADS) {
+    LsBlobRegs r;
+    ls_blob_load(r, src, words, i0, tid);
+    ls_blob_store(r, dst, words, i0, tid);
+  }
+}
+__device__ __forceinline__ void ls_rows_rest(float* dst, const float* src, long long stride, int n, int b0, int B, int w, int l) {
+  for (int e0 = 192; e0 < n; e0 += 192) {
+    LsRowRegs r;
+    ls_rows_load(r, src, stride, n, e0, b0, B, w, l);
+    ls_rows_store(r, dst, n, e0, w, l);
   }
 }
 
@@ -138,8 +155,17 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_fwd_ls_kernel(DevModel m, 
   float tr[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) tr[c] = a.trans ? a.trans[(long long)bs * a.trans_stride + c] : 0.f;
-  ls_stage_rows(ST, a.theta, a.theta_stride, J3, b0, a.B, w, l);
-  ls_stage_blob(TAB, m.ls_blob[a.jrest_mode == 0 ? 0 : 1], m.ls_words, tid);
+  {
+    const float* blob = m.ls_blob[a.jrest_mode == 0 ? 0 : 1];
+    LsRowRegs rt;
+    LsBlobRegs rb;
+    ls_rows_load(rt, a.theta, a.theta_stride, J3, 0, b0, a.B, w, l);
+    ls_blob_load(rb, blob, m.ls_words, 0, tid);
+    ls_rows_store(rt, ST, J3, 0, w, l);
+    ls_blob_store(rb, TAB, m.ls_words, 0, tid);
+    ls_rows_rest(ST, a.theta, a.theta_stride, J3, b0, a.B, w, l);
+    ls_blob_rest(TAB, blob, m.ls_words, tid);
+  }
   __syncthreads();
 
   // rest joint component e = 3j + c:  JT[e] + sum_k beta_k JS[k][e]  (row (JT | JS_0 .. | 0) of the re-laid table)
@@ -372,32 +398,48 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
   float be[NBMAX];
 #pragma unroll
   for (int k = 0; k < NBMAX; ++k) be[k] = (k < nb) ? a.beta[(long long)bs * a.beta_stride + k] : 0.f;
-  ls_stage_rows(TH, a.theta, a.theta_stride, J3, b0, a.B, w, l);
-  if (a.g_joints) ls_stage_rows(GJ, a.g_joints, J3, J3, b0, a.B, w, l);
-  if (!is_static) ls_stage_rows(JRS, a.jrest_in, J3, J3, b0, a.B, w, l);
-  ls_stage_blob(TAB, m.ls_blob[is_static ? 1 : 0], m.ls_words, tid);
-  {   // the forward's pair blocks: float4 (j, t) = (A_s0[2t], A_s1[2t], A_s0[2t+1], A_s1[2t+1]); one pair per warp
+  {
     static_assert(LS_NW == 16, "one sample pair per warp");
+    const float* blob = m.ls_blob[is_static ? 1 : 0];
+    // the forward's pair blocks: float4 (j, t) = (A_s0[2t], A_s1[2t], A_s0[2t+1], A_s1[2t+1]); one pair per warp
     const int npair_tot = (a.B + 1) >> 1;
     const float4* blk = reinterpret_cast<const float4*>(a.pp_saved + (long long)min((b0 >> 1) + w, npair_tot - 1) * a.pp_blk);
     float* x0 = AX + 2 * w;
-    for (int i0 = 0; i0 < 6 * J; i0 += 128) {
-      float4 v[4];
-      int jj[4], tt[4];
+    constexpr int PPC = 12;   // float4 per lane and chunk: 384 per warp covers 6 J for J <= 64 in one round trip
+    auto pp_chunk = [&](int i0, bool load, float4 (&v)[PPC]) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < PPC; ++u) {
         const int i = i0 + 32 * u + l;
-        jj[u] = (int)(((unsigned)i * 43691u) >> 18);   // i / 6 for i < 2^16
-        tt[u] = i - 6 * jj[u];
-        v[u] = (i < 6 * J) ? blk[jj[u] * (PPB / 4) + tt[u]] : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (i0 + 32 * u + l < 6 * J) {
-          float* x = x0 + (jj[u] * 12 + 2 * tt[u]) * LS_RS;
+        const int jj = (int)(((unsigned)i * 43691u) >> 18);   // i / 6 for i < 2^16
+        const int tt = i - 6 * jj;
+        if (load) {
+          v[u] = (i < 6 * J) ? blk[jj * (PPB / 4) + tt] : make_float4(0.f, 0.f, 0.f, 0.f);
+        } else if (i < 6 * J) {
+          float* x = x0 + (jj * 12 + 2 * tt) * LS_RS;
           x[0] = v[u].x; x[1] = v[u].y; x[LS_RS] = v[u].z; x[LS_RS + 1] = v[u].w;
         }
       }
+    };
+    LsRowRegs rt, rg, rj;
+    LsBlobRegs rb;
+    float4 vp[PPC];
+    ls_rows_load(rt, a.theta, a.theta_stride, J3, 0, b0, a.B, w, l);
+    if (a.g_joints) ls_rows_load(rg, a.g_joints, J3, J3, 0, b0, a.B, w, l);
+    if (!is_static) ls_rows_load(rj, a.jrest_in, J3, J3, 0, b0, a.B, w, l);
+    ls_blob_load(rb, blob, m.ls_words, 0, tid);
+    pp_chunk(0, true, vp);
+    ls_rows_store(rt, TH, J3, 0, w, l);
+    if (a.g_joints) ls_rows_store(rg, GJ, J3, 0, w, l);
+    if (!is_static) ls_rows_store(rj, JRS, J3, 0, w, l);
+    ls_blob_store(rb, TAB, m.ls_words, 0, tid);
+    pp_chunk(0, false, vp);
+    ls_rows_rest(TH, a.theta, a.theta_stride, J3, b0, a.B, w, l);
+    if (a.g_joints) ls_rows_rest(GJ, a.g_joints, J3, J3, b0, a.B, w, l);
+    if (!is_static) ls_rows_rest(JRS, a.jrest_in, J3, J3, b0, a.B, w, l);
+    ls_blob_rest(TAB, blob, m.ls_words, tid);
+    for (int i0 = 32 * PPC; i0 < 6 * J; i0 += 32 * PPC) {
+      pp_chunk(i0, true, vp);
+      pp_chunk(i0, false, vp);
     }
   }
   __syncthreads();
@@ -417,7 +459,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
   };
   // dL/dG_i of joint i from its own dL/dA_i (+ the closed-form posed joints) and the deposits of the chains hanging off
   // it; also folds rowsum_i g_joints_i into g_trans and GR_i^T g_joints . cm into g_beta.  Returns jacc in `ja`.
-  auto own_grad = [&](int i, const float4 (&g)[3], const m3& GRi, f3 Jri, m3& gGR, f3& gGt, f3& ja) {
+  auto own_grad = [&](int i, const float4 (&g)[3], const m3& GRi, f3 Jri, m3& gGR, f3& gGt, f3& ja, int dep0, int dep1) {
     m3 gAR;
     gAR.a[0] = g[0].x; gAR.a[1] = g[0].y; gAR.a[2] = g[0].z;
     gAR.a[3] = g[1].x; gAR.a[4] = g[1].y; gAR.a[5] = g[1].z;
@@ -466,7 +508,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
       const float* gi = GJ + 3 * i * LS_RS + l;
       gGt.x += gi[0]; gGt.y += gi[LS_RS]; gGt.z += gi[2 * LS_RS];
     }
-    for (int t = iDepPtr[i]; t < iDepPtr[i + 1]; ++t) {   // chains that hang off joint i (finished in earlier rounds)
+    for (int t = dep0; t < dep1; ++t) {   // chains that hang off joint i (finished in earlier rounds)
       const float* d = DEP + iDepChain[t] * 15 * LS_RS + l;
 #pragma unroll
       for (int q = 0; q < 9; ++q) gGR.a[q] += d[q * LS_RS];
@@ -514,6 +556,17 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
     }
   };
 
+  // joint i is done with the walk: its A slot (dead from here on) keeps (dL/dM_i | dL/dJrest_i) for the per-joint pass
+  auto park = [&](int i, const m3& gM, f3 dJ) {
+    float* ax = AX + i * 12 * LS_RS + l;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) ax[(4 * r + c) * LS_RS] = gM.a[3 * r + c];
+    }
+    ax[3 * LS_RS] = dJ.x; ax[7 * LS_RS] = dJ.y; ax[11 * LS_RS] = dJ.z;
+  };
+
   // ---- chains, deepest round first ----------------------------------------------------------------------------------------
   for (int r = m.ls_nround - 1; r >= 0; --r) {
     for (int ci = iSchedPtr[r * LS_NW + w]; ci < iSchedPtr[r * LS_NW + w + 1]; ++ci) {
@@ -536,7 +589,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
         load_GR(p, GRp);
         const f3 Ji = load_J(i), Jp = load_J(p);
         m3 gGR; f3 gGt, ja;
-        own_grad(i, g, GRi, Ji, gGR, gGt, ja);
+        own_grad(i, g, GRi, Ji, gGR, gGt, ja, iDepPtr[i], iDepPtr[i + 1]);
 #pragma unroll
         for (int q = 0; q < 9; ++q) gGR.a[q] += cGR.a[q];
         gGt.x += cGt.x; gGt.y += cGt.y; gGt.z += cGt.z;
@@ -551,7 +604,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
         cGR.a[6] = fmaf(gGt.z, tl.x, cGR.a[6]); cGR.a[7] = fmaf(gGt.z, tl.y, cGR.a[7]); cGR.a[8] = fmaf(gGt.z, tl.z, cGR.a[8]);
         cGt = gGt;
         cJ = mk3(-gtl.x, -gtl.y, -gtl.z);
-        finish(i, gM, mk3(ja.x + gtl.x, ja.y + gtl.y, ja.z + gtl.z));
+        park(i, gM, mk3(ja.x + gtl.x, ja.y + gtl.y, ja.z + gtl.z));
         GRi = GRp;
         if (t > t0) { g[0] = gn[0]; g[1] = gn[1]; g[2] = gn[2]; }
       }
@@ -563,13 +616,35 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
     }
     __syncthreads();
   }
-  if (w == 0) {   // root: G_0 = (R_0 | J_0)
+  // root: G_0 = (R_0 | J_0).  Its deposits (one per chain that starts below the root: 13 on the STICK rig) are first
+  // summed row by row by 15 warps into the first chain's slot, then warp 0 finishes the joint
+  const int rd0 = iDepPtr[0], rd1 = iDepPtr[1];
+  if (w < 15 && rd1 - rd0 > 1) {
+    float* first = DEP + iDepChain[rd0] * 15 * LS_RS + w * LS_RS + l;
+    float sum = *first;
+    for (int t = rd0 + 1; t < rd1; ++t) sum += DEP[iDepChain[t] * 15 * LS_RS + w * LS_RS + l];
+    *first = sum;
+  }
+  __syncthreads();
+  if (w == 0) {
     float4 g[3];
     load_gA(0, g);
     m3 GR0, gGR; f3 gGt, ja;
     load_GR(0, GR0);
-    own_grad(0, g, GR0, load_J(0), gGR, gGt, ja);
-    finish(0, gGR, mk3(ja.x + gGt.x, ja.y + gGt.y, ja.z + gGt.z));
+    own_grad(0, g, GR0, load_J(0), gGR, gGt, ja, rd0, min(rd1, rd0 + 1));
+    park(0, gGR, mk3(ja.x + gGt.x, ja.y + gGt.y, ja.z + gGt.z));
+  }
+  __syncthreads();
+  // ---- per joint, all warps: Rodrigues VJP and the rest-joint gradient through JS ------------------------------------
+  for (int i = w; i < J; i += LS_NW) {
+    const float* ax = AX + i * 12 * LS_RS + l;
+    m3 gM;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) gM.a[3 * r + c] = ax[(4 * r + c) * LS_RS];
+    }
+    finish(i, gM, mk3(ax[3 * LS_RS], ax[7 * LS_RS], ax[11 * LS_RS]));
   }
   __syncthreads();
 

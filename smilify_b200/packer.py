@@ -95,7 +95,7 @@ def tree_tables(parents: np.ndarray):
     )
 
 
-PACK_FORMAT = 7   # bump when the meaning of a packed table changes: invalidates cached packs
+PACK_FORMAT = 8   # bump when the meaning of a packed table changes: invalidates cached packs
 
 
 def pack_model_cached(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static=None, cache_dir=None):
@@ -110,7 +110,7 @@ def pack_model_cached(v_template, shapedirs, posedirs, J_regressor, weights, par
         if cache_dir is None else cache_dir
     if not cache_dir:
         return pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static)
-    h = hashlib.sha1(repr((PACK_FORMAT, FWD_CHUNK, BWD_CHUNK, VM_CHUNK, VM_PHASES, VM_WARPS, VM_CUT_TOL,
+    h = hashlib.sha1(repr((PACK_FORMAT, FWD_CHUNK, BWD_CHUNK, VM_CHUNK, VM_PHASES, VM_WARPS, VM_CUT_TOL, VM_SEG_COST, VM_FLUSH_COST,
                            sorted((k, v) for k, v in _os.environ.items() if k.startswith("SMIL_")))).encode())
     for a in (v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static):
         a = np.ascontiguousarray(np.asarray(a)) if a is not None else np.zeros(0)
@@ -609,7 +609,9 @@ VM_CHUNK = int(_os.environ.get("SMIL_VM_CHUNK", "168"))   # upper bound of the v
 VM_PHASES = int(_os.environ.get("SMIL_VM_PHASES", "1"))
 VM_WARPS = int(_os.environ.get("SMIL_VM_WARPS", "4"))       # warps of a CTA that share one tile (1: every warp owns a small tile)   # sub-ranges of a tile with their own row buffer (double buffering)
 VM_MODE_PACKED, VM_MODE_X, VM_MODE_Y = 0, 1, 2
-VM_CUT_TOL = float(_os.environ.get("SMIL_VM_CUT_TOL", "0.15"))   # how far a warp cut may move from the equal split
+VM_CUT_TOL = float(_os.environ.get("SMIL_VM_CUT_TOL", "0.06"))   # how far a warp cut may move from the equal-cost split
+VM_SEG_COST = float(_os.environ.get("SMIL_VM_SEG_COST", "2.0"))    # a segment switch, in units of one vertex of the pass
+VM_FLUSH_COST = float(_os.environ.get("SMIL_VM_FLUSH_COST", "6.0"))  # one flushed bone accumulator, same unit
 
 
 def vm_rec_floats(nbt: int) -> int:
@@ -713,17 +715,36 @@ def pack_backward_vm(vt, S3, idx, val, nnz_row, J, nB, chunk=None, nwarps=None, 
             # cut points between the shares: near the equal split, but preferably where the resident bones change
             # anyway (a cut inside a stretch with the same two bones costs two extra partial slots, at a boundary where
             # one bone changes one, where both change none)
+            # The split is equal in estimated COST, not in vertices: a change of the resident bones costs a segment
+            # switch plus one flush per replaced bone (VM_SEG_COST / VM_FLUSH_COST, in units of one vertex), and the
+            # warps of a CTA meet at a barrier after every sample group -- with equal vertex counts the warp that
+            # gets the many short runs at the end of a tile was 13 % (up to 22 %) over the mean on STICK.  Measured on
+            # B200 (skin_bwd_vm, B = 4096): equal vertex counts 98.7 us, (seg, flush) = (1.1, 1.6) 96.5, (1.6, 2.4) 92.4,
+            # (2.2, 3.2) 91.0, (2, 6) 89.2, (4, 5) 89.2, (6, 8) 89.3, (8, 10) 93.4; mouse 324 -> 293 us.  A flush weighs
+            # far more than its ~90 instructions: the vector reductions queue behind each other in the LSU.
+            cost = [0.0] * (n + 1)   # cost[pos]: estimated cost of flat[0:pos]
+            for pos in range(1, n + 1):
+                ch = 0
+                if pos < n:
+                    ch = int(flat[pos - 1][1] != flat[pos][1]) + int(flat[pos - 1][2] != flat[pos][2])
+                cost[pos] = cost[pos - 1] + 1.0 + ((VM_SEG_COST + VM_FLUSH_COST * ch) if ch else 0.0)
+            total = cost[n]
             cuts = [0]
-            tol = max(1, int(VM_CUT_TOL * n / nwarps))
+            tol = max(1.0, VM_CUT_TOL * total / nwarps)
             for w in range(1, nwarps):
-                ideal = (n * w) // nwarps
+                ideal = total * w / nwarps
                 best = None
-                for pos in range(max(cuts[-1] + 1, ideal - tol), min(n - (nwarps - w), ideal + tol) + 1):
+                for pos in range(cuts[-1] + 1, n - (nwarps - w) + 1):
+                    if abs(cost[pos] - ideal) > tol:
+                        continue
                     same = int(flat[pos - 1][1] == flat[pos][1]) + int(flat[pos - 1][2] == flat[pos][2])
-                    key = (same, abs(pos - ideal))
+                    key = (same, abs(cost[pos] - ideal))
                     if best is None or key < best[0]:
                         best = (key, pos)
-                cuts.append(best[1] if best else min(max(ideal, cuts[-1]), n))
+                if best is None:   # nothing inside the tolerance: the position closest to the ideal cost
+                    cand = range(min(cuts[-1] + 1, n), max(n - (nwarps - w), cuts[-1]) + 1)
+                    best = (None, min(cand, key=lambda pos: abs(cost[pos] - ideal))) if len(cand) else (None, min(cuts[-1], n))
+                cuts.append(best[1])
             cuts.append(n)
             shares = [flat[cuts[k]:cuts[k + 1]] for k in range(nwarps)]
             # which warp takes which share is free: give every share to the warp that already holds its bones
