@@ -408,7 +408,7 @@ def run_ours(args, rank, world, local_rank):
     else:
         from smilify_b200.graphed import HostPipeline
 
-        pipe = HostPipeline(model, B, depth=2)
+        pipe = HostPipeline(model, B, depth=2, pack_joints=False)
         for sl in pipe.slots:
             with torch.no_grad():
                 sl["step"].g_verts.copy_(gs.g_verts); sl["step"].g_joints.copy_(gs.g_joints)
@@ -427,8 +427,8 @@ def run_ours(args, rank, world, local_rank):
             for done in pipe.drain():
                 sink[0] += float(done["grad_trans"][0, 0])
         e2e_mode = ("HostPipeline depth 2: per step ONE pinned host->device copy (beta | theta | trans) and ONE "
-                    "device->host copy (parameter gradients | posed joints) overlap the kernels of neighbouring steps; "
-                    "posed vertices and upstream gradients stay device-resident (the loss lives on the device)")
+                    "device->host copy (the parameter gradients: the step's result) overlap the kernels of neighbouring steps; "
+                    "posed vertices, joints and upstream gradients stay device-resident (the loss lives on the device)")
 
     e2e_run(3)
     barrier()

@@ -20,7 +20,7 @@ import torch
 
 class GraphedStep:
     def __init__(self, model, batch, num_betas=None, with_scale=False, with_trans_offsets=False,
-                 propagate_scaling=False, shared_betas=False, warmup=3, packed_io=False):
+                 propagate_scaling=False, shared_betas=False, warmup=3, packed_io=False, pack_joints=True):
         dev = model._device
         J, V = model._tables["J"], model._tables["V"]
         nb = model.num_betas if num_betas is None else num_betas
@@ -59,10 +59,12 @@ class GraphedStep:
         with torch.cuda.graph(self.graph):
             outs, grads = self._run()
             if packed_io:   # (grad_beta | grad_theta | grad_trans | joints) contiguous, gathered on the device
-                parts = [grads[0], grads[1], grads[2], outs[1]]
+                # pack_joints=False: only the parameter gradients travel back (the posed joints are consumed by the
+                # loss on the device; a fit that wants them on the host keeps the default)
+                names = ["grad_beta", "grad_theta", "grad_trans"] + (["joints"] if pack_joints else [])
+                parts = [grads[0], grads[1], grads[2]] + ([outs[1]] if pack_joints else [])
                 self.packed_out = torch.cat([t.reshape(-1) for t in parts])
-                self.out_layout = [("grad_beta", tuple(parts[0].shape)), ("grad_theta", tuple(parts[1].shape)),
-                                   ("grad_trans", tuple(parts[2].shape)), ("joints", tuple(parts[3].shape))]
+                self.out_layout = [(n, tuple(t.shape)) for n, t in zip(names, parts)]
         self.verts, self.joints, self.Rs, self.v_shaped = outs
         it = iter(grads)
         self.grad_beta = next(it)
