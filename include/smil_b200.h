@@ -318,6 +318,17 @@ typedef struct SmilKp3dArgs {
   const float* g_loss; float* g_joints;
 } SmilKp3dArgs;
 int smil_keypoint3d_loss_forward(const SmilKp3dArgs* args, void* stream);
+/* Allocation-free variant of smil_keypoint3d_loss_forward.  No counterpart in the reference: added
+ * for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  Same inputs and the same `loss` output; `args->partials` is IGNORED (may be NULL): the per-sample
+ * partials live in a static device array of the library, 3 * SMIL_KP3D_STATIC_MAX_BATCH + 4 floats (192 KB) that every
+ * GPU loading the library holds until exit.  batch > SMIL_KP3D_STATIC_MAX_BATCH returns SMIL_EUNSUPPORTED.  The call
+ * makes no cudaMalloc / cudaFree / allocating library call; the first call per device resolves the array's device
+ * address (cudaGetSymbolAddress) with that device current.  All calls on a device share the array and it keeps the last
+ * call's contents: calls that overlap on the GPU (different streams) race; the backward of such a call is not provided
+ * (use smil_keypoint3d_loss_forward + _backward with a caller buffer). */
+#define SMIL_KP3D_STATIC_MAX_BATCH 16384
+int smil_keypoint3d_loss_forward_static(const SmilKp3dArgs* args, void* stream);
 int smil_keypoint3d_loss_backward(const SmilKp3dArgs* args, void* stream);
 
 /* ---- DLT triangulation from multi-view 2-D keypoints (multiview_smil_regressor.py:1707-1838) ----------------------

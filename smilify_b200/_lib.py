@@ -153,8 +153,9 @@ EXPORTS = (
     "smil_rodrigues_forward", "smil_rodrigues_backward", "smil_chain_forward", "smil_chain_backward",
     "smil_project_loss_forward", "smil_project_loss_backward", "smil_keypoint3d_loss_forward",
     "smil_keypoint3d_loss_backward", "smil_triangulate_dlt_forward", "smil_triangulate_dlt_backward",
-    "smil_rot6d_to_rotmat_forward", "smil_rot6d_to_rotmat_backward",
+    "smil_rot6d_to_rotmat_forward", "smil_rot6d_to_rotmat_backward", "smil_keypoint3d_loss_forward_static",
 )
+KP3D_STATIC_MAX_BATCH = 16384   # SMIL_KP3D_STATIC_MAX_BATCH
 
 _lib = None
 
@@ -194,6 +195,7 @@ def lib():
     L.smil_project_loss_backward.argtypes = [C.POINTER(SmilProjArgs), C.c_void_p]
     L.smil_keypoint3d_loss_forward.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
     L.smil_keypoint3d_loss_backward.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
+    L.smil_keypoint3d_loss_forward_static.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
     L.smil_triangulate_dlt_forward.argtypes = [C.POINTER(SmilTriArgs), C.c_void_p]
     L.smil_triangulate_dlt_backward.argtypes = [C.POINTER(SmilTriArgs), C.c_void_p]
     L.smil_rot6d_to_rotmat_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]

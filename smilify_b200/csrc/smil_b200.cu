@@ -1127,6 +1127,57 @@ int smil_keypoint3d_loss_backward(const SmilKp3dArgs* a, void* stream) {
   return SMIL_OK;
 }
 
+// ---- allocation-free variant of the 3-D keypoint loss forward ---------------------------------------------------
+// The per-sample partials (the kernel pair's scratch) live in a file-scope device array instead of a caller buffer, so
+// a caller that must not allocate (graph capture, serving loops) needs no scratch tensor.  Every GPU that loads the
+// library holds these SMIL_KP3D_STATIC_MAX_BATCH * 12 + 16 bytes until the process exits.  All calls on a device share
+// the array: calls that overlap on the GPU (different streams) race on it, and it keeps the last call's partials.
+static __device__ __align__(256) float g_kp3d_static_partials[3 * SMIL_KP3D_STATIC_MAX_BATCH + 4];
+
+namespace {
+constexpr int KP3D_MAX_DEVICES = 64;
+std::mutex g_kp3d_mu;
+float* g_kp3d_dev_ptr[KP3D_MAX_DEVICES] = {};   // device address of the array per device ordinal (host code must not
+                                                // pass the symbol itself: that is a host-side stand-in)
+int kp3d_static_ptr(float** out) {
+  int dev = -1;
+  SMIL_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= KP3D_MAX_DEVICES) return fail(SMIL_EUNSUPPORTED, "device ordinal %d beyond %d", dev, KP3D_MAX_DEVICES);
+  std::lock_guard<std::mutex> lk(g_kp3d_mu);
+  if (!g_kp3d_dev_ptr[dev]) {   // once per device, with that device current
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_kp3d_static_partials);
+    if (e != cudaSuccess || !p)
+      return fail(SMIL_ECUDA, "cudaGetSymbolAddress(static keypoint-loss scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+    g_kp3d_dev_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_kp3d_dev_ptr[dev];
+  return SMIL_OK;
+}
+}  // namespace
+
+int smil_keypoint3d_loss_forward_static(const SmilKp3dArgs* a, void* stream) {
+  if (!a || !a->joints || !a->target || !a->loss) return fail(SMIL_EINVAL, "smil_keypoint3d_loss_forward_static: NULL argument");
+  if (a->batch <= 0 || a->num_joints <= 0) return fail(SMIL_EINVAL, "batch/num_joints must be positive");
+  if (a->batch > SMIL_KP3D_STATIC_MAX_BATCH)
+    return fail(SMIL_EUNSUPPORTED, "smil_keypoint3d_loss_forward_static: batch %d exceeds the static scratch (max %d samples); "
+                "use smil_keypoint3d_loss_forward with a caller buffer", a->batch, SMIL_KP3D_STATIC_MAX_BATCH);
+  float* scratch = nullptr;
+  int rc = kp3d_static_ptr(&scratch);
+  if (rc != SMIL_OK) return rc;
+  SmilKp3dArgs b = *a;
+  b.partials = scratch;   // every slot the finalize pass reads ([0, 3 batch)) is written by the first kernel of THIS call,
+                          // and the tail by the finalize pass: nothing has to start at zero
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  prof_begin("kp3d_fwd_kernel", st);
+  kp3d_fwd_kernel<<<blocks_for((long long)b.batch * 32, 256), 256, 0, st>>>(b);
+  SMIL_LAUNCH_CHECK("kp3d_fwd_kernel");
+  prof_begin("kp3d_finalize_kernel", st);
+  kp3d_finalize_kernel<<<1, 256, 0, st>>>(b);
+  SMIL_LAUNCH_CHECK("kp3d_finalize_kernel");
+  return SMIL_OK;
+}
+
 // ---- DLT triangulation, 6-D rotations ---------------------------------------------------------------------
 static int check_tri(const SmilTriArgs* a) {
   if (!a) return fail(SMIL_EINVAL, "SmilTriArgs is NULL");
