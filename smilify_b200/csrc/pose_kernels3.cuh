@@ -29,7 +29,7 @@ constexpr int LS_RS = 33;              // row stride of the [row][sample] tiles
 
 // float offsets of the shared-memory regions (the same code sizes the launch on the host)
 struct PoseLs {
-  int ax, nj, jrs, st, rstg, tab, total;
+  int ax, nj, jrs, st, rstg, tab, flags, total;
   __host__ void init_fwd(const DevModel& m) {
     const int J = m.J;
     int o = 0;
@@ -53,6 +53,7 @@ struct PoseLs {
     rstg = o; o += (m.ls_nchain > 0 ? m.ls_nchain : 1) * 15 * LS_RS;
     o = (o + 3) & ~3;
     tab = o; o += m.ls_words;
+    flags = o; o += ((m.ls_nchain > 0 ? m.ls_nchain : 1) + 3) & ~3;   // one "deposit written" flag per chain
     total = o;
   }
 };
@@ -357,8 +358,13 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_fwd_ls_kernel(DevModel m, 
 // Backward of the same path (autograd of batch_lbs.py:75-197 + Rodrigues + the closed-form joints), lane = sample.
 // Configuration of pose_bwd_lean_kernel (no log-scales) without betas_trans / g_Rs, dense dL/dA from the skinning pass.
 // The chains are walked from their tails to their heads with the running (dL/dGR, dL/dGt, dL/dJrest-of-parent)
-// contribution in registers; a chain hands its final contribution to the joint it hangs off through a deposit slot,
-// the rounds run in reverse order, the root is processed last.  Per joint i with parent p (lean kernel, same algebra):
+// contribution in registers; a chain hands its final contribution to the joint it hangs off through a deposit slot
+// and a shared-memory flag (no CTA barrier between the rounds: a warp waits only for the chains that hang off the joint
+// it is about to process), the root is processed last, by one warp, while the others run the per-joint epilogue.
+// (Measured and dropped: a parallel pre-pass that folds the closed-form posed joints into dL/dA before the walk and hands
+// the result over through the dense scratch buffer -- 35.5 vs 31.2 us: the walk is bound by the L2 latency of its
+// per-joint dL/dA loads, which the inline pair work used to cover.)
+// Per joint i with parent p (lean kernel, same algebra):
 //   dL/dG_i = (dL/dA_i.R - dL/dA_i.t Jrest_i^T | dL/dA_i.t) + children,   jacc_i = -GR_i^T dL/dA_i.t
 //   M_i = GR_p^T GR_i, tl_i = Jrest_i - Jrest_p;   dL/dM_i = GR_p^T dL/dGR_i -> Rodrigues VJP -> g_theta_i
 //   to the parent: (dL/dGR_i M_i^T + dL/dGt_i tl_i^T | dL/dGt_i), dL/dJrest_p -= GR_p^T dL/dGt_i, dL/dJrest_i = jacc_i + GR_p^T dL/dGt_i
@@ -384,6 +390,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
   const int* iSchedChain = iS + m.ls_off[4];
   const int* iDepPtr = iS + m.ls_off[5];
   const int* iDepChain = iS + m.ls_off[6];
+  volatile int* FLAG = reinterpret_cast<volatile int*>(sm_ls + L.flags);
   const int* iPbp = reinterpret_cast<const int*>(TAB) + m.ls_o[LS_O_PBP];
   const int* iPbq = reinterpret_cast<const int*>(TAB) + m.ls_o[LS_O_PBQ];
   const int* iPjj = reinterpret_cast<const int*>(TAB) + m.ls_o[LS_O_PJJ];
@@ -420,6 +427,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
         }
       }
     };
+    for (int c = tid; c < m.ls_nchain; c += LS_THREADS) FLAG[c] = 0;
     LsRowRegs rt, rg, rj;
     LsBlobRegs rb;
     float4 vp[PPC];
@@ -459,7 +467,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
   };
   // dL/dG_i of joint i from its own dL/dA_i (+ the closed-form posed joints) and the deposits of the chains hanging off
   // it; also folds rowsum_i g_joints_i into g_trans and GR_i^T g_joints . cm into g_beta.  Returns jacc in `ja`.
-  auto own_grad = [&](int i, const float4 (&g)[3], const m3& GRi, f3 Jri, m3& gGR, f3& gGt, f3& ja, int dep0, int dep1) {
+  auto own_grad = [&](int i, const float4 (&g)[3], const m3& GRi, f3 Jri, m3& gGR, f3& gGt, f3& ja, int dep0, int dep1, bool wait) {
     m3 gAR;
     gAR.a[0] = g[0].x; gAR.a[1] = g[0].y; gAR.a[2] = g[0].z;
     gAR.a[3] = g[1].x; gAR.a[4] = g[1].y; gAR.a[5] = g[1].z;
@@ -509,7 +517,12 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
       gGt.x += gi[0]; gGt.y += gi[LS_RS]; gGt.z += gi[2 * LS_RS];
     }
     for (int t = dep0; t < dep1; ++t) {   // chains that hang off joint i (finished in earlier rounds)
-      const float* d = DEP + iDepChain[t] * 15 * LS_RS + l;
+      const int dc = iDepChain[t];
+      if (wait) {
+        while (FLAG[dc] == 0) __nanosleep(40);
+        __threadfence_block();
+      }
+      const float* d = DEP + dc * 15 * LS_RS + l;
 #pragma unroll
       for (int q = 0; q < 9; ++q) gGR.a[q] += d[q * LS_RS];
       gGt.x += d[9 * LS_RS]; gGt.y += d[10 * LS_RS]; gGt.z += d[11 * LS_RS];
@@ -567,7 +580,8 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
     ax[3 * LS_RS] = dJ.x; ax[7 * LS_RS] = dJ.y; ax[11 * LS_RS] = dJ.z;
   };
 
-  // ---- chains, deepest round first ----------------------------------------------------------------------------------------
+  // ---- chains, deepest round first; a chain of a deeper round is never scheduled behind a shallower one on its warp, so
+  // the flag waits cannot deadlock -------------------------------------------------------------------------------------------
   for (int r = m.ls_nround - 1; r >= 0; --r) {
     for (int ci = iSchedPtr[r * LS_NW + w]; ci < iSchedPtr[r * LS_NW + w + 1]; ++ci) {
       const int c = iSchedChain[ci];
@@ -589,7 +603,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
         load_GR(p, GRp);
         const f3 Ji = load_J(i), Jp = load_J(p);
         m3 gGR; f3 gGt, ja;
-        own_grad(i, g, GRi, Ji, gGR, gGt, ja, iDepPtr[i], iDepPtr[i + 1]);
+        own_grad(i, g, GRi, Ji, gGR, gGt, ja, iDepPtr[i], iDepPtr[i + 1], true);
 #pragma unroll
         for (int q = 0; q < 9; ++q) gGR.a[q] += cGR.a[q];
         gGt.x += cGt.x; gGt.y += cGt.y; gGt.z += cGt.z;
@@ -613,9 +627,12 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
       for (int q = 0; q < 9; ++q) d[q * LS_RS] = cGR.a[q];
       d[9 * LS_RS] = cGt.x; d[10 * LS_RS] = cGt.y; d[11 * LS_RS] = cGt.z;
       d[12 * LS_RS] = cJ.x; d[13 * LS_RS] = cJ.y; d[14 * LS_RS] = cJ.z;
+      __threadfence_block();
+      __syncwarp();
+      if (l == 0) FLAG[c] = 1;
     }
-    __syncthreads();
   }
+  __syncthreads();
   // root: G_0 = (R_0 | J_0).  Its deposits (one per chain that starts below the root: 13 on the STICK rig) are first
   // summed row by row by 15 warps into the first chain's slot, then warp 0 finishes the joint
   const int rd0 = iDepPtr[0], rd1 = iDepPtr[1];
@@ -626,25 +643,25 @@ __global__ void __launch_bounds__(LS_THREADS, 1) pose_bwd_ls_kernel(DevModel m, 
     *first = sum;
   }
   __syncthreads();
-  if (w == 0) {
+  if (w == 0) {   // root, while the other warps finish the joints below it
     float4 g[3];
     load_gA(0, g);
     m3 GR0, gGR; f3 gGt, ja;
     load_GR(0, GR0);
-    own_grad(0, g, GR0, load_J(0), gGR, gGt, ja, rd0, min(rd1, rd0 + 1));
-    park(0, gGR, mk3(ja.x + gGt.x, ja.y + gGt.y, ja.z + gGt.z));
-  }
-  __syncthreads();
-  // ---- per joint, all warps: Rodrigues VJP and the rest-joint gradient through JS ------------------------------------
-  for (int i = w; i < J; i += LS_NW) {
-    const float* ax = AX + i * 12 * LS_RS + l;
-    m3 gM;
+    own_grad(0, g, GR0, load_J(0), gGR, gGt, ja, rd0, min(rd1, rd0 + 1), false);
+    finish(0, gGR, mk3(ja.x + gGt.x, ja.y + gGt.y, ja.z + gGt.z));
+  } else {
+    // ---- per joint: Rodrigues VJP and the rest-joint gradient through JS ----------------------------------------------
+    for (int i = w; i < J; i += LS_NW - 1) {
+      const float* ax = AX + i * 12 * LS_RS + l;
+      m3 gM;
 #pragma unroll
-    for (int r = 0; r < 3; ++r) {
+      for (int r = 0; r < 3; ++r) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c) gM.a[3 * r + c] = ax[(4 * r + c) * LS_RS];
+        for (int c = 0; c < 3; ++c) gM.a[3 * r + c] = ax[(4 * r + c) * LS_RS];
+      }
+      finish(i, gM, mk3(ax[3 * LS_RS], ax[7 * LS_RS], ax[11 * LS_RS]));
     }
-    finish(i, gM, mk3(ax[3 * LS_RS], ax[7 * LS_RS], ax[11 * LS_RS]));
   }
   __syncthreads();
 
