@@ -356,6 +356,63 @@ typedef struct SmilTriArgs {
 int smil_triangulate_dlt_forward(const SmilTriArgs* args, void* stream);
 int smil_triangulate_dlt_backward(const SmilTriArgs* args, void* stream);
 
+/* Parameter-space terms of the fitter objective, value AND gradient in one call:
+ *   joint limits, pose prior, splay, betas prior   smal_fitter/fitter.py:298-331
+ *   temporal smoothness                            smal_fitter/fitter.py:337-350 (get_temporal)
+ * evaluated per window of `window` consecutive frames and summed over the windows, as optimize_to_joints.py:154-172
+ * drives them (every `mean` of fitter.py runs over ONE window).  The frames of a call may be a shard
+ * [frame_offset, frame_offset + num_frames) of a sequence of total_frames frames; with w_temp > 0 the parameters of
+ * the frames just outside the shard arrive as halos (layout [3 global | 3(J-1) joint | 3 trans]); a missing halo for an
+ * existing neighbour is an error.  Masks multiply the parameters (fitter.py:242-243).  pose_precs NULL = identity,
+ * pose_mean NULL = zero, pose_use NULL = all but the root's three angles (the prior fitter.py:25-52 builds for rigs
+ * without hard-coded body data).  Gradients are written (accumulate = 0) or added (accumulate = 1), scaled by g_scale. */
+typedef struct SmilFitterPriorArgs {
+  int32_t num_frames, num_joints, num_betas, window;
+  int64_t frame_offset, total_frames;
+  const float* global_rot;    /* [n][3] */
+  const float* joint_rot;     /* [n][J-1][3] */
+  const float* trans;         /* [n][3] */
+  const float* betas;         /* [nB], shared by the frames (fitter.py:240-241) or NULL */
+  const float* halo_prev;     /* [3J + 3] parameters of frame frame_offset - 1, or NULL */
+  const float* halo_next;     /* [3J + 3] parameters of frame frame_offset + n, or NULL */
+  const float* max_limits;    /* [J-1][3] or NULL */
+  const float* min_limits;    /* [J-1][3] or NULL */
+  const float* rotation_mask; /* [J-1][3] or NULL */
+  const float* global_mask;   /* [3] or NULL */
+  const float* pose_mean;     /* [3J] or NULL */
+  const float* pose_precs;    /* [3J][3J] or NULL */
+  const float* pose_use;      /* [3J] or NULL */
+  const float* betas_mean;    /* [nB] or NULL */
+  const float* betas_prec;    /* [nB][nB] or NULL (no betas prior) */
+  float w_limit, w_pose, w_splay, w_betas, w_temp, g_scale;
+  int32_t accumulate;
+  float* loss;                /* [1] sum of the terms of this call */
+  float* partials;            /* [n] scratch (per-frame values) */
+  float* g_global_rot;        /* [n][3] */
+  float* g_joint_rot;         /* [n][J-1][3] */
+  float* g_trans;             /* [n][3] or NULL */
+  float* g_betas;             /* [nB] or NULL */
+} SmilFitterPriorArgs;
+int smil_fitter_prior_terms(const SmilFitterPriorArgs* args, void* stream);
+
+/* Fused Adam step over up to SMIL_ADAM_MAX_TENSORS parameter tensors (torch.optim.Adam defaults: no weight decay, no
+ * amsgrad), the optimiser of smal_fitter/optimize_to_joints.py:117-126, :175.  `step` is a device counter that the call
+ * increments BEFORE the update (bias corrections use the incremented value), so that the call can be replayed from a
+ * CUDA graph. */
+#define SMIL_ADAM_MAX_TENSORS 8
+typedef struct SmilAdamArgs {
+  int32_t num_tensors;
+  float beta1, beta2, eps;
+  float* param[SMIL_ADAM_MAX_TENSORS];
+  const float* grad[SMIL_ADAM_MAX_TENSORS];
+  float* exp_avg[SMIL_ADAM_MAX_TENSORS];
+  float* exp_avg_sq[SMIL_ADAM_MAX_TENSORS];
+  int64_t numel[SMIL_ADAM_MAX_TENSORS];
+  float lr[SMIL_ADAM_MAX_TENSORS];
+  int32_t* step;
+} SmilAdamArgs;
+int smil_adam_step(const SmilAdamArgs* args, void* stream);
+
 /* 6-D rotation representation -> rotation matrix by Gram-Schmidt: d6 [N][6] -> R [N][9] row-major.
  * columns = 0: b1, b2, b3 are the ROWS (pytorch3d.transforms.rotation_6d_to_matrix, smil_image_regressor.py:87-96);
  * columns = 1: the COLUMNS (the reference's own _rotation_6d_to_matrix for cameras, multiview_smil_regressor.py:250-272). */

@@ -53,12 +53,12 @@ def temporal_terms(global_rot, joint_rot, trans, w_temp, rotation_mask=None, glo
 
     g = global_rot * (global_mask if global_mask is not None else 1.0)
     jr = joint_rot * (rotation_mask if rotation_mask is not None else 1.0)
-    zero = torch.zeros((), dtype=global_rot.dtype)
-    jl, gl, tl = zero.clone(), zero.clone(), zero.clone()
+    # the reference accumulates into fp32 scalars IN PLACE (fitter.py:341-348), whatever the dtype of the parameters
+    jl, gl, tl = torch.tensor(0.0).float(), torch.tensor(0.0).float(), torch.tensor(0.0).float()
     for i in range(global_rot.shape[0] - 1):
-        gl = gl + F.mse_loss(g[i], g[i + 1]) * w_temp
-        jl = jl + F.mse_loss(jr[i], jr[i + 1]) * w_temp
-        tl = tl + F.mse_loss(trans[i], trans[i + 1]) * w_temp
+        gl += F.mse_loss(g[i], g[i + 1]) * w_temp
+        jl += F.mse_loss(jr[i], jr[i + 1]) * w_temp
+        tl += F.mse_loss(trans[i], trans[i + 1]) * w_temp
     return jl, gl, tl
 
 
@@ -72,5 +72,5 @@ def epoch_objective(global_rot, joint_rot, trans, betas, w, window, **consts):
             total = total + v
     if w.get("w_temp", 0) > 0:
         jl, gl, tl = temporal_terms(global_rot, joint_rot, trans, w["w_temp"], consts.get("rotation_mask"), consts.get("global_mask"))
-        total = total + jl + gl + tl
+        total = total + jl.to(total.dtype) + gl.to(total.dtype) + tl.to(total.dtype)
     return total

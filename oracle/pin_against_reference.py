@@ -701,6 +701,122 @@ def pin_caller(ref, report):
     print("froze SMAL3DFitter.forward over the reference SMAL:", {k: v.shape for k, v in out.items()})
 
 
+def fitter_prior_cases():
+    """Seeded inputs of the fitter parameter-space pins (fp32-representable)."""
+    cases = {}
+    for name, (N, J, nB, window, ident, seed) in {"fp_n23_j55_w10": (23, 55, 5, 10, True, 1), "fp_n7_j31_w10": (7, 31, 3, 10, True, 2),
+                                                   "fp_n12_j35_dense": (12, 35, 6, 5, False, 3)}.items():
+        rs = np.random.RandomState(seed)
+        f = lambda a: np.asarray(a, dtype=np.float32)
+        P = 3 * J
+        c = dict(global_rot=f(rs.normal(0, 0.4, (N, 3))), joint_rot=f(rs.normal(0, 0.5, (N, J - 1, 3))),
+                 trans=f(rs.normal(0, 1, (N, 3))), betas=f(rs.normal(0, 0.5, (nB,))),
+                 max_limits=f(rs.uniform(0.1, 0.6, (J - 1, 3))), min_limits=f(-rs.uniform(0.1, 0.6, (J - 1, 3))),
+                 betas_mean=f(rs.normal(0, 0.1, (nB,))), betas_prec=f(rs.normal(0, 1, (nB, nB))),
+                 rotation_mask=f(rs.uniform(size=(J - 1, 3)) > 0.1), global_mask=f(np.ones((1, 3))),
+                 window=np.int64(window), weights=f([0.7, 1.3, 0.05, 0.9, 0.4]))   # limit, pose, splay, betas, temp
+        if ident:
+            use = np.ones(P, np.float32); use[:3] = 0
+            c.update(pose_mean=np.zeros(P, np.float32), pose_precs=np.eye(P, dtype=np.float32), pose_use=use)
+        else:
+            use = f(rs.uniform(size=P) > 0.2); use[:3] = 0
+            c.update(pose_mean=f(rs.normal(0, 0.2, P)), pose_precs=f(rs.normal(0, 0.3, (P, P))), pose_use=use)
+        cases[name] = c
+    return cases
+
+
+def pin_fitter_priors(ref, report):
+    """(f)2, first half: the parameter-space terms of ``SMALFitter.forward`` (fitter.py:298-331) and ``get_temporal``
+    (fitter.py:337-350), AST-extracted from the reference and executed window by window as optimize_to_joints.py:154-172
+    drives them; values and gradients frozen for the CUDA kernel, the oracle restatement checked against them."""
+    import textwrap
+
+    import torch.nn.functional as F
+
+    from oracle import fitter_oracle as FO
+
+    ft = os.path.join(ref, "smal_fitter", "fitter.py")
+
+    def pick(n):
+        if not isinstance(n, ast.If):
+            return False
+        t = n.test
+        if isinstance(t, ast.Attribute) and t.attr == "ignore_hardcoded_body":
+            return any(isinstance(x, ast.Name) and x.id == "w_limit" for x in ast.walk(n))
+        return (isinstance(t, ast.Compare) and isinstance(t.left, ast.Name) and t.left.id in ("w_pose", "w_splay", "w_betas"))
+    blocks = _extract_statements(ft, "forward", pick)
+    assert len(blocks) == 4, [b.splitlines()[0] for b in blocks]
+    fwd_src = "\n".join(blocks)
+    ns = {"torch": torch, "F": F}
+    exec(_extract_function(ft, "get_temporal"), ns)
+
+    def run_reference(c, dt):
+        t = lambda k: torch.from_numpy(c[k]).to(dt)
+        leaves = {k: t(k).clone().requires_grad_(True) for k in ("global_rot", "joint_rot", "trans", "betas")}
+        self = _Stub()
+        self.max_limits, self.min_limits = t("max_limits"), t("min_limits")
+        self.mean_betas, self.betas_prec, self.use_unity_prior = t("betas_mean"), t("betas_prec"), False
+        mean, precs, use = t("pose_mean"), t("pose_precs"), t("pose_use")
+        self.pose_prior = lambda x: (torch.tensordot(x.reshape(x.shape[0], -1) - mean.unsqueeze(0), precs, dims=([1], [0])) * use) ** 2
+        self.rotation_mask, self.global_mask = t("rotation_mask"), t("global_mask")
+        self.device = torch.device("cpu")
+        cfg = _Stub()
+        cfg.ignore_hardcoded_body = True
+        wl, wp, ws, wb, wt = (float(x) for x in c["weights"])
+        N, W = c["global_rot"].shape[0], int(c["window"])
+        total = torch.zeros((), dtype=dt)
+        for j in range(0, N, W):
+            rng = list(range(j, min(N, j + W)))
+            batch_params = {"global_rotation": leaves["global_rot"][rng] * self.global_mask,      # fitter.py:240-246
+                            "joint_rotations": leaves["joint_rot"][rng] * self.rotation_mask,
+                            "betas": leaves["betas"].expand(len(rng), -1)}
+            loc = {"self": self, "config": cfg, "torch": torch, "batch_params": batch_params, "objs": {},
+                   "w_limit": wl, "w_pose": wp, "w_splay": ws, "w_betas": wb}
+            exec(fwd_src, loc)
+            assert sorted(loc["objs"]) == ["betas", "limit", "pose", "splay"]
+            for v in loc["objs"].values():
+                total = total + v
+        # get_temporal reads the model's parameters
+        self.joint_rotations, self.global_rotation, self.trans = leaves["joint_rot"], leaves["global_rot"], leaves["trans"]
+        self.num_images = N
+        jl, gl, tl = ns["get_temporal"](self, wt)
+        total = total + jl.to(dt) + gl.to(dt) + tl.to(dt)
+        total.backward()
+        return total.detach(), {k: v.grad for k, v in leaves.items()}
+
+    def run_oracle(c, dt):
+        t = lambda k: torch.from_numpy(c[k]).to(dt)
+        leaves = {k: t(k).clone().requires_grad_(True) for k in ("global_rot", "joint_rot", "trans", "betas")}
+        wl, wp, ws, wb, wt = (float(x) for x in c["weights"])
+        total = FO.epoch_objective(leaves["global_rot"], leaves["joint_rot"], leaves["trans"], leaves["betas"],
+                                   dict(w_limit=wl, w_pose=wp, w_splay=ws, w_betas=wb, w_temp=wt), int(c["window"]),
+                                   max_limits=t("max_limits"), min_limits=t("min_limits"),
+                                   pose_prior=dict(mean=t("pose_mean"), precs=t("pose_precs"), use=t("pose_use")),
+                                   betas_mean=t("betas_mean"), betas_prec=t("betas_prec"),
+                                   rotation_mask=t("rotation_mask"), global_mask=t("global_mask"))
+        total.backward()
+        return total.detach(), {k: v.grad for k, v in leaves.items()}
+
+    flat, worst = {}, 0.0
+    for name, c in fitter_prior_cases().items():
+        r64, g64 = run_reference(c, torch.float64)
+        o64, og64 = run_oracle(c, torch.float64)
+        errs = [abs(float(o64 - r64)) / abs(float(r64))] + [rel(og64[k].numpy(), g64[k].numpy()) for k in g64]
+        worst = max(worst, max(errs))
+        assert max(errs) < 1e-12, (name, errs)
+        r32, g32 = run_reference(c, torch.float32)
+        for k, v in c.items():
+            flat["%s/in_%s" % (name, k)] = v
+        flat["%s/ref64_total" % name] = r64.numpy()
+        flat["%s/ref32_total" % name] = r32.numpy()
+        for k in g64:
+            flat["%s/ref64_grad_%s" % (name, k)] = g64[k].numpy()
+            flat["%s/ref32_grad_%s" % (name, k)] = g32[k].numpy()
+    np.savez_compressed(os.path.join(rigs.GOLDEN, "fitter_prior_pins.npz"), **flat)
+    report["fitter_prior_oracle_vs_reference_fp64"] = worst
+    print("pinned fitter parameter-space terms (limit, pose, splay, betas, temporal): oracle vs reference code %.2e" % worst)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ref", default="/root/reference")
@@ -715,6 +831,7 @@ def main():
     pin_loss_chains(a.ref, report)
     pin_triangulation(a.ref, report)
     pin_caller(a.ref, report)
+    pin_fitter_priors(a.ref, report)
     with open(os.path.join(rigs.GOLDEN, "PIN_REPORT.json"), "w") as fh:
         json.dump(report, fh, indent=1, sort_keys=True)
     print("pinned:", json.dumps(report["worst"]))

@@ -125,6 +125,33 @@ class SmilKp3dArgs(C.Structure):
     ]
 
 
+class SmilFitterPriorArgs(C.Structure):
+    _fields_ = [
+        ("num_frames", C.c_int32), ("num_joints", C.c_int32), ("num_betas", C.c_int32), ("window", C.c_int32),
+        ("frame_offset", C.c_int64), ("total_frames", C.c_int64),
+        ("global_rot", C.c_void_p), ("joint_rot", C.c_void_p), ("trans", C.c_void_p), ("betas", C.c_void_p),
+        ("halo_prev", C.c_void_p), ("halo_next", C.c_void_p), ("max_limits", C.c_void_p), ("min_limits", C.c_void_p),
+        ("rotation_mask", C.c_void_p), ("global_mask", C.c_void_p), ("pose_mean", C.c_void_p), ("pose_precs", C.c_void_p),
+        ("pose_use", C.c_void_p), ("betas_mean", C.c_void_p), ("betas_prec", C.c_void_p),
+        ("w_limit", C.c_float), ("w_pose", C.c_float), ("w_splay", C.c_float), ("w_betas", C.c_float),
+        ("w_temp", C.c_float), ("g_scale", C.c_float), ("accumulate", C.c_int32),
+        ("loss", C.c_void_p), ("partials", C.c_void_p), ("g_global_rot", C.c_void_p), ("g_joint_rot", C.c_void_p),
+        ("g_trans", C.c_void_p), ("g_betas", C.c_void_p),
+    ]
+
+
+ADAM_MAX_TENSORS = 8
+
+
+class SmilAdamArgs(C.Structure):
+    _fields_ = [
+        ("num_tensors", C.c_int32), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
+        ("param", C.c_void_p * ADAM_MAX_TENSORS), ("grad", C.c_void_p * ADAM_MAX_TENSORS),
+        ("exp_avg", C.c_void_p * ADAM_MAX_TENSORS), ("exp_avg_sq", C.c_void_p * ADAM_MAX_TENSORS),
+        ("numel", C.c_int64 * ADAM_MAX_TENSORS), ("lr", C.c_float * ADAM_MAX_TENSORS), ("step", C.c_void_p),
+    ]
+
+
 class SmilTriArgs(C.Structure):
     _fields_ = [
         ("batch", C.c_int32), ("num_views", C.c_int32), ("num_joints", C.c_int32), ("image_size", C.c_float),
@@ -154,6 +181,7 @@ EXPORTS = (
     "smil_project_loss_forward", "smil_project_loss_backward", "smil_keypoint3d_loss_forward",
     "smil_keypoint3d_loss_backward", "smil_triangulate_dlt_forward", "smil_triangulate_dlt_backward",
     "smil_rot6d_to_rotmat_forward", "smil_rot6d_to_rotmat_backward", "smil_keypoint3d_loss_forward_static",
+    "smil_fitter_prior_terms", "smil_adam_step",
 )
 KP3D_STATIC_MAX_BATCH = 16384   # SMIL_KP3D_STATIC_MAX_BATCH
 
@@ -196,6 +224,8 @@ def lib():
     L.smil_keypoint3d_loss_forward.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
     L.smil_keypoint3d_loss_backward.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
     L.smil_keypoint3d_loss_forward_static.argtypes = [C.POINTER(SmilKp3dArgs), C.c_void_p]
+    L.smil_fitter_prior_terms.argtypes = [C.POINTER(SmilFitterPriorArgs), C.c_void_p]
+    L.smil_adam_step.argtypes = [C.POINTER(SmilAdamArgs), C.c_void_p]
     L.smil_triangulate_dlt_forward.argtypes = [C.POINTER(SmilTriArgs), C.c_void_p]
     L.smil_triangulate_dlt_backward.argtypes = [C.POINTER(SmilTriArgs), C.c_void_p]
     L.smil_rot6d_to_rotmat_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]

@@ -13,6 +13,7 @@
 #include "pose_kernels.cuh"
 #include "pose_kernels2.cuh"
 #include "pose_kernels3.cuh"
+#include "fitter_kernels.cuh"
 #include "proj_kernels.cuh"
 #include "skin_bwd_vm.cuh"
 #include "tri_kernels.cuh"
@@ -1175,6 +1176,55 @@ int smil_keypoint3d_loss_forward_static(const SmilKp3dArgs* a, void* stream) {
   prof_begin("kp3d_finalize_kernel", st);
   kp3d_finalize_kernel<<<1, 256, 0, st>>>(b);
   SMIL_LAUNCH_CHECK("kp3d_finalize_kernel");
+  return SMIL_OK;
+}
+
+// ---- fitter parameter-space terms, fused Adam -----------------------------------------------------------------
+int smil_fitter_prior_terms(const SmilFitterPriorArgs* a, void* stream) {
+  if (!a || !a->global_rot || !a->joint_rot || !a->loss || !a->partials || !a->g_global_rot || !a->g_joint_rot)
+    return fail(SMIL_EINVAL, "smil_fitter_prior_terms: NULL argument");
+  if (a->num_frames <= 0 || a->num_joints < 2) return fail(SMIL_EINVAL, "num_frames must be positive and num_joints >= 2");
+  if (a->frame_offset < 0 || a->frame_offset + a->num_frames > a->total_frames)
+    return fail(SMIL_EINVAL, "frames [%lld, %lld) outside the sequence of %lld frames", (long long)a->frame_offset,
+                (long long)(a->frame_offset + a->num_frames), (long long)a->total_frames);
+  if (a->w_temp > 0.f) {
+    if (!a->trans) return fail(SMIL_EINVAL, "the temporal term needs trans");
+    if (a->frame_offset > 0 && !a->halo_prev) return fail(SMIL_EINVAL, "w_temp > 0: halo_prev is required for a shard that starts at frame %lld", (long long)a->frame_offset);
+    if (a->frame_offset + a->num_frames < a->total_frames && !a->halo_next) return fail(SMIL_EINVAL, "w_temp > 0: halo_next is required for a shard that ends before the sequence does");
+  }
+  if (a->w_betas > 0.f && a->betas_prec && (!a->betas || a->num_betas <= 0 || a->num_betas > 64))
+    return fail(SMIL_EINVAL, "the betas prior needs betas and 1 <= num_betas <= 64");
+  if (a->g_trans && !a->trans) return fail(SMIL_EINVAL, "g_trans without trans");
+  SmilFitterPriorArgs b = *a;
+  if (!b.trans) { b.g_trans = nullptr; b.trans = b.global_rot; }   // never dereferenced for the translation then
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t smem = (size_t)(6 * a->num_joints + FIT_THREADS) * sizeof(float);
+  prof_begin("fitter_prior_kernel", st);
+  fitter_prior_kernel<<<a->num_frames, FIT_THREADS, smem, st>>>(b);
+  SMIL_LAUNCH_CHECK("fitter_prior_kernel");
+  prof_begin("fitter_prior_finalize_kernel", st);
+  fitter_prior_finalize_kernel<<<1, 256, 0, st>>>(b);
+  SMIL_LAUNCH_CHECK("fitter_prior_finalize_kernel");
+  return SMIL_OK;
+}
+
+int smil_adam_step(const SmilAdamArgs* a, void* stream) {
+  if (!a || !a->step) return fail(SMIL_EINVAL, "smil_adam_step: NULL argument");
+  if (a->num_tensors <= 0 || a->num_tensors > SMIL_ADAM_MAX_TENSORS)
+    return fail(SMIL_EINVAL, "num_tensors must be in [1, %d]", SMIL_ADAM_MAX_TENSORS);
+  long long total = 0;
+  for (int t = 0; t < a->num_tensors; ++t) {
+    if (!a->param[t] || !a->grad[t] || !a->exp_avg[t] || !a->exp_avg_sq[t] || a->numel[t] <= 0)
+      return fail(SMIL_EINVAL, "tensor %d: NULL pointer or empty", t);
+    total += a->numel[t];
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  prof_begin("adam_tick_kernel", st);
+  adam_tick_kernel<<<1, 1, 0, st>>>(a->step);
+  SMIL_LAUNCH_CHECK("adam_tick_kernel");
+  prof_begin("adam_step_kernel", st);
+  adam_step_kernel<<<blocks_for(total, 256), 256, 0, st>>>(*a, total);
+  SMIL_LAUNCH_CHECK("adam_step_kernel");
   return SMIL_OK;
 }
 

@@ -164,3 +164,27 @@ def test_loss_chain_oracle_matches_frozen_reference_values():
         assert abs(float(loss) - float(z[name + "/loss"])) <= 1e-12 * abs(float(z[name + "/loss"]))
         for k, v in leaf.items():
             assert rel(v.grad.numpy(), z[name + "/grad_" + k]) < 1e-11, (name, k)
+
+
+def test_fitter_prior_oracle_matches_the_frozen_reference_code():
+    """(f)2: oracle/fitter_oracle.py against the outputs of the reference's own fitter.py statements (fp64, exact)."""
+    import torch
+
+    from oracle import fitter_oracle as FO
+
+    z = np.load(os.path.join(rigs.GOLDEN, "fitter_prior_pins.npz"))
+    for name in sorted({k.split("/")[0] for k in z.files}):
+        c = {k.split("/", 1)[1][3:]: z[k] for k in z.files if k.startswith(name + "/in_")}
+        t = lambda k: torch.from_numpy(c[k]).double()
+        leaves = {k: t(k).clone().requires_grad_(True) for k in ("global_rot", "joint_rot", "trans", "betas")}
+        wl, wp, ws, wb, wt = (float(x) for x in c["weights"])
+        total = FO.epoch_objective(leaves["global_rot"], leaves["joint_rot"], leaves["trans"], leaves["betas"],
+                                   dict(w_limit=wl, w_pose=wp, w_splay=ws, w_betas=wb, w_temp=wt), int(c["window"]),
+                                   max_limits=t("max_limits"), min_limits=t("min_limits"),
+                                   pose_prior=dict(mean=t("pose_mean"), precs=t("pose_precs"), use=t("pose_use")),
+                                   betas_mean=t("betas_mean"), betas_prec=t("betas_prec"),
+                                   rotation_mask=t("rotation_mask"), global_mask=t("global_mask"))
+        total.backward()
+        assert abs(float(total) - float(z[name + "/ref64_total"])) <= 1e-12 * abs(float(total))
+        for k, v in leaves.items():
+            assert np.abs(v.grad.numpy() - z["%s/ref64_grad_%s" % (name, k)]).max() <= 1e-12
