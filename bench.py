@@ -484,6 +484,7 @@ def run_ours(args, rank, world, local_rank):
                         "frac": round(ach / peak, 4), "traffic": traffic_for(top, args), "peak_source": peak_src,
                         "alg_bytes_per_launch": ab, "avg_us": kernels[top]["avg_us"]}
     fitter = None
+    fitter_full = None
     if world > 1 and not args.no_fitter:
         # the one collective of the path (north_star): BASELINE configs[3], frames strong-scaled over the ranks, shared
         # betas / fov, ONE packed NCCL all-reduce per step captured inside the step's CUDA graph
@@ -495,6 +496,10 @@ def run_ours(args, rank, world, local_rank):
         del gs
         torch.cuda.empty_cache()
         fitter = fm.run_fitter(args.fitter_frames, max(5, min(K, 20)), 3, rank, world, dev, rig="stick13")
+        torch.cuda.empty_cache()
+        # the same step with the fitter's parameter-space terms (halo exchange for the temporal term) and the fused Adam
+        # inside the graph: SURVEY.md section 8(f) row 2
+        fitter_full = fm.run_fitter(args.fitter_frames, max(5, min(K, 20)), 3, rank, world, dev, rig="stick13", full_step=True)
         smilify_b200.configure(rigs.REAL_RIGS[args.rig])
     if rank != 0:
         return
@@ -532,6 +537,8 @@ def run_ours(args, rank, world, local_rank):
         line["torch_gpu_baseline"] = torch_gpu
     if fitter is not None:
         line["fitter"] = fitter
+    if fitter_full is not None:
+        line["fitter_full"] = fitter_full
     if cores_pinned:
         line["config"]["host_cores_per_rank"] = cores_pinned
     if cpu_val is not None:

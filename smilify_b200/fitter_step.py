@@ -61,6 +61,54 @@ def allreduce_shared_grads(shared: Sequence[torch.Tensor], group=None) -> int:
     return buf.numel() * 4
 
 
+def pack_boundary_frames(frame_params: Dict[str, torch.Tensor]) -> torch.Tensor:
+    """``[first frame | last frame]`` of a shard, each ``[global(3) | joints(3(J-1)) | trans(3)]`` (the halo layout of
+    ``smil_fitter_prior_terms``)."""
+    def one(i):
+        return torch.cat([frame_params["global_rotation"][i].reshape(-1), frame_params["joint_rotations"][i].reshape(-1),
+                          frame_params["trans"][i].reshape(-1)])
+    return torch.cat([one(0), one(-1)]).detach().to(torch.float32)
+
+
+def exchange_halos(frame_params: Dict[str, torch.Tensor], group=None):
+    """The 1-frame halo of SURVEY.md section 8(e) for the temporal term (fitter.py:337-350 couples frame i and i+1):
+    every rank contributes its first and last frame to ONE ``all_gather`` (2 (3J + 3) floats per rank) and picks the
+    last frame of the rank before it and the first frame of the rank after it.  Returns ``(halo_prev, halo_next)``,
+    ``None`` at the ends of the sequence (and for a single process)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return None, None
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    mine = pack_boundary_frames(frame_params)
+    n = mine.numel() // 2
+    allb = torch.empty(world * 2 * n, dtype=mine.dtype, device=mine.device)
+    dist.all_gather_into_tensor(allb, mine, group=group)
+    allb = allb.view(world, 2, n)
+    return (allb[rank - 1, 1] if rank > 0 else None), (allb[rank + 1, 0] if rank + 1 < world else None)
+
+
+def with_prior_terms(loss_fn, num_frames_total: int, frame_offset: int, weights: Dict[str, float], window: int = 10,
+                     group=None, prior_fn=None, **consts):
+    """``loss_fn`` + the fitter's parameter-space terms (fitter.py:298-350) for :class:`ShardedFitterStep`.
+
+    The step divides what ``loss_fn`` returns by ``num_frames_total`` (the joint loss is a mean over all frames); the
+    prior terms carry their own per-window normalisation, so they enter multiplied by ``num_frames_total``.  With
+    ``w_temp > 0`` the shard boundaries are exchanged by :func:`exchange_halos` (one small all_gather per step, inside
+    the captured graph).  ``prior_fn`` defaults to the CUDA kernel (``fitter_terms.fitter_prior_terms``); the gloo CPU
+    tests inject a stand-in with the same signature."""
+    if prior_fn is None:
+        from .fitter_terms import fitter_prior_terms as prior_fn
+
+    def fn(fp, sp):
+        hp = hn = None
+        if weights.get("w_temp", 0.0) > 0.0:
+            hp, hn = exchange_halos(fp, group)
+        prior = prior_fn(fp["global_rotation"], fp["joint_rotations"], fp["trans"], sp.get("betas"), weights, window=window,
+                         frame_offset=frame_offset, total_frames=num_frames_total, halo_prev=hp, halo_next=hn, **consts)
+        return loss_fn(fp, sp) + prior * float(num_frames_total)
+
+    return fn
+
+
 class ShardedFitterStep:
     """One optimisation step of a frame-sharded joint fit.
 
@@ -111,8 +159,12 @@ class GraphedShardedFitterStep(ShardedFitterStep):
     optimiser); ``.grad`` tensors are allocated during capture and rewritten by every replay.  CUDA only."""
 
     def __init__(self, frame_params, shared_params, loss_fn, num_frames_total, group=None, warmup=3,
-                 capture_collective=True):
+                 capture_collective=True, optimizer=None):
         super().__init__(frame_params, shared_params, loss_fn, num_frames_total, group)
+        # optimizer: an object with a graph-capturable ``step()`` over the leaves (``fitter_terms.FusedAdam``): the update
+        # then runs inside the captured step, after the shared gradients are final (the whole of optimize_to_joints.py:
+        # 153-175 is one graph replay).  NOTE: the warm-up iterations below do NOT step it.
+        self.optimizer = optimizer
         leaves = list(frame_params.values()) + list(shared_params.values())
         if not leaves or not all(p.is_cuda for p in leaves):
             raise RuntimeError("GraphedShardedFitterStep needs CUDA leaf tensors (there is no CPU fallback)")
@@ -151,6 +203,10 @@ class GraphedShardedFitterStep(ShardedFitterStep):
                 dist.all_reduce(self._buf, op=dist.ReduceOp.SUM, group=self.group)
                 for p, g in zip(self._shared, unpack_grads(self._buf[:-1], self._shared)):
                     p.grad.copy_(g)
+            self._opt_in_graph = False
+            if self.optimizer is not None and (with_collective or not self._distributed):
+                self.optimizer.step()
+                self._opt_in_graph = True
 
     def _local(self):
         for p in list(self.frame_params.values()) + list(self.shared_params.values()):
@@ -171,6 +227,8 @@ class GraphedShardedFitterStep(ShardedFitterStep):
             with torch.no_grad():
                 for p, g in zip(self._shared, unpack_grads(buf[:-1], self._shared)):
                     p.grad.copy_(g)
+        if self.optimizer is not None and not self._opt_in_graph:
+            self.optimizer.step()
         return buf[-1]
 
 

@@ -209,3 +209,161 @@ def test_graphed_step_equals_eager_step():
     with pytest.raises(RuntimeError):
         FS.GraphedShardedFitterStep({k: v.detach().cpu().requires_grad_(True) for k, v in fp.items()},
                                     {k: v.detach().cpu().requires_grad_(True) for k, v in sp.items()}, fn, n)
+
+
+@pytest.mark.gpu
+def test_graphed_full_step_with_priors_and_fused_adam_follows_torch_adam():
+    """joint loss + parameter-space terms + Adam as ONE graph replay per optimisation step,
+    against the eager step driven by torch.optim.Adam (optimize_to_joints.py:117-126, :153-175)."""
+    import smilify_b200
+    from smilify_b200.fitter_terms import FusedAdam
+    from smilify_b200.smal_torch import SMAL
+
+    dd = rigs.get_rig("stick")
+    smilify_b200.configure(rigs.REAL_RIGS["stick"])
+    dev = torch.device("cuda:0")
+    model = SMAL(dev)
+    n = 23
+    frame, shared, R, T, target, vis = _problem(dd, n, dtype=torch.float32)
+    J = frame["joint_rotations"].shape[1] + 1
+    rs = np.random.RandomState(5)
+    f = lambda a: torch.from_numpy(np.asarray(a, dtype=np.float32)).to(dev)
+    consts = dict(max_limits=f(rs.uniform(0.1, 0.5, (J - 1, 3))), min_limits=f(-rs.uniform(0.1, 0.5, (J - 1, 3))),
+                  betas_mean=f(np.zeros(5)), betas_prec=f(np.eye(5) + 0.1 * rs.standard_normal((5, 5))))
+    weights = dict(w_limit=1.0, w_pose=0.5, w_splay=0.01, w_betas=0.3, w_temp=0.2)
+
+    def make():
+        fp = {k: v.to(dev).clone().requires_grad_(True) for k, v in frame.items()}
+        sp = {k: v.to(dev).clone().requires_grad_(True) for k, v in shared.items()}
+        fn = FS.with_prior_terms(FS.smal_joint_loss_fn(model, R.to(dev), T.to(dev), target.to(dev), vis.to(dev), get_skin=True),
+                                 n, 0, weights, window=10, **consts)
+        groups = [{"params": list(fp.values()) + [sp["betas"]], "lr": 5e-3}, {"params": [sp["fov"]], "lr": 1.0}]
+        return fp, sp, fn, groups
+
+    fp_g, sp_g, fn_g, groups_g = make()
+    graphed = FS.GraphedShardedFitterStep(fp_g, sp_g, fn_g, n, optimizer=FusedAdam(groups_g, lr=5e-3))
+    assert graphed._opt_in_graph
+    fp_e, sp_e, fn_e, groups_e = make()
+    eager = FS.ShardedFitterStep(fp_e, sp_e, fn_e, n)
+    opt = torch.optim.Adam(groups_e, lr=5e-3)
+    for it in range(4):
+        lg = float(graphed())
+        le = float(eager())
+        opt.step()
+        assert abs(lg - le) <= 2e-5 * abs(le), (it, lg, le)
+        for k, v in list(fp_e.items()) + list(sp_e.items()):
+            w = (fp_g if k in fp_g else sp_g)[k]
+            assert float((w - v).abs().max()) <= 2e-5 * float(v.abs().max()), (it, k)
+
+
+# ---- (f)2 host logic on the CPU: shards + halo exchange + prior terms, the oracle standing in for the kernel ----------
+def _oracle_prior_fn(global_rot, joint_rot, trans, betas, weights, window, frame_offset, total_frames, halo_prev, halo_next,
+                     **consts):
+    """Same signature and sharding semantics as ``fitter_terms.fitter_prior_terms``, built from oracle/fitter_oracle.py."""
+    import torch.nn.functional as F
+
+    from oracle import fitter_oracle as FO
+
+    n, N = global_rot.shape[0], int(total_frames)
+    total = torch.zeros((), dtype=global_rot.dtype)
+    ww = dict(weights)
+    for w0 in range((frame_offset // window) * window, frame_offset + n, window):
+        w1 = min(N, w0 + window)
+        a, b = max(w0, frame_offset) - frame_offset, min(w1, frame_offset + n) - frame_offset
+        part = dict(ww, w_betas=ww.get("w_betas", 0.0) if w0 >= frame_offset else 0.0)   # a window's betas term: once
+        objs = FO.window_objective(global_rot[a:b], joint_rot[a:b], betas, part, **consts)
+        frac = (b - a) / float(w1 - w0)                                                   # means run over the WHOLE window
+        for k, v in objs.items():
+            total = total + (v * frac if k in ("limit", "pose") else v)
+    wt = ww.get("w_temp", 0.0)
+    if wt > 0:
+        J3 = joint_rot.shape[1] * 3
+        seq = lambda h: (h[:3], h[3:3 + J3].reshape(-1, 3), h[3 + J3:])
+        pair = lambda A, Bb: (F.mse_loss(A[0], Bb[0]) + F.mse_loss(A[1], Bb[1]) + F.mse_loss(A[2], Bb[2])) * wt
+        fr = lambda i: (global_rot[i], joint_rot[i], trans[i])
+        for i in range(n - 1):
+            total = total + pair(fr(i), fr(i + 1))
+        if halo_next is not None:
+            total = total + pair(fr(n - 1), seq(halo_next.to(global_rot.dtype)))
+        if halo_prev is not None:   # counted by the rank before: gradient only
+            t = pair(seq(halo_prev.to(global_rot.dtype)), fr(0))
+            total = total + (t - t.detach())
+    return total
+
+
+_PRIOR_W = dict(w_limit=0.7, w_pose=1.3, w_splay=0.05, w_betas=0.9, w_temp=0.4)
+
+
+def _prior_consts(J, nB, dtype=torch.float64):
+    rs = np.random.RandomState(9)
+    t = lambda a: torch.from_numpy(np.asarray(a)).to(dtype)
+    return dict(max_limits=t(rs.uniform(0.1, 0.4, (J - 1, 3))), min_limits=t(-rs.uniform(0.1, 0.4, (J - 1, 3))),
+                betas_mean=t(rs.normal(0, 0.1, nB)), betas_prec=t(rs.normal(0, 1, (nB, nB))),
+                pose_prior=None)
+
+
+def _prior_worker(rank, world, port, out_q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(1)
+        from oracle import fitter_oracle as FO
+
+        dd = rigs.get_rig("syn_k3")
+        frame, shared, R, T, target, vis = _problem(dd, N_FRAMES)
+        J, nB = frame["joint_rotations"].shape[1] + 1, shared["betas"].numel()
+        consts = _prior_consts(J, nB)
+        consts["pose_prior"] = FO.identity_pose_prior(J)
+        lo, hi = FS.shard_range(N_FRAMES, rank, world)
+        model = SO.build_model(dd, dtype=torch.float64)
+        fp = {k: v[lo:hi].clone().requires_grad_(True) for k, v in frame.items()}
+        sp = {k: v.clone().requires_grad_(True) for k, v in shared.items()}
+        fn = FS.with_prior_terms(_oracle_loss_fn(model, R, T, target[lo:hi], vis[lo:hi]), N_FRAMES, lo, _PRIOR_W, window=4,
+                                 prior_fn=_oracle_prior_fn, **consts)
+        hp, hn = FS.exchange_halos(fp)
+        loss = FS.ShardedFitterStep(fp, sp, fn, N_FRAMES)()
+        out_q.put((rank, lo, hi, float(loss), {k: v.grad.numpy() for k, v in fp.items()}, {k: v.grad.numpy() for k, v in sp.items()},
+                   None if hp is None else hp.numpy(), None if hn is None else hn.numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_gloo_world2_prior_terms_with_halos_match_single_process():
+    from oracle import fitter_oracle as FO
+
+    dd = rigs.get_rig("syn_k3")
+    frame, shared, R, T, target, vis = _problem(dd, N_FRAMES)
+    J, nB = frame["joint_rotations"].shape[1] + 1, shared["betas"].numel()
+    consts = _prior_consts(J, nB)
+    consts["pose_prior"] = FO.identity_pose_prior(J)
+    model = SO.build_model(dd, dtype=torch.float64)
+    fp = {k: v.clone().requires_grad_(True) for k, v in frame.items()}
+    sp = {k: v.clone().requires_grad_(True) for k, v in shared.items()}
+    joint = _oracle_loss_fn(model, R, T, target, vis)(fp, sp) / N_FRAMES
+    ref = joint + FO.epoch_objective(fp["global_rotation"], fp["joint_rotations"], fp["trans"], sp["betas"], _PRIOR_W, 4, **consts)
+    ref.backward()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_prior_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    full = lambda i: np.concatenate([frame["global_rotation"][i].numpy().ravel(), frame["joint_rotations"][i].numpy().ravel(),
+                                     frame["trans"][i].numpy().ravel()]).astype(np.float32)
+    for rank, lo, hi, loss, fg, sg, hp, hn in res:
+        assert abs(loss - float(ref)) <= 1e-6 * abs(float(ref))
+        assert (hp is None) == (lo == 0) and (hn is None) == (hi == N_FRAMES)
+        if hp is not None:
+            np.testing.assert_array_equal(hp, full(lo - 1))     # the LAST frame of the rank before
+        if hn is not None:
+            np.testing.assert_array_equal(hn, full(hi))         # the FIRST frame of the rank after
+        for k in fg:
+            np.testing.assert_allclose(fg[k], fp[k].grad[lo:hi].numpy(), rtol=1e-7, atol=1e-12)
+        for k in sg:
+            np.testing.assert_allclose(sg[k], sp[k].grad.numpy(), rtol=2e-6, atol=1e-9)

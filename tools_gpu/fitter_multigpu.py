@@ -48,7 +48,20 @@ def frame_block(lo, hi, J, block=4096):
     return {k: np.concatenate(v) for k, v in out.items()}
 
 
-def run_fitter(frames, steps, warmup, rank, world, dev, rig="stick13", graph=True, get_skin=True, check=True):
+def prior_setup(J, nB, dev):
+    """Synthetic constants of the parameter-space terms (fitter.py:298-350) for the full-step record: joint limits,
+    the identity pose prior of fitter.py:25-52 (kernel default), a betas precision, masks; the weights of a late
+    optimisation stage."""
+    rs = np.random.RandomState(11)
+    f = lambda a: torch.from_numpy(np.asarray(a, dtype=np.float32)).to(dev)
+    consts = dict(max_limits=f(rs.uniform(0.2, 0.8, (J - 1, 3))), min_limits=f(-rs.uniform(0.2, 0.8, (J - 1, 3))),
+                  betas_mean=f(np.zeros(nB)), betas_prec=f(np.eye(nB) + 0.05 * rs.standard_normal((nB, nB))),
+                  rotation_mask=f(np.ones((J - 1, 3))), global_mask=f(np.ones((1, 3))))
+    weights = dict(w_limit=1.0, w_pose=0.5, w_splay=0.01, w_betas=0.3, w_temp=0.2)
+    return consts, weights
+
+
+def run_fitter(frames, steps, warmup, rank, world, dev, rig="stick13", graph=True, get_skin=True, check=True, full_step=False):
     """One frame-sharded SMALFitter-style step timed on this rank's device (the process group, if any, is initialised
     by the caller).  Returns the result dict on rank 0 (None elsewhere).  ``rig``: "stick13" is the OmniAnt stand-in of
     SURVEY.md section 8(d) config 4 (STICK geometry, shape space padded to nB = 13)."""
@@ -73,10 +86,23 @@ def run_fitter(frames, steps, warmup, rank, world, dev, rig="stick13", graph=Tru
 
     lo, hi = FS.shard_range(frames, rank, world)
     fp, sp, fn = build(lo, hi)
+    optimizer = None
+    if full_step:
+        # (f)2: + joint limits / pose prior / splay / betas prior / temporal smoothness (1-frame halos between the
+        # shards) + the fused Adam of optimize_to_joints.py:117-126, all inside the captured step
+        from smilify_b200.fitter_terms import FusedAdam
+
+        consts, weights = prior_setup(J, nB, dev)
+        fn = FS.with_prior_terms(fn, frames, lo, weights, window=10, **consts)
+        optimizer = FusedAdam([{"params": [fp["global_rotation"], fp["joint_rotations"], fp["trans"], sp["betas"]], "lr": 5e-3},
+                               {"params": [sp["fov"]], "lr": 1.0}], lr=5e-3)
     c0 = _lib.launch_count()
-    FS.ShardedFitterStep(fp, sp, fn, frames)()          # one eager step: counts the kernels a step launches
+    loss0 = FS.ShardedFitterStep(fp, sp, fn, frames)()   # one eager step: counts the kernels a step launches
     per_step = _lib.launch_count() - c0
-    step = (FS.GraphedShardedFitterStep if graph else FS.ShardedFitterStep)(fp, sp, fn, frames)
+    g_first = {k: v.grad.detach().clone() for k, v in sp.items()}   # at the INITIAL parameters (the optimiser moves them)
+    loss_first = float(loss0)
+    kw = dict(optimizer=optimizer) if (graph and optimizer is not None) else {}
+    step = (FS.GraphedShardedFitterStep if graph else FS.ShardedFitterStep)(fp, sp, fn, frames, **kw)
 
     def barrier():
         if world > 1:
@@ -110,8 +136,8 @@ def run_fitter(frames, steps, warmup, rank, world, dev, rig="stick13", graph=Tru
         t = torch.tensor([ms, ar_us], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, ar_us = float(t[0].item()), float(t[1].item())
-    g_sharded = {k: v.grad.detach().clone() for k, v in sp.items()}
-    loss_sharded = float(loss)
+    g_sharded, loss_sharded = g_first, loss_first
+    loss_last = float(loss)
 
     # single-process run over ALL frames on rank 0 (chunked accumulation): what the sharded gradients must equal
     chk = None
@@ -125,13 +151,24 @@ def run_fitter(frames, steps, warmup, rank, world, dev, rig="stick13", graph=Tru
             tot += float(part.detach())
             for k in acc:
                 acc[k] += spc[k].grad
+        if full_step:   # the parameter-space terms over the WHOLE sequence in one call (no halos needed)
+            from smilify_b200.fitter_terms import fitter_prior_terms
+
+            fpa, spa, _ = build(0, frames)
+            pr = fitter_prior_terms(fpa["global_rotation"], fpa["joint_rotations"], fpa["trans"], spa["betas"], weights, window=10, **consts)
+            pr.backward()
+            tot += float(pr.detach())
+            acc["betas"] += spa["betas"].grad
         chk = {k: float((g_sharded[k] - acc[k]).abs().max() / acc[k].abs().max().clamp_min(1e-30)) for k in acc}
         chk["loss"] = abs(loss_sharded - tot) / abs(tot)
     if rank != 0:
         return None
     in_graph = bool(getattr(step, "collective_in_graph", False))
     return {
-        "metric": "SMALFitter-style frames/s (SMAL fwd+bwd + joint reprojection loss, shared betas/fov)",
+        "metric": ("SMALFitter-style frames/s (SMAL fwd+bwd + joint reprojection loss + limits / pose prior / splay / betas "
+                   "prior / temporal terms + fused Adam, shared betas/fov)") if full_step else
+                  "SMALFitter-style frames/s (SMAL fwd+bwd + joint reprojection loss, shared betas/fov)",
+        "full_step": bool(full_step), "optimizer_in_graph": bool(getattr(step, "_opt_in_graph", False)), "loss_last": loss_last,
         "value": frames / ms * 1e3, "frames_per_s": frames / ms * 1e3, "unit": "frames/s", "n_gpus": world, "ms_per_step": ms,
         "steps": steps, "warmup": warmup, "frames_total": frames, "frames_per_gpu": hi - lo, "scaling": "strong",
         "collective": "1 all_reduce(SUM) per step, %d bytes (g_betas, g_fov, loss)" % step.collective_bytes,
