@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define SMIL_ABI_VERSION 6
+#define SMIL_ABI_VERSION 7
 
 enum {
   SMIL_OK = 0,

@@ -11,7 +11,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsmil_b200.so")
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 c_f = C.POINTER(C.c_float)
 c_i = C.POINTER(C.c_int32)
