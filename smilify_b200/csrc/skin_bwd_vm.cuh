@@ -108,13 +108,15 @@ __global__ void __launch_bounds__(128) skin_bwd_vm_kernel(DevModel m, SkinBwdVmA
   const int first_seg = [&]() { for (int p = 0; p < NPH; ++p) if (wsp[NW * p + warp] < wsp[NW * p + warp + 1]) return wsp[NW * p + warp] - seg_base; return -1; }();
   // producer (warp 0, all lanes): lane r issues the bulk copy of sample row r of one phase (16-byte aligned superset of
   // the phase's float range); the byte total is folded with one warp reduction before lane 0 arms the barrier
-  auto phase_n = [&](int p) { return 3 * max(0, min(PW, V - ti * C - p * PW)); };
+  // a tile is the vertex range [rec_base, rec_base + rec_cnt): one record per vertex, tiles consecutive; the packer
+  // sizes the tiles for equal estimated COST (not equal vertex counts), C = vm_chunk is only their upper bound
+  auto phase_n = [&](int p) { return 3 * max(0, min(PW, rec_cnt - p * PW)); };
   auto issue = [&](int grp, int p) {
     const int b0 = grp * SKIN_BWD_G;
     const int Gn = min(SKIN_BWD_G, a.B - b0);
     const int n = phase_n(p);
     const bool act = lane < Gn && n > 0;
-    const long long off = ((long long)(b0 + lane) * V + (long long)ti * C + (long long)p * PW) * 3;
+    const long long off = ((long long)(b0 + lane) * V + (long long)rec_base + (long long)p * PW) * 3;
     const int ph = (int)(off & 3);
     long long len = (ph + n + 3) & ~3;
     if (off - ph + len > a.total_floats) len -= 4;  // never read past the buffer; tail fixed up below
@@ -187,11 +189,11 @@ __global__ void __launch_bounds__(128) skin_bwd_vm_kernel(DevModel m, SkinBwdVmA
 
     for (int p = 0; p < NPH; ++p) {
       const int n = phase_n(p);
-      const long long off = ((long long)bb * V + (long long)ti * C + (long long)p * PW) * 3;
+      const long long off = ((long long)bb * V + (long long)rec_base + (long long)p * PW) * 3;
       mbar_wait(&bars[p], parity);
       {   // the (at most 3) floats a clipped superset load left out (last sample, last tile, last phase only): plain
           // loads by the owning lanes; the condition is the same for the whole CTA
-        const long long offl = ((long long)min(b0 + SKIN_BWD_G - 1, a.B - 1) * V + (long long)ti * C + (long long)p * PW) * 3;
+        const long long offl = ((long long)min(b0 + SKIN_BWD_G - 1, a.B - 1) * V + (long long)rec_base + (long long)p * PW) * 3;
         const int phl = (int)(offl & 3);
         if (n > 0 && offl - phl + ((phl + n + 3) & ~3) > a.total_floats) {
           const int ph = (int)(off & 3);

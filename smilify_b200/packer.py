@@ -95,7 +95,7 @@ def tree_tables(parents: np.ndarray):
     )
 
 
-PACK_FORMAT = 8   # bump when the meaning of a packed table changes: invalidates cached packs
+PACK_FORMAT = 9   # bump when the meaning of a packed table changes: invalidates cached packs
 
 
 def pack_model_cached(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static=None, cache_dir=None):
@@ -110,7 +110,7 @@ def pack_model_cached(v_template, shapedirs, posedirs, J_regressor, weights, par
         if cache_dir is None else cache_dir
     if not cache_dir:
         return pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static)
-    h = hashlib.sha1(repr((PACK_FORMAT, FWD_CHUNK, BWD_CHUNK, VM_CHUNK, VM_PHASES, VM_WARPS, VM_CUT_TOL, VM_SEG_COST, VM_FLUSH_COST,
+    h = hashlib.sha1(repr((PACK_FORMAT, FWD_CHUNK, BWD_CHUNK, VM_CHUNK, VM_PHASES, VM_WARPS, VM_CUT_TOL, VM_SEG_COST, VM_FLUSH_COST, VM_TILE_BALANCE, VM_CHUNK_MAX,
                            sorted((k, v) for k, v in _os.environ.items() if k.startswith("SMIL_")))).encode())
     for a in (v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static):
         a = np.ascontiguousarray(np.asarray(a)) if a is not None else np.zeros(0)
@@ -277,7 +277,7 @@ def pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J
     t["fused_ok"] = bool(K <= MAX_FUSED_K and nbt_of(nB) > 0 and P == 0)
     t["vm_ok"] = False
     if t["fused_ok"] and K <= 2 and _os.environ.get("SMIL_BWD_VM", "1") != "0":
-        t.update(pack_backward_vm(vt, S3, idx, val, nnz_row, J, nB))
+        t.update(pack_backward_vm_balanced(vt, S3, idx, val, nnz_row, J, nB))
     return t
 
 
@@ -668,7 +668,90 @@ def _vm_order_runs(combos, X=None, Y=None, lv0=0):
     return ops, (X, Y)
 
 
-def pack_backward_vm(vt, S3, idx, val, nnz_row, J, nB, chunk=None, nwarps=None, nphase=None):
+VM_CHUNK_MAX = int(_os.environ.get("SMIL_VM_CHUNK_MAX", "180"))       # upper bound of a tile after balancing (55.6 KB of shared memory)
+VM_TILE_BALANCE = int(_os.environ.get("SMIL_VM_TILE_BALANCE", "4"))   # re-packing rounds that equalise the tiles' cost (0: equal vertex counts)
+
+
+def _vm_tile_costs(t, nwarps):
+    """Estimated cost of every tile of a vertex-major pack: its most loaded warp (vertices + weighted segment switches
+    and flushes, the same model the warp cuts use) -- the warps of a CTA meet at a barrier after every sample group."""
+    wsp, seg = t["vm_warp_seg_ptr"], t["vm_seg"].reshape(-1, 8)
+    nph = t["vm_nphase"]
+    out = []
+    for ti in range(t["vm_ntile"]):
+        worst = 0.0
+        for w in range(nwarps):
+            c = 0.0
+            for ph in range(nph):
+                s0, s1 = wsp[(ti * nph + ph) * nwarps + w], wsp[(ti * nph + ph) * nwarps + w + 1]
+                sg = seg[s0:s1]
+                c += float(sg[:, 3].sum()) + VM_SEG_COST * (s1 - s0) + VM_FLUSH_COST * float((sg[:, 4] >= 0).sum() + (sg[:, 5] >= 0).sum())
+            worst = max(worst, c)
+        out.append(worst)
+    return np.asarray(out)
+
+
+def pack_backward_vm_balanced(vt, S3, idx, val, nnz_row, J, nB, rounds=None):
+    """:func:`pack_backward_vm` with the tile boundaries moved so that every tile has about the same estimated cost.
+    All tiles of the pass are resident at once (one CTA per (tile, sample-group column)), so the pass ends with its most
+    expensive tile: with equal vertex counts that tile was 14 % (STICK) / 33 % (mouse) over the mean.  The cost of a tile is
+    not additive in its vertices (it depends on where the bone runs fall), so the boundaries are found by bisection on the
+    cost bound T: left to right, every tile takes the most vertices (a multiple of 4, at most ``VM_CHUNK_MAX``) whose
+    single-tile pack costs at most T; the smallest T for which the tiles cover the mesh wins.  Single-tile packs are
+    memoised; the whole search takes a few seconds per rig and its result lives in the on-disk pack cache.
+    Measured on B200 (B = 4096): skin_bwd_vm 92.0 -> 87.8 us on STICK (estimated worst tile 83 -> 74), 293.8 -> 260.2 us
+    on the mouse rig (78 -> 65, and 713 -> 678 flush slots)."""
+    rounds = VM_TILE_BALANCE if rounds is None else rounds
+    V = vt.shape[0]
+    base = pack_backward_vm(vt, S3, idx, val, nnz_row, J, nB)
+    nt, nw = base["vm_ntile"], base["vm_warps"]
+    if rounds <= 0 or nt < 2 or base["vm_nphase"] != 1:
+        return base
+    cmax = max(base["vm_chunk"], VM_CHUNK_MAX)   # light tiles may grow up to here (shared-memory bound: 4 CTAs per SM)
+    memo = {}
+
+    def tile_cost(v0, v1):
+        if (v0, v1) not in memo:
+            n = v1 - v0
+            t1 = pack_backward_vm(vt[v0:v1], S3[:, v0:v1], idx[v0:v1], val[v0:v1], nnz_row[v0:v1], J, nB,
+                                  chunk=(n + 3) // 4 * 4, tile_starts=[0, n])
+            memo[(v0, v1)] = float(_vm_tile_costs(t1, nw)[0])
+        return memo[(v0, v1)]
+
+    def partition(T):
+        starts = [0]
+        for _ in range(nt):
+            v0 = starts[-1]
+            if v0 >= V:
+                break
+            n = min(cmax, V - v0)
+            n = n if v0 + n == V else n // 4 * 4
+            while n > 8 and tile_cost(v0, v0 + n) > T:
+                n = (n - 1) // 4 * 4
+            starts.append(v0 + n)
+        return starts if starts[-1] == V else None
+
+    base_cost = _vm_tile_costs(base, nw)
+    hi, lo = float(base_cost.max()), float(base_cost.mean()) * 0.9
+    best = None
+    for _ in range(max(rounds, 1) + 3):
+        mid = 0.5 * (lo + hi)
+        st = partition(mid)
+        if st is None:
+            lo = mid
+        else:
+            best, hi = st, mid
+    if best is None:
+        return base
+    while len(best) - 1 < nt:          # fewer tiles than CTAs columns: split the largest (keeps the grid shape)
+        sizes = np.diff(best)
+        i = int(np.argmax(sizes))
+        best = best[:i + 1] + [best[i] + int(sizes[i]) // 8 * 4] + best[i + 1:]
+    out = pack_backward_vm(vt, S3, idx, val, nnz_row, J, nB, chunk=(int(np.diff(best).max()) + 3) // 4 * 4, tile_starts=best)
+    return out if _vm_tile_costs(out, nw).max() < base_cost.max() else base
+
+
+def pack_backward_vm(vt, S3, idx, val, nnz_row, J, nB, chunk=None, nwarps=None, nphase=None, tile_starts=None):
     """Vertex-major tables of the fused backward skin pass (``skin_bwd_vm_kernel``).
 
     A tile is ``chunk`` consecutive vertices cut into ``nphase`` PHASES (sub-ranges that start on a multiple of four
@@ -691,6 +774,13 @@ def pack_backward_vm(vt, S3, idx, val, nnz_row, J, nB, chunk=None, nwarps=None, 
     chunk = max(q, (chunk + q - 1) // q * q)   # phases start on 16-byte boundaries of a row when 3V % 4 == 0
     pw = chunk // nphase                       # vertices per phase
     ntile = (V + chunk - 1) // chunk
+    if tile_starts is not None:                # explicit tile boundaries (pack_backward_vm_balanced); chunk = upper bound
+        if nphase != 1:
+            raise ValueError("explicit tile boundaries need nphase = 1")
+        tile_starts = [int(x) for x in tile_starts]
+        ntile = len(tile_starts) - 1
+        if tile_starts[0] != 0 or tile_starts[-1] != V or any(b <= a or b - a > chunk for a, b in zip(tile_starts, tile_starts[1:])):
+            raise ValueError("tile boundaries must cover [0, V) with 1..chunk vertices per tile")
     nbt = max(nbt_of(nB), 1)
     recf = vm_rec_floats(nbt)
     Sv = S3.transpose(1, 0, 2)  # (V, nB, 3)
@@ -699,7 +789,7 @@ def pack_backward_vm(vt, S3, idx, val, nnz_row, J, nB, chunk=None, nwarps=None, 
     flush_bone = []          # bone of every flush, in creation order; slot ids are assigned bone-major afterwards
     max_tile_recs = max_tile_segs = 0
     for ti in range(ntile):
-        v0, v1 = ti * chunk, min(V, (ti + 1) * chunk)
+        v0, v1 = (ti * chunk, min(V, (ti + 1) * chunk)) if tile_starts is None else (tile_starts[ti], tile_starts[ti + 1])
         wts = [{int(idx[v, s]): float(val[v, s]) for s in range(int(nnz_row[v]))} for v in range(v0, v1)]
         tile_first_seg = len(segs)
         cur = [[None, None] for _ in range(nwarps)]       # bones in the warps' slots X / Y

@@ -164,7 +164,7 @@ def skin_backward_vm(t, beta, GR, gv):
                         wX, wY = r[0], r[1]
                         lv = int(t["vm_rec"][it, 2].view(np.int32)) // 3
                         assert 0 <= lv < PW
-                        v = ti * C + ph * PW + lv
+                        v = int(rbase) + ph * PW + lv   # tiles are consecutive vertex ranges, one record per vertex
                         seen[v] += 1
                         g = gv[:, v]
                         S_ = r[6:6 + 3 * nB].reshape(nB, 3)[:nb]
