@@ -408,7 +408,7 @@ def run_ours(args, rank, world, local_rank):
     else:
         from smilify_b200.graphed import HostPipeline
 
-        pipe = HostPipeline(model, B, depth=2, pack_joints=False)
+        pipe = HostPipeline(model, B, depth=args.e2e_depth, pack_joints=False)
         for sl in pipe.slots:
             with torch.no_grad():
                 sl["step"].g_verts.copy_(gs.g_verts); sl["step"].g_joints.copy_(gs.g_joints)
@@ -426,7 +426,7 @@ def run_ours(args, rank, world, local_rank):
                     sink[0] += float(done["grad_trans"][0, 0])   # the caller reads the finished step's result
             for done in pipe.drain():
                 sink[0] += float(done["grad_trans"][0, 0])
-        e2e_mode = ("HostPipeline depth 2: per step ONE pinned host->device copy (beta | theta | trans) and ONE "
+        e2e_mode = ("HostPipeline depth %d: per step" % args.e2e_depth + " ONE pinned host->device copy (beta | theta | trans) and ONE "
                     "device->host copy (the parameter gradients: the step's result) overlap the kernels of neighbouring steps; "
                     "posed vertices, joints and upstream gradients stay device-resident (the loss lives on the device)")
 
@@ -560,6 +560,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="time the eager Python call instead of the graph replay")
     ap.add_argument("--cpu-batch", type=int, default=4096, help="meshes per CPU step (4096 = the full batch of a step)")
     ap.add_argument("--no-torch-gpu", action="store_true", help="skip the torch-on-the-same-GPU comparator")
+    ap.add_argument("--e2e-depth", type=int, default=3, help="graphed buffer sets of the host pipeline (copies of neighbouring steps overlap the kernels)")
     ap.add_argument("--no-fitter", action="store_true", help="N > 1: skip the frame-sharded fitter step (the NCCL path)")
     ap.add_argument("--fitter-frames", type=int, default=65536)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
