@@ -41,6 +41,16 @@ METRIC = "fwd+bwd posed meshes/s (SMIL LBS, B=4096)"
 UNIT = "meshes/s"
 
 
+def rig_path(name):
+    """On-disk rig file: the two shipped pickles, or a stand-in written to a temp .npz by tests/common.py."""
+    from tests import rigs
+    if name in rigs.REAL_RIGS:
+        return rigs.REAL_RIGS[name]
+    from tests.common import rig_file
+
+    return rig_file(name)
+
+
 def algorithmic_bytes(V, J, nB):
     """fp32, every tensor of the call contract moved exactly once."""
     n_in = nB + 3 * J + 3
@@ -274,7 +284,7 @@ def run_reference(args, rank, world):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     Bs = args.cpu_batch
-    step, V, J, nB = cpu_step_fn(rigs.REAL_RIGS[args.rig], Bs)
+    step, V, J, nB = cpu_step_fn(rig_path(args.rig), Bs)
     for _ in range(args.warmup):
         step()
     t0 = time.perf_counter()
@@ -287,7 +297,7 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "SMILy_STICK.pkl fwd+bwd batch %d synthetic poses (CPU arm: %d-mesh sample per step)"
+        "config": {"workload": ("SMILy_STICK.pkl" if args.rig == "stick" else args.rig + " rig") + " fwd+bwd batch %d synthetic poses (CPU arm: %d-mesh sample per step)"
                                % (args.batch, Bs), "rig": args.rig, "V": V, "J": J, "nB": nB, "batch_per_gpu": args.batch},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -314,7 +324,7 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     cores_pinned = pin_rank_to_cores(local_rank, world) if world > 1 else None
-    smilify_b200.configure(rigs.REAL_RIGS[args.rig])
+    smilify_b200.configure(rig_path(args.rig))
     model = SMAL(dev)
     V, J, nB = model._tables["V"], model._tables["J"], model.num_betas
     B, K, W = args.batch, args.steps, args.warmup
@@ -500,25 +510,26 @@ def run_ours(args, rank, world, local_rank):
         # the same step with the fitter's parameter-space terms (halo exchange for the temporal term) and the fused Adam
         # inside the graph: SURVEY.md section 8(f) row 2
         fitter_full = fm.run_fitter(args.fitter_frames, max(5, min(K, 20)), 3, rank, world, dev, rig="stick13", full_step=True)
-        smilify_b200.configure(rigs.REAL_RIGS[args.rig])
+        smilify_b200.configure(rig_path(args.rig))
     if rank != 0:
         return
     torch_gpu = None
     if world == 1 and not args.no_torch_gpu:
         try:
-            torch_gpu = torch_gpu_baseline(rigs.REAL_RIGS[args.rig], B, dev)
+            torch_gpu = torch_gpu_baseline(rig_path(args.rig), B, dev)
         except Exception as e:   # e.g. out of memory on a smaller part: the dense graph materialises (B, V, J) tensors
             torch_gpu = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:120])}
     peak, peak_src = measured_peaks()
     ms_step = ms_total / K
     value = world * B * K / (ms_total * 1e-3)
     step_gbs = (fwd_b + bwd_b) * B / (ms_step * 1e-3) / 1e9
-    cpu_val, cores, n_it = time_cpu(rigs.REAL_RIGS[args.rig], args.cpu_batch, args.cpu_seconds) if world == 1 else (None, None, 0)
+    cpu_val, cores, n_it = time_cpu(rig_path(args.rig), args.cpu_batch, args.cpu_seconds) if world == 1 else (None, None, 0)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": "SMILy_STICK.pkl fwd+bwd batch %d synthetic poses per GPU (BASELINE configs[1])" % B,
+        "config": {"workload": ("SMILy_STICK.pkl fwd+bwd batch %d synthetic poses per GPU (BASELINE configs[1])" % B) if args.rig == "stick"
+                   else "%s rig fwd+bwd batch %d synthetic poses per GPU" % (args.rig, B),
                    "rig": args.rig, "V": V, "J": J, "nB": nB, "batch_per_gpu": B, "global_batch": B * world,
                    "parallelism": "frames sharded, dp%d, no collective" % world,
                    "launch": "eager" if args.no_graph else "cuda-graph replay of SMAL.__call__ + autograd",
@@ -555,7 +566,8 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--rig", default="stick", choices=["stick", "mouse"])
+    ap.add_argument("--rig", default="stick", choices=["stick", "mouse", "stick13", "mouse40"],
+                    help="stick13 / mouse40: the stand-ins for the missing BASELINE rigs (nB = 13 OmniAnt, J = 40 Falkner mouse)")
     ap.add_argument("--batch", type=int, default=4096, help="meshes per GPU per step")
     ap.add_argument("--no-graph", action="store_true", help="time the eager Python call instead of the graph replay")
     ap.add_argument("--cpu-batch", type=int, default=4096, help="meshes per CPU step (4096 = the full batch of a step)")
