@@ -9,7 +9,8 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "smilify_b200", "libsmil_b200.so")
-KEEP = [r"pose_fwd_kernel", r"skin_fwd_kernelILi5", r"skin_bwd_vm_kernelILi5", r"pose_bwd_lean_kernel", r"skin_bwd_kernelILi5",
+KEEP = [r"pose_fwd_ls_kernelILi8", r"skin_fwd_kernelILi5", r"skin_bwd_vm_kernelILi5", r"pose_bwd_ls_kernelILi8", r"pose_fwd_kernel",
+        r"pose_bwd_lean_kernel", r"skin_bwd_kernelILi5", r"fitter_prior", r"adam_step",
         r"slot_reduce", r"skin_fwd_kernelILi3", r"skin_bwd_vm_kernelILi3", r"keypoint|proj_", r"tri_fwd|tri_bwd", r"rot6d"]
 COLS = ["UBLKCP", "SYNCS", "FFMA", "FFMA2", "FMUL2|FADD2", "LDS", "STS", "LDG", "STG", "REDG|RED|ATOMG|ATOM", "BAR", "SHFL", "MUFU", "DFMA|DADD|DMUL"]
 
