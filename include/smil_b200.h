@@ -232,7 +232,7 @@ typedef struct SmilBwdArgs {
   float* g_trans;             /* [B][3] */
   float* g_logscale;          /* [B][J][3] */
   float* g_btrans;            /* [B][J][3] */
-  float* g_del_v;             /* [B][V][3] */
+  float* g_del_v;             /* [B][V][3] dL/d(v_shaped) per sample: gradient of del_v; summed over B = gradient of a v_template override */
   void* scratch; size_t scratch_bytes;  /* >= smil_bwd_scratch_bytes(...) */
 } SmilBwdArgs;
 

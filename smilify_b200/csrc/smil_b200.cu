@@ -1015,7 +1015,7 @@ int smil_backward(const SmilModel* model, const SmilBwdArgs* g, void* stream) {
   if ((rc = launch_pose(m, pa, true, st)) != SMIL_OK) return rc;
   prof_begin("vshaped_grad_kernel", st);
   vshaped_grad_kernel<<<blocks_for(nbv, 256), 256, 0, st>>>(m, B, g_vp, g->g_v_shaped, p.is_static ? nullptr : g_jrest,
-                                                            f->del_v ? g->g_del_v : nullptr);
+                                                            g->g_del_v);   // dL/d(v_shaped) per sample: the gradient of del_v and, summed over the batch by the caller, of a v_template override
   SMIL_LAUNCH_CHECK("vshaped_grad_kernel");
   if (g->g_beta && nb > 0) {
     prof_begin("shape_bwd_kernel", st);

@@ -232,7 +232,8 @@ class SmalFunction(torch.autograd.Function):
             o_beta = _empty((B, nb), **opts) if (need[3] and nb > 0 and shape_path) else None
             o_theta = _empty(tuple(theta.shape), **opts) if need[4] else None
             o_trans = _empty((B, 3), **opts) if (need[5] and trans is not None and shape_path) else None
-            o_delv = _empty((B, V, 3), **opts) if (need[6] and del_v is not None and shape_path) else None
+            want_vt = need[2] and v_template is not None and shape_path   # smal_torch.py:223-232: v_template is differentiable too
+            o_delv = _empty((B, V, 3), **opts) if (((need[6] and del_v is not None) or want_vt) and shape_path) else None
             o_ls = _empty((B, J, 3), **opts) if (need[7] and ls is not None) else None
             o_bt = _empty((B, J, 3), **opts) if (need[8] and bt is not None) else None
             g.g_beta = o_beta.data_ptr() if o_beta is not None else None
@@ -244,9 +245,12 @@ class SmalFunction(torch.autograd.Function):
             scratch = _empty(L.smil_bwd_scratch_bytes(dm.handle, C.byref(g)), device=dev, dtype=torch.uint8)
             g.scratch, g.scratch_bytes = scratch.data_ptr(), scratch.numel()
             _lib.check(L.smil_backward(dm.handle, C.byref(g), _stream()), "smil_backward")
+        o_vt = o_delv.sum(0) if (o_delv is not None and want_vt) else None
+        if not (need[6] and del_v is not None):
+            o_delv = None
         if o_delv is not None and ctx.del_v_shape != (B, V, 3):
             o_delv = o_delv.sum(0).reshape(ctx.del_v_shape)
-        return None, None, None, o_beta, o_theta, o_trans, o_delv, o_ls, o_bt
+        return None, None, o_vt, o_beta, o_theta, o_trans, o_delv, o_ls, o_bt
 
 
 class RodriguesFunction(torch.autograd.Function):

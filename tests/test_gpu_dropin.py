@@ -114,3 +114,36 @@ def test_errors_are_python_exceptions_not_aborts():
     wrong = m(t["beta"], torch.zeros(3, 7, 3, device=DEV), trans=t["trans"])   # wrong-width pose -> zeros (smal_torch.py:281-286)
     zero = m(t["beta"], torch.zeros(3, 55, 3, device=DEV), trans=t["trans"])
     assert torch.equal(wrong[0], zero[0])
+
+
+def test_v_template_override_is_differentiable():
+    """The reference graph differentiates through ``v_template`` (smal_torch.py:223-232: v_shaped = v_template + blend);
+    the CUDA path returns the batch sum of dL/dv_shaped."""
+    import smilify_b200
+    from oracle import smal_oracle as SO
+    from smilify_b200.smal_torch import SMAL
+    from tests import rigs
+    from tests.common import TOL, rel
+
+    dd = rigs.get_rig("stick")
+    smilify_b200.configure(rigs.REAL_RIGS["stick"])
+    dev = torch.device("cuda:0")
+    model = SMAL(dev)
+    B = 3
+    inp = rigs.make_inputs(dd, B, seed=4)
+    rs = np.random.RandomState(2)
+    V = np.asarray(dd["v_template"]).shape[0]
+    vt = (np.asarray(dd["v_template"]) + 0.01 * rs.standard_normal((V, 3))).astype(np.float32)
+    gv = rs.standard_normal((B, V, 3)).astype(np.float32)
+    t = {k: torch.from_numpy(inp[k]).to(dev).requires_grad_(True) for k in ("beta", "theta", "trans")}
+    vt_c = torch.from_numpy(vt).to(dev).requires_grad_(True)
+    verts, joints, _, _ = model(t["beta"], t["theta"], trans=t["trans"], v_template=vt_c)
+    (verts * torch.from_numpy(gv).to(dev)).sum().backward()
+    m = SO.build_model(dd, dtype=torch.float64)
+    o = {k: torch.from_numpy(inp[k]).double().requires_grad_(True) for k in ("beta", "theta", "trans")}
+    vt_o = torch.from_numpy(vt).double().requires_grad_(True)
+    out = SO.smal_forward_full(m, o["beta"], o["theta"], o["trans"], None, None, None, vt_o, False, True, True)
+    (out["verts"] * torch.from_numpy(gv).double()).sum().backward()
+    assert rel(vt_c.grad.cpu().numpy(), vt_o.grad.numpy()) <= TOL
+    for k in t:
+        assert rel(t[k].grad.cpu().numpy(), o[k].grad.numpy()) <= TOL, k
