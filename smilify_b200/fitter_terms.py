@@ -134,6 +134,8 @@ class FusedAdam:
                 self.lrs.append(float(lr))
         if not self.params:
             raise ValueError("FusedAdam: no parameters")
+        if len(self.params) > _lib.ADAM_MAX_TENSORS:   # one launch, one tick of the device step counter
+            raise ValueError("FusedAdam: at most %d parameter tensors (got %d)" % (_lib.ADAM_MAX_TENSORS, len(self.params)))
         dev = self.params[0].device
         for p in self.params:
             if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous() or p.device != dev:
@@ -167,8 +169,5 @@ class FusedAdam:
                     a.param[t], a.grad[t] = self.params[i].data_ptr(), g.data_ptr()
                     a.exp_avg[t], a.exp_avg_sq[t] = self.exp_avg[i].data_ptr(), self.exp_avg_sq[i].data_ptr()
                     a.numel[t], a.lr[t] = self.params[i].numel(), self.lrs[i]
-                # one counter per launch group would tick several times per step: only the first chunk ticks
                 a.step = self.step_count.data_ptr()
-                if c0 > 0:
-                    raise RuntimeError("FusedAdam: more than %d parameter tensors" % _lib.ADAM_MAX_TENSORS)
                 _lib.check(L.smil_adam_step(C.byref(a), _stream()), "smil_adam_step")
