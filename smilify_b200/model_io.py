@@ -61,7 +61,7 @@ def load_rig(path) -> dict:
     path = str(path)
     if path.endswith(".npz"):
         with np.load(path, allow_pickle=False) as z:
-            dd = {k: z[k] for k in z.files}
+            dd = {k: z[k] for k in z.files if not k.startswith("pack/") and k not in ("flat_format", "pack_key")}
         if "static_joint_locs" in dd:
             dd["static_joint_locs"] = bool(dd["static_joint_locs"])
         if "J_names" in dd:
@@ -152,3 +152,55 @@ def reference_layout(dd: dict, static_joints: bool, shape_family_betas=None) -> 
         weights=f32(dd["weights"]), parents=np.asarray(dd["kintree_table"])[0].astype(np.int32),   # :193
         J=f32(dd["J"]) if (static_joints and "J" in dd) else None,
     )
+
+
+FLAT_FORMAT = 1
+_FLAT_SKIP = ("J_names",)
+
+
+def export_flat(src_path, dst_path, static_joints=None) -> str:
+    """write a rig as ONE flat, pickle-free ``.npz`` -- the validated arrays of the SMPL-style
+    schema (``f, v_template, shapedirs, posedirs, J_regressor, J, weights, kintree_table, J_names, static_joint_locs`` and
+    whatever else the source holds as plain arrays: ``scaledirs, transdirs, shape_cov, shape_mean_betas, sym_verts``) plus
+    the PACKED device tables of the kernels (``pack/<name>``), so that a later ``SMAL`` construction neither unpickles
+    chumpy objects nor spends seconds in the packer.  ``config.SMAL_FILE`` may point at the result: :func:`load_rig` reads
+    ``.npz`` files with ``allow_pickle=False`` and ``packer.pack_model_cached`` is pre-seeded from the embedded tables
+    (:func:`embedded_pack`).  ``static_joints`` defaults to the file's own ``static_joint_locs`` flag."""
+    from . import packer
+
+    dd = load_rig(src_path)
+    static = bool(dd.get("static_joint_locs", False)) if static_joints is None else bool(static_joints)
+    lay = reference_layout(dd, static_joints=static)
+    tables = packer.pack_model(lay["v_template"], lay["shapedirs"], lay["posedirs"], lay["J_regressor"], lay["weights"],
+                               lay["parents"], lay["J"])
+    out = {"flat_format": np.asarray(FLAT_FORMAT), "pack_key": np.asarray(packer.pack_key(
+        lay["v_template"], lay["shapedirs"], lay["posedirs"], lay["J_regressor"], lay["weights"], lay["parents"], lay["J"]))}
+    for k, v in dd.items():
+        if k == "J_names":
+            out[k] = np.asarray([str(x) for x in v])
+        elif k == "static_joint_locs":
+            out[k] = np.asarray(bool(v))
+        else:
+            a = np.asarray(v)
+            if a.dtype == object:      # nothing that needs pickle goes into the flat file
+                continue
+            out[k] = a
+    for k, v in tables.items():
+        out["pack/" + k] = np.asarray(v)
+    np.savez(dst_path, **out)
+    return str(dst_path) if str(dst_path).endswith(".npz") else str(dst_path) + ".npz"
+
+
+def embedded_pack(path, key):
+    """The packed tables embedded in a flat rig file, if they were made for exactly this rig layout and packer version
+    (``key`` = ``packer.pack_key`` of the arrays about to be packed); else None."""
+    path = str(path)
+    if not path.endswith(".npz"):
+        return None
+    try:
+        with np.load(path, allow_pickle=False) as z:
+            if "pack_key" not in z.files or str(z["pack_key"]) != key:
+                return None
+            return {k[5:]: (z[k].item() if z[k].ndim == 0 else z[k]) for k in z.files if k.startswith("pack/")}
+    except Exception:
+        return None

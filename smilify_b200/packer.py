@@ -98,25 +98,39 @@ def tree_tables(parents: np.ndarray):
 PACK_FORMAT = 9   # bump when the meaning of a packed table changes: invalidates cached packs
 
 
-def pack_model_cached(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static=None, cache_dir=None):
-    """:func:`pack_model` through an on-disk cache: the packed tables of a rig as ONE flat ``.npz`` (every table a
-    plain fp32 / int32 array, scalars as 0-d arrays), keyed by a hash of the rig arrays, the pack format and the
-    packer's tuning switches.  The anchor search and the run ordering take seconds per rig; the 8 ranks of a launch
-    and every later process load the file instead.  ``SMILIFY_B200_CACHE`` names the directory ("" disables)."""
+def pack_key(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static=None) -> str:
+    """Hash of the rig arrays, the pack format and the packer's tuning switches: names a pack in the on-disk cache and
+    inside a flat rig file (model_io.export_flat)."""
     import hashlib
-    import tempfile
 
-    cache_dir = _os.environ.get("SMILIFY_B200_CACHE", _os.path.join(_os.path.expanduser("~"), ".cache", "smilify_b200")) \
-        if cache_dir is None else cache_dir
-    if not cache_dir:
-        return pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static)
     h = hashlib.sha1(repr((PACK_FORMAT, FWD_CHUNK, BWD_CHUNK, VM_CHUNK, VM_PHASES, VM_WARPS, VM_CUT_TOL, VM_SEG_COST, VM_FLUSH_COST, VM_TILE_BALANCE, VM_CHUNK_MAX,
                            sorted((k, v) for k, v in _os.environ.items() if k.startswith("SMIL_")))).encode())
     for a in (v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static):
         a = np.ascontiguousarray(np.asarray(a)) if a is not None else np.zeros(0)
         h.update(str((a.shape, a.dtype.str)).encode())
         h.update(a.tobytes())
-    path = _os.path.join(cache_dir, "pack_%s.npz" % h.hexdigest()[:24])
+    return h.hexdigest()[:24]
+
+
+def pack_model_cached(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static=None, cache_dir=None, source=None):
+    """:func:`pack_model` through an on-disk cache: the packed tables of a rig as ONE flat ``.npz`` (every table a
+    plain fp32 / int32 array, scalars as 0-d arrays), keyed by a hash of the rig arrays, the pack format and the
+    packer's tuning switches.  The anchor search and the run ordering take seconds per rig; the 8 ranks of a launch
+    and every later process load the file instead.  ``SMILIFY_B200_CACHE`` names the directory ("" disables)."""
+    import tempfile
+
+    key = pack_key(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static)
+    if source is not None:      # a flat rig file that carries its own pack (model_io.export_flat)
+        from .model_io import embedded_pack
+
+        t = embedded_pack(source, key)
+        if t is not None:
+            return t
+    cache_dir = _os.environ.get("SMILIFY_B200_CACHE", _os.path.join(_os.path.expanduser("~"), ".cache", "smilify_b200")) \
+        if cache_dir is None else cache_dir
+    if not cache_dir:
+        return pack_model(v_template, shapedirs, posedirs, J_regressor, weights, parents, J_static)
+    path = _os.path.join(cache_dir, "pack_%s.npz" % key)
     if _os.path.exists(path):
         try:
             with np.load(path, allow_pickle=False) as z:

@@ -103,7 +103,7 @@ class SMAL(nn.Module):
 
         self._device = device
         self._tables = packer.pack_model_cached(v_template, lay["shapedirs"], lay["posedirs"], lay["J_regressor"],
-                                         lay["weights"], lay["parents"], lay["J"])
+                                         lay["weights"], lay["parents"], lay["J"], source=cfg.SMAL_FILE)
         self._dm = DeviceModel(self._tables, device)  # raises on non-CUDA devices / missing library
 
     # the reference overrides __call__, not forward (smal_torch.py:198), so nn.Module hooks are bypassed

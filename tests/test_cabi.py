@@ -170,3 +170,28 @@ def test_rig_schema_validation_and_pack_cache(tmp_path):
         for other in (first, again):
             a, b = np.ascontiguousarray(np.asarray(v)), np.ascontiguousarray(np.asarray(other[k]))
             assert a.shape == b.shape and a.dtype == b.dtype and a.tobytes() == b.tobytes(), k
+
+
+def test_flat_rig_file_roundtrip_and_embedded_pack(tmp_path, monkeypatch):
+    """a rig exported as one pickle-free .npz loads to the same arrays, carries its packed
+    tables, and a stale embedded pack (another packer version) is ignored."""
+    import numpy as np
+
+    from smilify_b200 import model_io, packer
+    from tests import rigs
+
+    src = rigs.REAL_RIGS["stick"]
+    dst = model_io.export_flat(src, str(tmp_path / "stick_flat.npz"))
+    a, b = model_io.load_rig(src), model_io.load_rig(dst)
+    for k in ("v_template", "shapedirs", "posedirs", "J_regressor", "weights", "kintree_table", "f"):
+        assert np.array_equal(np.asarray(a[k]), np.asarray(b[k])), k
+    assert [str(x) for x in a["J_names"]] == list(b["J_names"])
+    with np.load(dst, allow_pickle=False) as z:      # nothing in the file needs pickle
+        assert "pack_key" in z.files and any(k.startswith("pack/") for k in z.files)
+    lay = model_io.reference_layout(b, static_joints=bool(b.get("static_joint_locs", False)))
+    args = (lay["v_template"], lay["shapedirs"], lay["posedirs"], lay["J_regressor"], lay["weights"], lay["parents"], lay["J"])
+    monkeypatch.setattr(packer, "pack_model", lambda *a_, **k_: (_ for _ in ()).throw(AssertionError("packed again")))
+    t = packer.pack_model_cached(*args, cache_dir="", source=dst)      # served from the file: the packer is not called
+    assert t["V"] == 3020 and t["vm_ok"]
+    monkeypatch.setattr(packer, "PACK_FORMAT", packer.PACK_FORMAT + 1)
+    assert model_io.embedded_pack(dst, packer.pack_key(*args)) is None  # other packer version: the embedded pack is stale

@@ -147,3 +147,23 @@ def test_v_template_override_is_differentiable():
     assert rel(vt_c.grad.cpu().numpy(), vt_o.grad.numpy()) <= TOL
     for k in t:
         assert rel(t[k].grad.cpu().numpy(), o[k].grad.numpy()) <= TOL, k
+
+
+def test_smal_from_flat_rig_file_equals_smal_from_pickle(tmp_path):
+    """``config.SMAL_FILE`` pointing at the flat pickle-free export gives the same model."""
+    import smilify_b200
+    from smilify_b200 import model_io
+    from smilify_b200.smal_torch import SMAL
+    from tests import rigs
+
+    dev = torch.device("cuda:0")
+    dd = rigs.get_rig("stick")
+    inp = rigs.make_inputs(dd, 5, seed=9)
+    t = {k: torch.from_numpy(inp[k]).to(dev) for k in ("beta", "theta", "trans")}
+    outs = []
+    for path in (rigs.REAL_RIGS["stick"], model_io.export_flat(rigs.REAL_RIGS["stick"], str(tmp_path / "stick_flat.npz"))):
+        smilify_b200.configure(path)
+        model = SMAL(dev)
+        outs.append(model(t["beta"], t["theta"], trans=t["trans"]))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
