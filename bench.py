@@ -438,7 +438,9 @@ def run_ours(args, rank, world, local_rank):
                 sink[0] += float(done["grad_trans"][0, 0])
         e2e_mode = ("HostPipeline depth %d: per step" % args.e2e_depth + " ONE pinned host->device copy (beta | theta | trans) and ONE "
                     "device->host copy (the parameter gradients: the step's result) overlap the kernels of neighbouring steps; "
-                    "posed vertices, joints and upstream gradients stay device-resident (the loss lives on the device)")
+                    "posed vertices, joints and upstream gradients stay device-resident (the loss lives on the device); with several "
+                    "steps in flight the latency-bound pose kernels of one step run under the skin kernels of another, so this "
+                    "number can exceed the single-stream `value`")
 
     e2e_run(3)
     barrier()
