@@ -181,3 +181,36 @@ def test_atomic_accumulation_spread_is_rounding_only():
     for r in runs[1:]:
         for a, b in zip(runs[0], r):
             assert float((a - b).abs().max() / a.abs().max()) < 2e-6
+
+
+def test_guard_bands_fitter_terms_and_adam(guard):
+    """The fitter objective kernel (dense pose-prior path, shard with both halos) and the fused Adam: no write outside
+    their buffers, no unwritten output (a NaN from the poisoned allocations would show in the results)."""
+    from smilify_b200.fitter_terms import FusedAdam, fitter_prior_terms
+
+    rs = np.random.RandomState(3)
+    n, J, nB = 37, 35, 6
+    f = lambda *s: torch.from_numpy(rs.standard_normal(s).astype(np.float32)).to(DEV)
+    g, j, tr, be = f(n, 3).requires_grad_(True), f(n, J - 1, 3).requires_grad_(True), f(n, 3).requires_grad_(True), f(nB).requires_grad_(True)
+    P = 3 * J
+    loss = fitter_prior_terms(g, j, tr, be, dict(w_limit=1.0, w_pose=0.5, w_splay=0.1, w_betas=0.3, w_temp=0.2), window=10,
+                              max_limits=f(J - 1, 3).abs(), min_limits=-f(J - 1, 3).abs(), betas_mean=f(nB), betas_prec=f(nB, nB),
+                              pose_prior=dict(mean=f(P), precs=f(P, P) * 0.1, use=(f(P) > 0).float()),
+                              frame_offset=20, total_frames=100, halo_prev=f(P + 3), halo_next=f(P + 3))
+    loss.backward()
+    for t in (g, j, tr, be):
+        assert bool(torch.isfinite(t.grad).all())
+    assert bool(torch.isfinite(loss))
+    nbuf, bad = guard.check()
+    assert nbuf >= 5 and not bad, bad
+    # Adam updates caller tensors in place: surround them with guard bands by hand
+    raw = torch.full((3, 4096 + 1001 + 4096), float("nan"), device=DEV)
+    p, m_, v_ = (raw[i, 4096:4096 + 1001] for i in range(3))
+    p.copy_(f(1001)); m_.zero_(); v_.zero_()
+    opt = FusedAdam([p.detach()], lr=1e-2)
+    opt.exp_avg[0], opt.exp_avg_sq[0] = m_, v_
+    opt.params[0] = p
+    opt.step([f(1001)])
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(raw[:, 4096:4096 + 1001]).all())
+    assert bool(torch.isnan(raw[:, :4096]).all()) and bool(torch.isnan(raw[:, 4096 + 1001:]).all())
