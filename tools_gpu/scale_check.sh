@@ -13,6 +13,7 @@ for N in (1,2,4,8):
         print(N,"failed",e); continue
     if N==1: base=d
     f=d.get("fitter") or {}
-    print(N, "value %.2fM eff %.3f | e2e %.2fM eff %.3f (%.4f ms) | fitter %s %s"%(d["value"]/1e6, d["value"]/base["value"]/N, d["e2e"]["value"]/1e6, d["e2e"]["value"]/base["e2e"]["value"]/N, d["e2e"]["ms_per_step"], f.get("value"), f.get("launch")))
+    ff=d.get("fitter_full") or {}
+    print(N, "value %.2fM eff %.3f | single %.2fM | e2e %.2fM eff %.3f (%.4f ms) | fitter %s full %s"%(d["value"]/1e6, d["value"]/base["value"]/N, d["value_single_stream"]["value"]/1e6, d["e2e"]["value"]/1e6, d["e2e"]["value"]/base["e2e"]["value"]/N, d["e2e"]["ms_per_step"], f.get("value"), ff.get("value")))
 PY
 nvidia-smi topo -m | head -12; lscpu | grep -i "numa\|^CPU(s)"
